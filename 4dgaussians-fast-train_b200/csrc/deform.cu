@@ -1,0 +1,849 @@
+// Fused HexPlane sampler + deformation MLP, forward and backward, for sm_100a.
+//
+// Replaces deform_network.forward / Deformation.forward_dynamic (scene/deformation.py:97-148,185-212)
+// and HexPlaneField.forward (scene/hexplane.py:73-106,160-183) — ~200 ATen launches forward and ~400
+// backward per view in the reference — by one kernel per direction (+ tiny pack/unpack helpers).
+//
+// Data layout in HBM
+//   * planes are repacked channel-LAST ([H][W][C]) once per parameter version, so the C channels of a
+//     bilinear corner are one or two 32-byte sectors instead of C scattered ones;
+//   * the three time planes of every level are pre-blended per view into [W][C] row tables
+//     (all points of a view share one timestamp), which halves their gathers and removes the
+//     reference's two-row atomic hot spot in the backward;
+//   * activations never leave the SM: feat / h / z live in shared memory, k-major with a padded pitch.
+//
+// This file is the FP32 SIMT implementation of the MLP tile GEMMs (exact FP32, used for parity);
+// the tile structure (128 points x Wn) is the one the tcgen05 path uses.
+#include "fdgs_common.cuh"
+
+namespace {
+
+constexpr int TP = 128;      // points per tile
+constexpr int TPP = 132;     // padded pitch of the k-major activation tiles (16-byte aligned rows)
+constexpr int NT = 256;      // threads per CTA
+constexpr int KC = 32;       // reduction chunk staged per step
+constexpr int BP = 132;      // pitch of the staged weight chunk
+
+__host__ __device__ constexpr int pa_of(int k) { return k < 3 ? 0 : (k < 5 ? 1 : 2); }
+__host__ __device__ constexpr int pb_of(int k) { return k == 0 ? 1 : (k == 1 || k == 3) ? 2 : 3; }
+static const int h_pa[6] = {0, 0, 0, 1, 1, 2};
+static const int h_pb[6] = {1, 2, 3, 2, 3, 3};
+static const int h_tslot[6] = {-1, -1, 0, -1, 1, 2};   // time-plane slot of plane k
+
+struct Layout {
+    int L, C, F, Wn, depth, head_mask, apply_rotation;
+    int pw[FDGS_MAX_LEVELS][6], ph[FDGS_MAX_LEVELS][6];
+    long long poff[FDGS_MAX_LEVELS][6];     // float offset of packed plane [H][W][C]
+    long long toff[FDGS_MAX_LEVELS][3];     // float offset of per-view time row table [W][C] (slots: xt, yt, zt)
+    long long plane_floats, trow_floats;
+    float aabb[6];
+};
+
+static int make_layout(const FdgsDeformNet& n, Layout& lo) {
+    if (n.levels < 1 || n.levels > FDGS_MAX_LEVELS) return FDGS_E_BADARG;
+    if (!(n.channels == 4 || (n.channels % 8 == 0 && n.channels >= 8 && n.channels <= 64))) return FDGS_E_UNSUPPORTED;
+    if (n.width != 64 && n.width != 128) return FDGS_E_UNSUPPORTED;
+    lo.L = n.levels; lo.C = n.channels; lo.F = n.levels * n.channels; lo.Wn = n.width;
+    lo.depth = n.depth < 1 ? 1 : n.depth;
+    if (lo.depth > 8) return FDGS_E_UNSUPPORTED;
+    if (lo.F > 128) return FDGS_E_UNSUPPORTED;
+    lo.head_mask = n.head_mask; lo.apply_rotation = n.apply_rotation;
+    long long off = 0, toff = 0;
+    for (int l = 0; l < lo.L; ++l)
+        for (int k = 0; k < 6; ++k) {
+            lo.pw[l][k] = n.res[l][h_pa[k]];
+            lo.ph[l][k] = n.res[l][h_pb[k]];
+            if (lo.pw[l][k] < 2 || lo.ph[l][k] < 2) return FDGS_E_BADARG;
+            lo.poff[l][k] = off;
+            off += (long long)lo.pw[l][k] * lo.ph[l][k] * lo.C;
+            if (h_tslot[k] >= 0) { lo.toff[l][h_tslot[k]] = toff; toff += (long long)lo.pw[l][k] * lo.C; }
+        }
+    lo.plane_floats = off; lo.trow_floats = toff;
+    for (int i = 0; i < 6; ++i) lo.aabb[i] = n.aabb[i];
+    return FDGS_OK;
+}
+
+struct NetPtrs {
+    const float* planes[FDGS_MAX_LEVELS][6];
+    const float* trunk_w[8]; const float* trunk_b[8];
+    const float* w1[FDGS_NUM_HEADS]; const float* b1[FDGS_NUM_HEADS];
+    const float* w2[FDGS_NUM_HEADS]; const float* b2[FDGS_NUM_HEADS];
+};
+struct GradPtrs {
+    float* planes[FDGS_MAX_LEVELS][6];
+    float* trunk_w[8]; float* trunk_b[8];
+    float* w1[FDGS_NUM_HEADS]; float* b1[FDGS_NUM_HEADS];
+    float* w2[FDGS_NUM_HEADS]; float* b2[FDGS_NUM_HEADS];
+};
+
+__host__ __device__ inline int head_out(int h) { return h == 0 ? 3 : h == 1 ? 3 : h == 2 ? 4 : h == 3 ? 1 : 48; }
+
+// ATen grid_sampler coordinate mapping, align_corners=True, padding_mode='border'
+// (ATen/native/GridSampler.h: grid_sampler_unnormalize + clip_coordinates).
+__device__ __forceinline__ float unnorm_clip(float q, int size, float* gmul = nullptr) {
+    float ix = ((q + 1.f) / 2) * (float)(size - 1);
+    if (gmul) *gmul = (ix <= 0.f || ix >= (float)(size - 1)) ? 0.f : (float)(size - 1) * 0.5f;
+    return fminf((float)(size - 1), fmaxf(ix, 0.f));
+}
+
+// ---- pack / unpack --------------------------------------------------------------------------------
+__global__ void k_pack_plane(const float* __restrict__ src /*[C][H][W]*/, float* __restrict__ dst /*[H][W][C]*/,
+                             int C, int HW) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;      // over HW*C, dst-major
+    if (i >= HW * C) return;
+    const int c = i % C, p = i / C;
+    dst[i] = src[(size_t)c * HW + p];
+}
+
+// time rows: trow[x][c] = wy0 * P[y0][x][c] + wy1 * P[y0+1][x][c]   (packed planes in, per view)
+__global__ void k_time_rows(Layout lo, const float* __restrict__ packed, float* __restrict__ trow, float time) {
+    const int l = blockIdx.y / 3, slot = blockIdx.y % 3;
+    if (l >= lo.L) return;
+    const int k = slot == 0 ? 2 : slot == 1 ? 4 : 5;
+    const int W = lo.pw[l][k], H = lo.ph[l][k], C = lo.C;
+    const float iy = unnorm_clip(time, H);
+    const float y0f = floorf(iy);
+    const int y0 = (int)y0f;
+    const float wy0 = (y0f + 1.f) - iy, wy1 = iy - y0f;
+    const float* P = packed + lo.poff[l][k];
+    float* T = trow + lo.toff[l][slot];
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < W * C; i += gridDim.x * blockDim.x) {
+        float v = P[(size_t)y0 * W * C + i] * wy0;
+        if (y0 + 1 < H) v += P[(size_t)(y0 + 1) * W * C + i] * wy1;
+        T[i] = v;
+    }
+}
+
+// d_planes[c][y][x] += packed_grad[y][x][c]                      (spatial planes)
+__global__ void k_unpack_spatial(float* __restrict__ dst /*[C][H][W]*/, const float* __restrict__ g /*[H][W][C]*/,
+                                 int C, int HW) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;      // over C*HW, dst-major
+    if (i >= HW * C) return;
+    const int c = i / HW, p = i % HW;
+    const float v = g[(size_t)p * C + c];
+    if (v != 0.f) dst[i] += v;
+}
+// time planes: only rows y0 and y0+1 receive gradient
+__global__ void k_unpack_time(float* __restrict__ dst /*[C][H][W]*/, const float* __restrict__ gt /*[W][C]*/,
+                              int C, int H, int W, float time) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;      // over C*W
+    if (i >= C * W) return;
+    const int c = i / W, x = i % W;
+    const float iy = unnorm_clip(time, H);
+    const float y0f = floorf(iy);
+    const int y0 = (int)y0f;
+    const float wy0 = (y0f + 1.f) - iy, wy1 = iy - y0f;
+    const float v = gt[(size_t)x * C + c];
+    if (v == 0.f) return;
+    dst[((size_t)c * H + y0) * W + x] += wy0 * v;
+    if (y0 + 1 < H) dst[((size_t)c * H + y0 + 1) * W + x] += wy1 * v;
+}
+
+// ---- shared-memory tile GEMM (FP32 SIMT) ------------------------------------------------------------
+// acc[i][g*4+j] += sum_r Xs[r][ty*8+i] * Wm(r, o)   with o = g*64 + tx*4 + j, Wm(r,o) = Wg[o*so + r*sr]
+template <int G>
+__device__ __forceinline__ void gemm_acc(float (&acc)[8][4 * G], const float* __restrict__ Xs, int K,
+                                         const float* __restrict__ Wg, int so, int sr, int NO, float* __restrict__ Bs) {
+    const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+    constexpr int NOP = 64 * G;
+    for (int k0 = 0; k0 < K; k0 += KC) {
+        const int kc = min(KC, K - k0);
+        __syncthreads();
+        if (sr == 1) {          // reduce index contiguous in memory: coalesce along r
+            for (int idx = threadIdx.x; idx < NOP * KC; idx += NT) {
+                const int r = idx % KC, o = idx / KC;
+                Bs[r * BP + o] = (o < NO && r < kc) ? Wg[(size_t)o * so + (k0 + r)] : 0.f;
+            }
+        } else {                // output index contiguous in memory
+            for (int idx = threadIdx.x; idx < NOP * KC; idx += NT) {
+                const int o = idx % NOP, r = idx / NOP;
+                Bs[r * BP + o] = (o < NO && r < kc) ? Wg[(size_t)o * so + (size_t)(k0 + r) * sr] : 0.f;
+            }
+        }
+        __syncthreads();
+#pragma unroll 4
+        for (int r = 0; r < kc; ++r) {
+            const float4 a0 = *reinterpret_cast<const float4*>(Xs + (k0 + r) * TPP + ty * 8);
+            const float4 a1 = *reinterpret_cast<const float4*>(Xs + (k0 + r) * TPP + ty * 8 + 4);
+            const float a[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+#pragma unroll
+            for (int g = 0; g < G; ++g) {
+                const float4 b4 = *reinterpret_cast<const float4*>(Bs + r * BP + g * 64 + tx * 4);
+                const float b[4] = {b4.x, b4.y, b4.z, b4.w};
+#pragma unroll
+                for (int i = 0; i < 8; ++i)
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) acc[i][g * 4 + j] += a[i] * b[j];
+            }
+        }
+    }
+}
+
+// dW[o][k] += sum_pt Gs[o][pt] * Xs[k][pt]  (atomics into global), db[o] += sum_pt Gs[o][pt]
+__device__ __forceinline__ void wgrad(const float* __restrict__ Gs, int NO, const float* __restrict__ Xs, int K,
+                                      float* __restrict__ dW, float* __restrict__ db) {
+    const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+    for (int o0 = 0; o0 < NO; o0 += 128) {
+        float acc[8][8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
+        bool any_o = false;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) any_o |= (o0 + ty * 8 + i) < NO;
+        if (any_o) {
+            for (int p4 = 0; p4 < TP; p4 += 4) {
+                float4 g[8], x[8];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const int o = o0 + ty * 8 + i;
+                    g[i] = (o < NO) ? *reinterpret_cast<const float4*>(Gs + o * TPP + p4) : make_float4(0.f, 0.f, 0.f, 0.f);
+                }
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const int k = tx + 16 * j;
+                    x[j] = (k < K) ? *reinterpret_cast<const float4*>(Xs + k * TPP + p4) : make_float4(0.f, 0.f, 0.f, 0.f);
+                }
+#pragma unroll
+                for (int i = 0; i < 8; ++i)
+#pragma unroll
+                    for (int j = 0; j < 8; ++j)
+                        acc[i][j] += g[i].x * x[j].x + g[i].y * x[j].y + g[i].z * x[j].z + g[i].w * x[j].w;
+            }
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const int o = o0 + ty * 8 + i;
+                if (o < NO) {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        const int k = tx + 16 * j;
+                        if (k < K && acc[i][j] != 0.f) atomicAdd(&dW[(size_t)o * K + k], acc[i][j]);
+                    }
+                }
+            }
+        }
+    }
+    if (db) {
+        for (int o = threadIdx.x; o < NO; o += NT) {
+            float s = 0.f;
+            for (int p = 0; p < TP; ++p) s += Gs[o * TPP + p];
+            if (s != 0.f) atomicAdd(&db[o], s);
+        }
+    }
+}
+
+// ---- sampling ------------------------------------------------------------------------------------------
+struct PlaneTap {            // one plane's bilinear tap for one point
+    int i00, i01, i10, i11;  // element offsets (already * C) or -1 when out of range
+    float w00, w01, w10, w11;
+};
+
+__device__ __forceinline__ void point_coords(const Layout& lo, const float* __restrict__ xyz, int p, float time, float q[4]) {
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        const float mx = lo.aabb[a], mn = lo.aabb[3 + a];
+        q[a] = (xyz[3 * (size_t)p + a] - mx) * (2.0f / (mn - mx)) - 1.0f;
+    }
+    q[3] = time;
+}
+
+// Forward sample of NCH consecutive channels [c0, c0+NCH) of level l for one point into prod[].
+template <int NCH>
+__device__ __forceinline__ void sample_level(const Layout& lo, int l, const float q[4], const float* __restrict__ packed,
+                                             const float* __restrict__ trow, int c0, float (&prod)[NCH]) {
+    const int C = lo.C;
+#pragma unroll
+    for (int c = 0; c < NCH; ++c) prod[c] = 1.f;
+#pragma unroll
+    for (int k = 0; k < 6; ++k) {
+        const int a = pa_of(k);
+        const int W = lo.pw[l][k];
+        const float ix = unnorm_clip(q[a], W);
+        const float x0f = floorf(ix);
+        const int x0 = (int)x0f;
+        const float wx0 = (x0f + 1.f) - ix, wx1 = ix - x0f;
+        const bool xin = x0 + 1 < W;
+        float s[NCH];
+        if (k == 2 || k == 4 || k == 5) {
+            const float* T = trow + lo.toff[l][k == 2 ? 0 : (k == 4 ? 1 : 2)] + c0;
+#pragma unroll
+            for (int c4 = 0; c4 < NCH; c4 += 4) {
+                const float4 v0 = *reinterpret_cast<const float4*>(T + (size_t)x0 * C + c4);
+                float4 v1 = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (xin) v1 = *reinterpret_cast<const float4*>(T + (size_t)(x0 + 1) * C + c4);
+                s[c4 + 0] = v0.x * wx0 + v1.x * wx1; s[c4 + 1] = v0.y * wx0 + v1.y * wx1;
+                s[c4 + 2] = v0.z * wx0 + v1.z * wx1; s[c4 + 3] = v0.w * wx0 + v1.w * wx1;
+            }
+        } else {
+            const int b = pb_of(k);
+            const int H = lo.ph[l][k];
+            const float iy = unnorm_clip(q[b], H);
+            const float y0f = floorf(iy);
+            const int y0 = (int)y0f;
+            const float wy0 = (y0f + 1.f) - iy, wy1 = iy - y0f;
+            const bool yin = y0 + 1 < H;
+            const float nw = wx0 * wy0, ne = wx1 * wy0, sw = wx0 * wy1, se = wx1 * wy1;
+            const float* Pp = packed + lo.poff[l][k] + c0;
+            const size_t o00 = ((size_t)y0 * W + x0) * C;
+#pragma unroll
+            for (int c4 = 0; c4 < NCH; c4 += 4) {
+                const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+                const float4 v00 = *reinterpret_cast<const float4*>(Pp + o00 + c4);
+                const float4 v01 = xin ? *reinterpret_cast<const float4*>(Pp + o00 + C + c4) : z4;
+                const float4 v10 = yin ? *reinterpret_cast<const float4*>(Pp + o00 + (size_t)W * C + c4) : z4;
+                const float4 v11 = (xin && yin) ? *reinterpret_cast<const float4*>(Pp + o00 + (size_t)W * C + C + c4) : z4;
+                s[c4 + 0] = v00.x * nw + v01.x * ne + v10.x * sw + v11.x * se;
+                s[c4 + 1] = v00.y * nw + v01.y * ne + v10.y * sw + v11.y * se;
+                s[c4 + 2] = v00.z * nw + v01.z * ne + v10.z * sw + v11.z * se;
+                s[c4 + 3] = v00.w * nw + v01.w * ne + v10.w * sw + v11.w * se;
+            }
+        }
+#pragma unroll
+        for (int c = 0; c < NCH; ++c) prod[c] *= s[c];
+    }
+}
+
+// feat tile: Fs[(l*C + c)][pt], pt = tid & 127, channel half = tid >> 7
+__device__ __forceinline__ void sample_tile(const Layout& lo, const float* __restrict__ xyz, int P, int p0, float time,
+                                            const float* __restrict__ packed, const float* __restrict__ trow,
+                                            float* __restrict__ Fs) {
+    const int pt = threadIdx.x & (TP - 1), half = threadIdx.x >> 7;
+    const int p = p0 + pt;
+    const int C = lo.C, CH = C >> 1;      // channels per thread (C/2, multiple of 2; handled in groups of 4 or 2)
+    float q[4];
+    if (p < P) point_coords(lo, xyz, p, time, q);
+    for (int l = 0; l < lo.L; ++l) {
+        for (int cc = 0; cc < CH; cc += 4) {
+            // CH is a multiple of 4 for C in {8,16,32,64}; C == 4 falls back to half 0 doing all 4
+            const int c0 = half * CH + cc;
+            float prod[4] = {0.f, 0.f, 0.f, 0.f};
+            if (CH >= 4) {
+                if (p < P) sample_level<4>(lo, l, q, packed, trow, c0, prod);
+#pragma unroll
+                for (int c = 0; c < 4; ++c) Fs[(l * C + c0 + c) * TPP + pt] = prod[c];
+            }
+        }
+        if (CH < 4) {         // C == 4
+            if (half == 0) {
+                float prod[4] = {0.f, 0.f, 0.f, 0.f};
+                if (p < P) sample_level<4>(lo, l, q, packed, trow, 0, prod);
+#pragma unroll
+                for (int c = 0; c < 4; ++c) Fs[(l * C + c) * TPP + pt] = prod[c];
+            }
+        }
+    }
+}
+
+// ---- forward kernel ------------------------------------------------------------------------------------
+struct FwdIO {
+    int P, sh_coeffs;
+    float time;
+    const float *xyz, *scales, *rot, *opacity, *shs;
+    float *o_xyz, *o_scales, *o_rot, *o_opacity, *o_shs;
+};
+
+template <int WN>
+__device__ __forceinline__ void trunk_forward(const Layout& lo, const NetPtrs& net, const float* Fs, float* Hs, float* Zs, float* Bs) {
+    constexpr int G = WN / 64;
+    const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+    const float* X = Fs;
+    int K = lo.F;
+    for (int d = 0; d < lo.depth; ++d) {
+        float acc[8][4 * G];
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+#pragma unroll
+            for (int j = 0; j < 4 * G; ++j) acc[i][j] = 0.f;
+        gemm_acc<G>(acc, X, K, net.trunk_w[d], K, 1, WN, Bs);
+        // every consumer applies ReLU first (next trunk layer or the heads): store relu(h)
+        float* Y = (d == lo.depth - 1) ? Hs : ((d & 1) ? Hs : Zs);
+        if (d == lo.depth - 1 && X == Hs) Y = Hs;   // in-place is safe only after the sync below
+        __syncthreads();
+#pragma unroll
+        for (int g = 0; g < G; ++g)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const int o = g * 64 + tx * 4 + j;
+                const float bv = net.trunk_b[d][o];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) Y[o * TPP + ty * 8 + i] = fmaxf(acc[i][g * 4 + j] + bv, 0.f);
+            }
+        __syncthreads();
+        X = Y; K = WN;
+    }
+}
+
+template <int WN>
+__global__ void __launch_bounds__(NT, 1)
+k_deform_fwd(Layout lo, NetPtrs net, FwdIO io, const float* __restrict__ packed, const float* __restrict__ trow, int ntiles) {
+    extern __shared__ __align__(16) float smem[];
+    constexpr int G = WN / 64;
+    float* Fs = smem;                         // [F][TPP]   (F <= 128)
+    float* Hs = Fs + 128 * TPP;               // [WN][TPP]
+    float* Zs = Hs + WN * TPP;                // [WN][TPP]
+    float* Bs = Zs + WN * TPP;                // [KC][BP]
+    const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        const int p0 = tile * TP;
+        __syncthreads();
+        sample_tile(lo, io.xyz, io.P, p0, io.time, packed, trow, Fs);
+        __syncthreads();
+        trunk_forward<WN>(lo, net, Fs, Hs, Zs, Bs);     // Hs = relu(h)
+
+        for (int h = 0; h < FDGS_NUM_HEADS; ++h) {
+            if (!((lo.head_mask >> h) & 1)) continue;
+            {
+                float acc[8][4 * G];
+#pragma unroll
+                for (int i = 0; i < 8; ++i)
+#pragma unroll
+                    for (int j = 0; j < 4 * G; ++j) acc[i][j] = 0.f;
+                gemm_acc<G>(acc, Hs, WN, net.w1[h], WN, 1, WN, Bs);
+                __syncthreads();
+#pragma unroll
+                for (int g = 0; g < G; ++g)
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        const int o = g * 64 + tx * 4 + j;
+                        const float bv = net.b1[h][o];
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) Zs[o * TPP + ty * 8 + i] = fmaxf(acc[i][g * 4 + j] + bv, 0.f);
+                    }
+                __syncthreads();
+            }
+            const int NO = head_out(h);
+            float acc2[8][4];
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) acc2[i][j] = 0.f;
+            gemm_acc<1>(acc2, Zs, WN, net.w2[h], WN, 1, NO, Bs);
+            float* outp = h == 0 ? io.o_xyz : h == 1 ? io.o_scales : h == 2 ? io.o_rot : h == 3 ? io.o_opacity : io.o_shs;
+            const float* inp = h == 0 ? io.xyz : h == 1 ? io.scales : h == 2 ? io.rot : h == 3 ? io.opacity : io.shs;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const int o = tx * 4 + j;
+                if (o < NO) {
+                    const float bv = net.b2[h][o];
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        const int p = p0 + ty * 8 + i;
+                        if (p < io.P) {
+                            float base;
+                            if (h == 2 && lo.apply_rotation) base = 0.f;
+                            else if (h == 4) base = (io.sh_coeffs == 16) ? inp[(size_t)p * 48 + o] : inp[(size_t)p * io.sh_coeffs * 3 + (o % 3)];
+                            else base = inp[(size_t)p * NO + o];
+                            outp[(size_t)p * NO + o] = base + (acc2[i][j] + bv);
+                        }
+                    }
+                }
+            }
+        }
+    }
+}
+
+// ---- backward kernel -----------------------------------------------------------------------------------
+struct BwdIO {
+    int P;
+    float time;
+    const float* xyz;
+    const float* g[FDGS_NUM_HEADS];
+    float* d_xyz;
+};
+
+template <int WN>
+__global__ void __launch_bounds__(NT, 1)
+k_deform_bwd(Layout lo, NetPtrs net, GradPtrs gp, BwdIO io, const float* __restrict__ packed, const float* __restrict__ trow,
+             float* __restrict__ gpacked, float* __restrict__ gtrow, int ntiles) {
+    extern __shared__ __align__(16) float smem[];
+    constexpr int G = WN / 64;
+    float* Fs = smem;                         // [F][TPP]
+    float* Hs = Fs + 128 * TPP;               // [WN][TPP]  relu(h); later g_feat
+    float* Zs = Hs + WN * TPP;                // [WN][TPP]  relu(z) -> g_z ; later g_h
+    float* Gos = Zs + WN * TPP;               // [48][TPP]  upstream grads of the current head
+    float* Bs = Gos + 48 * TPP;               // [KC][BP]
+    const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        const int p0 = tile * TP;
+        __syncthreads();
+        sample_tile(lo, io.xyz, io.P, p0, io.time, packed, trow, Fs);
+        __syncthreads();
+        trunk_forward<WN>(lo, net, Fs, Hs, Zs, Bs);     // depth == 1 enforced by the host for backward
+
+        float acc_h[8][4 * G];
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+#pragma unroll
+            for (int j = 0; j < 4 * G; ++j) acc_h[i][j] = 0.f;
+
+        for (int h = 0; h < FDGS_NUM_HEADS; ++h) {
+            if (!((lo.head_mask >> h) & 1) || io.g[h] == nullptr) continue;
+            const int NO = head_out(h);
+            // z = relu(W1 relu(h) + b1)
+            {
+                float acc[8][4 * G];
+#pragma unroll
+                for (int i = 0; i < 8; ++i)
+#pragma unroll
+                    for (int j = 0; j < 4 * G; ++j) acc[i][j] = 0.f;
+                gemm_acc<G>(acc, Hs, WN, net.w1[h], WN, 1, WN, Bs);
+                __syncthreads();
+#pragma unroll
+                for (int g = 0; g < G; ++g)
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        const int o = g * 64 + tx * 4 + j;
+                        const float bv = net.b1[h][o];
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) Zs[o * TPP + ty * 8 + i] = fmaxf(acc[i][g * 4 + j] + bv, 0.f);
+                    }
+            }
+            // stage upstream grads, k-major
+            for (int idx = threadIdx.x; idx < NO * TP; idx += NT) {
+                const int pt = idx / NO, o = idx % NO;      // coalesced global read
+                const int p = p0 + pt;
+                Gos[o * TPP + pt] = (p < io.P) ? io.g[h][(size_t)p * NO + o] : 0.f;
+            }
+            __syncthreads();
+            wgrad(Gos, NO, Zs, WN, gp.w2[h], gp.b2[h]);                 // dW2 += g_o^T relu(z)
+            // g_relu_z = g_o W2   (reduce over NO)
+            {
+                float acc[8][4 * G];
+#pragma unroll
+                for (int i = 0; i < 8; ++i)
+#pragma unroll
+                    for (int j = 0; j < 4 * G; ++j) acc[i][j] = 0.f;
+                gemm_acc<G>(acc, Gos, NO, net.w2[h], 1, WN, WN, Bs);   // Wm(r=n, o=k) = W2[n*WN + k]
+                __syncthreads();                                        // wgrad finished reading Zs
+#pragma unroll
+                for (int g = 0; g < G; ++g)
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        const int o = g * 64 + tx * 4 + j;
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) {
+                            const int a = o * TPP + ty * 8 + i;
+                            Zs[a] = (Zs[a] > 0.f) ? acc[i][g * 4 + j] : 0.f;   // g_z
+                        }
+                    }
+                __syncthreads();
+            }
+            wgrad(Zs, WN, Hs, WN, gp.w1[h], gp.b1[h]);                  // dW1 += g_z^T relu(h)
+            gemm_acc<G>(acc_h, Zs, WN, net.w1[h], 1, WN, WN, Bs);       // g_relu_h += g_z W1
+        }
+        // g_h = g_relu_h * [h > 0]  -> Zs
+        __syncthreads();
+#pragma unroll
+        for (int g = 0; g < G; ++g)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const int o = g * 64 + tx * 4 + j;
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const int a = o * TPP + ty * 8 + i;
+                    Zs[a] = (Hs[a] > 0.f) ? acc_h[i][g * 4 + j] : 0.f;
+                }
+            }
+        __syncthreads();
+        wgrad(Zs, WN, Fs, lo.F, gp.trunk_w[0], gp.trunk_b[0]);          // dW0 += g_h^T feat
+        // g_feat = g_h W0 -> Hs[f][pt]   (F <= 128: up to two 64-wide groups)
+        {
+            float acc[8][8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+#pragma unroll
+                for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
+            gemm_acc<2>(acc, Zs, WN, net.trunk_w[0], 1, lo.F, lo.F, Bs); // Wm(r=n, o=f) = W0[n*F + f]
+            __syncthreads();
+#pragma unroll
+            for (int g = 0; g < 2; ++g)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const int o = g * 64 + tx * 4 + j;
+                    if (o < lo.F) {
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) Hs[o * TPP + ty * 8 + i] = acc[i][g * 4 + j];
+                    }
+                }
+            __syncthreads();
+        }
+        // ---- sampler backward: thread = (point, channel half) ------------------------------------------
+        {
+            const int pt = threadIdx.x & (TP - 1), half = threadIdx.x >> 7;
+            const int p = p0 + pt;
+            const int C = lo.C;
+            const int CH = (C >= 8) ? (C >> 1) : C;
+            const bool worker = (p < io.P) && (C >= 8 || half == 0);
+            float dq[3] = {0.f, 0.f, 0.f};
+            if (worker) {
+                float q[4];
+                point_coords(lo, io.xyz, p, io.time, q);
+                for (int l = 0; l < lo.L; ++l) {
+                    for (int cc = 0; cc < CH; cc += 4) {
+                        const int c0 = ((C >= 8) ? half * CH : 0) + cc;
+                        // recompute the six per-plane samples of these 4 channels
+                        float s[6][4];
+                        float gx_c[6][4];       // d s_k / d ix  (per channel), for the coordinate grads
+                        float gy_c[6][4];
+                        float gmx[6], gmy[6];
+                        int x0a[6], y0a[6]; float wx0a[6], wx1a[6], wy0a[6], wy1a[6]; bool xina[6], yina[6];
+#pragma unroll
+                        for (int k = 0; k < 6; ++k) {
+                            const int a = pa_of(k);
+                            const int W = lo.pw[l][k];
+                            const float ix = unnorm_clip(q[a], W, &gmx[k]);
+                            const float x0f = floorf(ix);
+                            const int x0 = (int)x0f;
+                            const float wx0 = (x0f + 1.f) - ix, wx1 = ix - x0f;
+                            const bool xin = x0 + 1 < W;
+                            x0a[k] = x0; wx0a[k] = wx0; wx1a[k] = wx1; xina[k] = xin;
+                            const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+                            if (k == 2 || k == 4 || k == 5) {
+                                const float* T = trow + lo.toff[l][k == 2 ? 0 : (k == 4 ? 1 : 2)] + c0;
+                                const float4 v0 = *reinterpret_cast<const float4*>(T + (size_t)x0 * C);
+                                const float4 v1 = xin ? *reinterpret_cast<const float4*>(T + (size_t)(x0 + 1) * C) : z4;
+                                const float a0[4] = {v0.x, v0.y, v0.z, v0.w}, a1[4] = {v1.x, v1.y, v1.z, v1.w};
+#pragma unroll
+                                for (int c = 0; c < 4; ++c) {
+                                    s[k][c] = a0[c] * wx0 + a1[c] * wx1;
+                                    gx_c[k][c] = a1[c] - a0[c];
+                                    gy_c[k][c] = 0.f;
+                                }
+                                gmy[k] = 0.f; y0a[k] = 0; wy0a[k] = 0.f; wy1a[k] = 0.f; yina[k] = false;
+                            } else {
+                                const int b = pb_of(k);
+                                const int H = lo.ph[l][k];
+                                const float iy = unnorm_clip(q[b], H, &gmy[k]);
+                                const float y0f = floorf(iy);
+                                const int y0 = (int)y0f;
+                                const float wy0 = (y0f + 1.f) - iy, wy1 = iy - y0f;
+                                const bool yin = y0 + 1 < H;
+                                y0a[k] = y0; wy0a[k] = wy0; wy1a[k] = wy1; yina[k] = yin;
+                                const float* Pp = packed + lo.poff[l][k] + c0;
+                                const size_t o00 = ((size_t)y0 * W + x0) * C;
+                                const float4 v00 = *reinterpret_cast<const float4*>(Pp + o00);
+                                const float4 v01 = xin ? *reinterpret_cast<const float4*>(Pp + o00 + C) : z4;
+                                const float4 v10 = yin ? *reinterpret_cast<const float4*>(Pp + o00 + (size_t)W * C) : z4;
+                                const float4 v11 = (xin && yin) ? *reinterpret_cast<const float4*>(Pp + o00 + (size_t)W * C + C) : z4;
+                                const float a00[4] = {v00.x, v00.y, v00.z, v00.w}, a01[4] = {v01.x, v01.y, v01.z, v01.w};
+                                const float a10[4] = {v10.x, v10.y, v10.z, v10.w}, a11[4] = {v11.x, v11.y, v11.z, v11.w};
+#pragma unroll
+                                for (int c = 0; c < 4; ++c) {
+                                    s[k][c] = a00[c] * (wx0 * wy0) + a01[c] * (wx1 * wy0) + a10[c] * (wx0 * wy1) + a11[c] * (wx1 * wy1);
+                                    gx_c[k][c] = (a01[c] - a00[c]) * wy0 + (a11[c] - a10[c]) * wy1;
+                                    gy_c[k][c] = (a10[c] - a00[c]) * wx0 + (a11[c] - a01[c]) * wx1;
+                                }
+                            }
+                        }
+                        float df[4];
+#pragma unroll
+                        for (int c = 0; c < 4; ++c) df[c] = Hs[(l * C + c0 + c) * TPP + pt];
+#pragma unroll
+                        for (int k = 0; k < 6; ++k) {
+                            float ds[4];
+#pragma unroll
+                            for (int c = 0; c < 4; ++c) {
+                                float pr = df[c];
+#pragma unroll
+                                for (int j = 0; j < 6; ++j) if (j != k) pr *= s[j][c];
+                                ds[c] = pr;
+                            }
+                            // coordinate grads
+                            float gx = 0.f, gy = 0.f;
+#pragma unroll
+                            for (int c = 0; c < 4; ++c) { gx += ds[c] * gx_c[k][c]; gy += ds[c] * gy_c[k][c]; }
+                            dq[pa_of(k)] += gx * gmx[k];
+                            if (!(k == 2 || k == 4 || k == 5)) dq[pb_of(k)] += gy * gmy[k];
+                            // parameter grads (vector atomics, channel-last)
+                            const int W = lo.pw[l][k];
+                            if (k == 2 || k == 4 || k == 5) {
+                                float* T = gtrow + lo.toff[l][k == 2 ? 0 : (k == 4 ? 1 : 2)] + c0;
+                                atomicAdd(reinterpret_cast<float4*>(T + (size_t)x0a[k] * C),
+                                          make_float4(ds[0] * wx0a[k], ds[1] * wx0a[k], ds[2] * wx0a[k], ds[3] * wx0a[k]));
+                                if (xina[k])
+                                    atomicAdd(reinterpret_cast<float4*>(T + (size_t)(x0a[k] + 1) * C),
+                                              make_float4(ds[0] * wx1a[k], ds[1] * wx1a[k], ds[2] * wx1a[k], ds[3] * wx1a[k]));
+                            } else {
+                                float* Gp = gpacked + lo.poff[l][k] + c0;
+                                const size_t o00 = ((size_t)y0a[k] * W + x0a[k]) * C;
+                                const float nw = wx0a[k] * wy0a[k], ne = wx1a[k] * wy0a[k], sw = wx0a[k] * wy1a[k], se = wx1a[k] * wy1a[k];
+                                atomicAdd(reinterpret_cast<float4*>(Gp + o00), make_float4(ds[0] * nw, ds[1] * nw, ds[2] * nw, ds[3] * nw));
+                                if (xina[k])
+                                    atomicAdd(reinterpret_cast<float4*>(Gp + o00 + C), make_float4(ds[0] * ne, ds[1] * ne, ds[2] * ne, ds[3] * ne));
+                                if (yina[k])
+                                    atomicAdd(reinterpret_cast<float4*>(Gp + o00 + (size_t)W * C), make_float4(ds[0] * sw, ds[1] * sw, ds[2] * sw, ds[3] * sw));
+                                if (xina[k] && yina[k])
+                                    atomicAdd(reinterpret_cast<float4*>(Gp + o00 + (size_t)W * C + C), make_float4(ds[0] * se, ds[1] * se, ds[2] * se, ds[3] * se));
+                            }
+                        }
+                    }
+                }
+            }
+            // combine the two channel halves and write d_xyz (through the aabb normalisation)
+            __syncthreads();
+            float* red = Bs;       // [2][TP][3]
+            red[(half * TP + pt) * 3 + 0] = dq[0];
+            red[(half * TP + pt) * 3 + 1] = dq[1];
+            red[(half * TP + pt) * 3 + 2] = dq[2];
+            __syncthreads();
+            if (half == 0 && p < io.P) {
+#pragma unroll
+                for (int a = 0; a < 3; ++a) {
+                    const float mx = lo.aabb[a], mn = lo.aabb[3 + a];
+                    io.d_xyz[3 * (size_t)p + a] = (red[pt * 3 + a] + red[(TP + pt) * 3 + a]) * (2.0f / (mn - mx));
+                }
+            }
+        }
+    }
+}
+
+template <int WN> constexpr size_t fwd_smem() { return sizeof(float) * (size_t)(128 * TPP + 2 * WN * TPP + KC * BP); }
+template <int WN> constexpr size_t bwd_smem() { return sizeof(float) * (size_t)(128 * TPP + 2 * WN * TPP + 48 * TPP + KC * BP); }
+
+static void fill_net(const FdgsDeformNet& n, NetPtrs& p) {
+    for (int l = 0; l < FDGS_MAX_LEVELS; ++l) for (int k = 0; k < 6; ++k) p.planes[l][k] = n.planes[l][k];
+    for (int d = 0; d < 8; ++d) { p.trunk_w[d] = n.trunk_w[d]; p.trunk_b[d] = n.trunk_b[d]; }
+    for (int h = 0; h < FDGS_NUM_HEADS; ++h) { p.w1[h] = n.head_w1[h]; p.b1[h] = n.head_b1[h]; p.w2[h] = n.head_w2[h]; p.b2[h] = n.head_b2[h]; }
+}
+
+static int check_net_ptrs(const FdgsDeformNet& n, const Layout& lo, bool need_planes) {
+    if (need_planes)
+        for (int l = 0; l < lo.L; ++l) for (int k = 0; k < 6; ++k) if (!n.planes[l][k]) return FDGS_E_BADARG;
+    for (int d = 0; d < lo.depth; ++d) if (!n.trunk_w[d] || !n.trunk_b[d]) return FDGS_E_BADARG;
+    for (int h = 0; h < FDGS_NUM_HEADS; ++h)
+        if ((lo.head_mask >> h) & 1) if (!n.head_w1[h] || !n.head_b1[h] || !n.head_w2[h] || !n.head_b2[h]) return FDGS_E_BADARG;
+    return FDGS_OK;
+}
+
+static int sm_count() {
+    static int n = 0;
+    if (!n) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev); if (n <= 0) n = 148; }
+    return n;
+}
+
+}  // namespace
+
+extern "C" {
+
+size_t fdgs_deform_ws_bytes(const FdgsDeformNet* net) {
+    Layout lo;
+    if (!net || make_layout(*net, lo)) return 0;
+    return fdgs_align_up(sizeof(float) * (size_t)lo.plane_floats) + fdgs_align_up(sizeof(float) * (size_t)lo.trow_floats);
+}
+size_t fdgs_deform_backward_ws_bytes(const FdgsDeformNet* net) { return fdgs_deform_ws_bytes(net); }
+
+int fdgs_deform_forward(const FdgsDeformForward* a, void* stream_) {
+    if (!a) return FDGS_E_BADARG;
+    cudaStream_t stream = (cudaStream_t)stream_;
+    Layout lo;
+    int rc = make_layout(a->net, lo);
+    if (rc) return rc;
+    if (a->P < 0) return FDGS_E_BADARG;
+    if (a->P == 0) return FDGS_OK;
+    rc = check_net_ptrs(a->net, lo, !a->planes_packed_valid);
+    if (rc) return rc;
+    if (!a->xyz || !a->ws || a->ws_bytes < fdgs_deform_ws_bytes(&a->net)) return a->ws ? FDGS_E_WORKSPACE : FDGS_E_BADARG;
+    const int hm = lo.head_mask;
+    if (((hm >> 0) & 1) && !a->out_xyz) return FDGS_E_BADARG;
+    if (((hm >> 1) & 1) && (!a->out_scales || !a->scales)) return FDGS_E_BADARG;
+    if (((hm >> 2) & 1) && (!a->out_rotations || (!a->rotations && !lo.apply_rotation))) return FDGS_E_BADARG;
+    if (((hm >> 3) & 1) && (!a->out_opacity || !a->opacity)) return FDGS_E_BADARG;
+    if (((hm >> 4) & 1) && (!a->out_shs || !a->shs || (a->sh_coeffs != 16 && a->sh_coeffs != 1))) return FDGS_E_BADARG;
+
+    float* packed = (float*)a->ws;
+    float* trow = (float*)((char*)a->ws + fdgs_align_up(sizeof(float) * (size_t)lo.plane_floats));
+    if (!a->planes_packed_valid) {
+        for (int l = 0; l < lo.L; ++l)
+            for (int k = 0; k < 6; ++k) {
+                const int HW = lo.pw[l][k] * lo.ph[l][k];
+                const int n = HW * lo.C;
+                k_pack_plane<<<(n + 255) / 256, 256, 0, stream>>>(a->net.planes[l][k], packed + lo.poff[l][k], lo.C, HW);
+            }
+        FDGS_LAUNCH_CHECK(a->debug, stream);
+    }
+    k_time_rows<<<dim3(8, lo.L * 3), 256, 0, stream>>>(lo, packed, trow, a->time);
+    FDGS_LAUNCH_CHECK(a->debug, stream);
+
+    NetPtrs np; fill_net(a->net, np);
+    FwdIO io;
+    io.P = a->P; io.sh_coeffs = a->sh_coeffs; io.time = a->time;
+    io.xyz = a->xyz; io.scales = a->scales; io.rot = a->rotations; io.opacity = a->opacity; io.shs = a->shs;
+    io.o_xyz = a->out_xyz; io.o_scales = a->out_scales; io.o_rot = a->out_rotations; io.o_opacity = a->out_opacity; io.o_shs = a->out_shs;
+    const int ntiles = (a->P + TP - 1) / TP;
+    const int grid = ntiles < sm_count() ? ntiles : sm_count();
+    if (lo.Wn == 128) {
+        static bool set = false;
+        if (!set) { FDGS_CUDA(cudaFuncSetAttribute(k_deform_fwd<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fwd_smem<128>())); set = true; }
+        k_deform_fwd<128><<<grid, NT, fwd_smem<128>(), stream>>>(lo, np, io, packed, trow, ntiles);
+    } else {
+        static bool set = false;
+        if (!set) { FDGS_CUDA(cudaFuncSetAttribute(k_deform_fwd<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fwd_smem<64>())); set = true; }
+        k_deform_fwd<64><<<grid, NT, fwd_smem<64>(), stream>>>(lo, np, io, packed, trow, ntiles);
+    }
+    FDGS_LAUNCH_CHECK(a->debug, stream);
+    return FDGS_OK;
+}
+
+int fdgs_deform_backward(const FdgsDeformBackward* a, void* stream_) {
+    if (!a) return FDGS_E_BADARG;
+    cudaStream_t stream = (cudaStream_t)stream_;
+    Layout lo;
+    int rc = make_layout(a->net, lo);
+    if (rc) return rc;
+    if (lo.depth != 1) return FDGS_E_UNSUPPORTED;      // every shipped config has defor_depth in {0,1}
+    if (a->P < 0) return FDGS_E_BADARG;
+    if (a->P == 0) return FDGS_OK;
+    rc = check_net_ptrs(a->net, lo, false);
+    if (rc) return rc;
+    if (!a->xyz || !a->fwd_ws || !a->ws || !a->d_xyz_grid) return FDGS_E_BADARG;
+    if (a->ws_bytes < fdgs_deform_backward_ws_bytes(&a->net)) return FDGS_E_WORKSPACE;
+    const float* packed = (const float*)a->fwd_ws;
+    const float* trow = (const float*)((const char*)a->fwd_ws + fdgs_align_up(sizeof(float) * (size_t)lo.plane_floats));
+    float* gpacked = (float*)a->ws;
+    float* gtrow = (float*)((char*)a->ws + fdgs_align_up(sizeof(float) * (size_t)lo.plane_floats));
+    FDGS_CUDA(cudaMemsetAsync(a->ws, 0, fdgs_deform_backward_ws_bytes(&a->net), stream));
+
+    NetPtrs np; fill_net(a->net, np);
+    GradPtrs gp;
+    for (int l = 0; l < FDGS_MAX_LEVELS; ++l) for (int k = 0; k < 6; ++k) gp.planes[l][k] = a->d_planes[l][k];
+    for (int d = 0; d < 8; ++d) { gp.trunk_w[d] = a->d_trunk_w[d]; gp.trunk_b[d] = a->d_trunk_b[d]; }
+    for (int h = 0; h < FDGS_NUM_HEADS; ++h) { gp.w1[h] = a->d_head_w1[h]; gp.b1[h] = a->d_head_b1[h]; gp.w2[h] = a->d_head_w2[h]; gp.b2[h] = a->d_head_b2[h]; }
+    if (!gp.trunk_w[0] || !gp.trunk_b[0]) return FDGS_E_BADARG;
+    BwdIO io;
+    io.P = a->P; io.time = a->time; io.xyz = a->xyz; io.d_xyz = a->d_xyz_grid;
+    io.g[0] = a->g_xyz; io.g[1] = a->g_scales; io.g[2] = a->g_rotations; io.g[3] = a->g_opacity; io.g[4] = a->g_shs;
+    for (int h = 0; h < FDGS_NUM_HEADS; ++h)
+        if (((lo.head_mask >> h) & 1) && io.g[h] && (!gp.w1[h] || !gp.b1[h] || !gp.w2[h] || !gp.b2[h])) return FDGS_E_BADARG;
+    const int ntiles = (a->P + TP - 1) / TP;
+    const int grid = ntiles < sm_count() ? ntiles : sm_count();
+    if (lo.Wn == 128) {
+        static bool set = false;
+        if (!set) { FDGS_CUDA(cudaFuncSetAttribute(k_deform_bwd<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bwd_smem<128>())); set = true; }
+        k_deform_bwd<128><<<grid, NT, bwd_smem<128>(), stream>>>(lo, np, gp, io, packed, trow, gpacked, gtrow, ntiles);
+    } else {
+        static bool set = false;
+        if (!set) { FDGS_CUDA(cudaFuncSetAttribute(k_deform_bwd<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bwd_smem<64>())); set = true; }
+        k_deform_bwd<64><<<grid, NT, bwd_smem<64>(), stream>>>(lo, np, gp, io, packed, trow, gpacked, gtrow, ntiles);
+    }
+    FDGS_LAUNCH_CHECK(a->debug, stream);
+    // scatter the packed plane grads back into the reference layout (+=)
+    for (int l = 0; l < lo.L; ++l)
+        for (int k = 0; k < 6; ++k) {
+            if (!a->d_planes[l][k]) return FDGS_E_BADARG;
+            const int W = lo.pw[l][k], H = lo.ph[l][k];
+            if (h_tslot[k] >= 0) {
+                const int n = lo.C * W;
+                k_unpack_time<<<(n + 255) / 256, 256, 0, stream>>>(a->d_planes[l][k], gtrow + lo.toff[l][h_tslot[k]], lo.C, H, W, a->time);
+            } else {
+                const int n = lo.C * W * H;
+                k_unpack_spatial<<<(n + 255) / 256, 256, 0, stream>>>(a->d_planes[l][k], gpacked + lo.poff[l][k], lo.C, W * H);
+            }
+        }
+    FDGS_LAUNCH_CHECK(a->debug, stream);
+    return FDGS_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,243 @@
+/*
+ * fdgs.h — C ABI of the B200-native 4D-Gaussian training hot path.
+ *
+ * This is the drop-in boundary.  Every entry point replaces one function of the
+ * reference's torch/pybind glue (cited per function, paths relative to the
+ * reference checkout; RAST = submodules/depth-diff-gaussian-rasterization).
+ *
+ * Conventions
+ *   - extern "C", plain pointers and sizes only; no torch / C++ types.
+ *   - every `const float*` / `float*` is a DEVICE pointer to contiguous FP32
+ *     unless the field name ends in `_host`.
+ *   - `stream` is a cudaStream_t passed as void* (0 = legacy default stream).
+ *   - the library never allocates or frees device memory and never keeps a
+ *     pointer past the call: outputs and workspaces are caller-owned.
+ *   - return value: 0 = ok, <0 = FDGS_E_* argument/capacity error,
+ *     >0 = cudaError_t raised by a launch (see fdgs_error_string).
+ *   - `debug != 0` synchronises the stream after every launch and reports the
+ *     first failing stage (reference: CHECK_CUDA, RAST/cuda_rasterizer/auxiliary.h:166-173).
+ */
+#ifndef FDGS_H_INCLUDED
+#define FDGS_H_INCLUDED
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FDGS_ABI_VERSION 1
+
+enum {
+    FDGS_OK = 0,
+    FDGS_E_BADARG = -1,    /* null/inconsistent arguments (reference: AT_ERROR, RAST/rasterize_points.cu:57-59) */
+    FDGS_E_WORKSPACE = -2, /* a caller-owned workspace is smaller than fdgs_*_bytes() says */
+    FDGS_E_UNSUPPORTED = -3,
+    FDGS_E_SMEM = -4       /* configuration does not fit the 227 KB shared-memory budget */
+};
+
+/* ---- library info ------------------------------------------------------- */
+int fdgs_abi_version(void);
+const char* fdgs_error_string(int code);
+/* sm_XY the library was compiled for (100 for sm_100a). */
+int fdgs_compiled_arch(void);
+
+/* ---- rasterizer workspaces ----------------------------------------------
+ * Replaces the three resize-callback byte buffers of the reference
+ * (geomBuffer / binningBuffer / imgBuffer, RAST/rasterize_points.cu:27-33,74-79
+ * and RAST/cuda_rasterizer/rasterizer_impl.cu:155-194).  They are typed,
+ * caller-owned and must be 256-byte aligned.  geom/img/bin must be kept alive
+ * (and unmodified) until the matching backward call.                        */
+size_t fdgs_raster_geom_bytes(int P);
+size_t fdgs_raster_img_bytes(int W, int H);
+size_t fdgs_raster_bin_bytes(int64_t R);
+
+typedef struct FdgsRasterForward {
+    /* shapes / scalars (reference: RasterizeGaussiansCUDA args, RAST/rasterize_points.cu:35-56) */
+    int32_t P, D, M, W, H;
+    float tanfovx, tanfovy, scale_modifier;
+    int32_t prefiltered, debug;
+    /* inputs */
+    const float* background;     /* [3] */
+    const float* means3D;        /* [P,3] */
+    const float* shs;            /* [P,M,3] or NULL */
+    const float* colors_precomp; /* [P,3] or NULL */
+    const float* opacities;      /* [P] */
+    const float* scales;         /* [P,3] or NULL */
+    const float* rotations;      /* [P,4] or NULL */
+    const float* cov3D_precomp;  /* [P,6] or NULL */
+    const float* viewmatrix;     /* [16], transposed world->view (scene/cameras.py:61-65) */
+    const float* projmatrix;     /* [16] */
+    const float* campos;         /* [3] */
+    /* outputs */
+    float* out_color;            /* [3,H,W] */
+    float* out_depth;            /* [H,W] */
+    int32_t* radii;              /* [P] */
+    /* workspaces */
+    void* geom_ws;  size_t geom_bytes;
+    void* img_ws;   size_t img_bytes;
+    void* bin_ws;   size_t bin_bytes;   /* only read by fdgs_raster_forward_render */
+    /* pinned host scratch: [0]=num_rendered R, [1]=max instances in one tile */
+    int32_t* counts_host;
+    /* optional parity/debug outputs (NULL to skip): sorted 64-bit tile|depth keys [R]
+     * and sorted Gaussian ids [R], laid out exactly like the reference's
+     * point_list_keys / point_list (RAST/cuda_rasterizer/rasterizer_impl.cu:181-194) */
+    uint64_t* keys_out;
+    uint32_t* point_list_out;
+} FdgsRasterForward;
+
+/* Stage 1 of Rasterizer::forward (RAST/cuda_rasterizer/rasterizer_impl.cu:198-282):
+ * per-Gaussian preprocess (cull, EWA projection, conic, radius, tile rect, SH->RGB),
+ * per-tile instance histogram and tile ranges.  Synchronises `stream` once to
+ * return num_rendered (the reference does the same blocking read at :282).
+ * On return counts_host[0] = R.                                              */
+int fdgs_raster_forward_plan(const FdgsRasterForward* a, void* stream);
+
+/* Stage 2 (rasterizer_impl.cu:284-338): tile-bucketed key scatter, per-tile
+ * segmented sort (== stable sort of tile|depth keys), record packing, and the
+ * front-to-back blend.  `R` must be the value returned by the plan call and
+ * bin_ws must hold fdgs_raster_bin_bytes(R).                                  */
+int fdgs_raster_forward_render(const FdgsRasterForward* a, int64_t R, void* stream);
+
+/* Reads back the tile ranges (uint2 per tile, (0,0) for empty tiles exactly as
+ * rasterizer_impl.cu:311-319 leaves them) into a device buffer — parity/debug. */
+int fdgs_raster_copy_ranges(const void* img_ws, int W, int H, uint32_t* ranges_out, void* stream);
+
+typedef struct FdgsRasterBackward {
+    /* reference: RasterizeGaussiansBackwardCUDA args, RAST/rasterize_points.cu:119-142 */
+    int32_t P, D, M, W, H;
+    int64_t R;
+    float tanfovx, tanfovy, scale_modifier;
+    int32_t debug;
+    const float* background;
+    const float* means3D;
+    const float* shs;            /* or NULL */
+    const float* colors_precomp; /* or NULL */
+    const float* scales;         /* or NULL */
+    const float* rotations;      /* or NULL */
+    const float* cov3D_precomp;  /* or NULL */
+    const float* viewmatrix;
+    const float* projmatrix;
+    const float* campos;
+    const int32_t* radii;
+    const void* geom_ws;
+    const void* img_ws;
+    const void* bin_ws;
+    const float* dL_dpix;        /* [3,H,W] */
+    /* outputs — fully written by the call (no pre-zeroing needed) */
+    float* dL_dmeans2D;          /* [P,3]  (.z always 0, RAST/cuda_rasterizer/backward.cu:545-546) */
+    float* dL_dconic;            /* [P,4]  scratch (dA,dB,unused,dC) */
+    float* dL_dopacity;          /* [P] */
+    float* dL_dcolors;           /* [P,3]  (this IS grad_colors_precomp when colors_precomp != NULL) */
+    float* dL_dmeans3D;          /* [P,3] */
+    float* dL_dcov3D;            /* [P,6]  (this IS grad_cov3Ds_precomp when cov3D_precomp != NULL) */
+    float* dL_dsh;               /* [P,M,3] or NULL when M == 0 */
+    float* dL_dscales;           /* [P,3] */
+    float* dL_drots;             /* [P,4] */
+} FdgsRasterBackward;
+
+/* Rasterizer::backward (RAST/cuda_rasterizer/rasterizer_impl.cu:343-437):
+ * reverse-order blend backward with warp-reduced accumulation, then the fused
+ * cov2D / mean / SH / cov3D chain (backward.cu:144-396).                     */
+int fdgs_raster_backward(const FdgsRasterBackward* a, void* stream);
+
+/* Rasterizer::markVisible (rasterizer_impl.cu:141-153): present[i] = z_view > 0.2 */
+int fdgs_mark_visible(int P, const float* means3D, const float* viewmatrix,
+                      const float* projmatrix, uint8_t* present, void* stream);
+
+/* ---- HexPlane deformation field -----------------------------------------
+ * Replaces deform_network.forward -> Deformation.forward_dynamic
+ * (scene/deformation.py:185-212, 97-148) with HexPlaneField.forward
+ * (scene/hexplane.py:160-183) fused in.  All P points share one time value. */
+#define FDGS_MAX_LEVELS 4
+#define FDGS_HEAD_POS 0
+#define FDGS_HEAD_SCALE 1
+#define FDGS_HEAD_ROT 2
+#define FDGS_HEAD_OPACITY 3
+#define FDGS_HEAD_SHS 4
+#define FDGS_NUM_HEADS 5
+
+typedef struct FdgsDeformNet {
+    int32_t levels;                 /* L = len(multires)            (scene/hexplane.py:131-151) */
+    int32_t channels;               /* C = output_coordinate_dim                                  */
+    int32_t width;                  /* Wn = net_width                (scene/deformation.py:45-65) */
+    int32_t depth;                  /* D = defor_depth: number of trunk Linear layers = max(D,1)  */
+    int32_t head_mask;              /* bit h set = head h active (= !no_dx/!no_ds/!no_dr/!no_do/!no_dshs) */
+    int32_t apply_rotation;         /* scene/deformation.py:127-128 */
+    int32_t res[FDGS_MAX_LEVELS][4];/* per level [rx,ry,rz,rt]                                    */
+    float aabb[6];                  /* aabb[0..2] = "max", aabb[3..5] = "min" (scene/hexplane.py:118-119) */
+    /* plane k of level l: [C, H_k, W_k] row-major, pair order (0,1),(0,2),(0,3),(1,2),(1,3),(2,3);
+     * W_k = res[first], H_k = res[second]  (scene/hexplane.py:58-63) */
+    const float* planes[FDGS_MAX_LEVELS][6];
+    /* trunk: feature_out.0 (weight [Wn, C*L], bias [Wn]) then (depth-1) x (ReLU, Linear Wn->Wn) */
+    const float* trunk_w[8];
+    const float* trunk_b[8];
+    /* heads: *_deform.1 (weight [Wn,Wn], bias [Wn]) and *_deform.3 (weight [out,Wn], bias [out]) */
+    const float* head_w1[FDGS_NUM_HEADS];
+    const float* head_b1[FDGS_NUM_HEADS];
+    const float* head_w2[FDGS_NUM_HEADS];
+    const float* head_b2[FDGS_NUM_HEADS];
+} FdgsDeformNet;
+
+typedef struct FdgsDeformForward {
+    FdgsDeformNet net;
+    int32_t P;
+    int32_t sh_coeffs;              /* second dim of shs (16, or 1 with broadcast)   */
+    float time;                     /* the view's timestamp (times_sel[:,0] is constant per view)   */
+    int32_t precision;              /* 0 = FP32 (SIMT / 3xTF32-split), 1 = single-pass TF32          */
+    int32_t planes_packed_valid;    /* 1 = ws already holds the packed planes of these parameters   */
+    const float* xyz;               /* [P,3] */
+    const float* scales;            /* [P,3] */
+    const float* rotations;         /* [P,4] */
+    const float* opacity;           /* [P,1] */
+    const float* shs;               /* [P,sh_coeffs,3] */
+    /* outputs; a NULL pointer means "head inactive: caller returns its input unchanged".
+     * out = input + delta, except out_rotations = delta alone when net.apply_rotation
+     * (the caller then applies the quaternion product, scene/deformation.py:127-128). */
+    float* out_xyz;
+    float* out_scales;
+    float* out_rotations;
+    float* out_opacity;
+    float* out_shs;                 /* [P,16,3] */
+    void* ws; size_t ws_bytes;      /* fdgs_deform_ws_bytes(): packed channel-last planes + per-view time rows */
+    int32_t debug;
+} FdgsDeformForward;
+
+size_t fdgs_deform_ws_bytes(const FdgsDeformNet* net);
+int fdgs_deform_forward(const FdgsDeformForward* a, void* stream);
+
+typedef struct FdgsDeformBackward {
+    FdgsDeformNet net;
+    int32_t P;
+    float time;
+    int32_t precision;
+    const float* xyz;
+    /* upstream grads w.r.t. the five outputs (NULL = head inactive / no grad) */
+    const float* g_xyz;             /* [P,3] */
+    const float* g_scales;          /* [P,3] */
+    const float* g_rotations;       /* [P,4] */
+    const float* g_opacity;         /* [P,1] */
+    const float* g_shs;             /* [P,16,3] */
+    /* outputs: grad wrt xyz THROUGH THE GRID only (identity paths are added by the caller),
+     * and parameter grads ACCUMULATED (+=) into caller-owned buffers laid out like the params */
+    float* d_xyz_grid;              /* [P,3] */
+    float* d_planes[FDGS_MAX_LEVELS][6];
+    float* d_trunk_w[8];
+    float* d_trunk_b[8];
+    float* d_head_w1[FDGS_NUM_HEADS];
+    float* d_head_b1[FDGS_NUM_HEADS];
+    float* d_head_w2[FDGS_NUM_HEADS];
+    float* d_head_b2[FDGS_NUM_HEADS];
+    const void* fwd_ws;             /* the forward call's ws (packed planes + time rows of this view) */
+    void* ws; size_t ws_bytes;      /* fdgs_deform_backward_ws_bytes(): packed plane-grad scratch */
+    int32_t debug;
+} FdgsDeformBackward;
+
+size_t fdgs_deform_backward_ws_bytes(const FdgsDeformNet* net);
+int fdgs_deform_backward(const FdgsDeformBackward* a, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FDGS_H_INCLUDED */
