@@ -1,0 +1,154 @@
+"""ctypes binding of libfdgs.so (C ABI declared in include/fdgs.h).
+
+There is no CPU fallback: if the CUDA library is missing this module raises at
+import of the first symbol.
+"""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libfdgs.so")
+
+FDGS_MAX_LEVELS = 4
+FDGS_NUM_HEADS = 5
+HEAD_OUT = (3, 3, 4, 1, 48)
+
+c_float_p = C.c_void_p  # raw device pointers are passed as integers
+
+
+class FdgsRasterForward(C.Structure):
+    _fields_ = [
+        ("P", C.c_int32), ("D", C.c_int32), ("M", C.c_int32), ("W", C.c_int32), ("H", C.c_int32),
+        ("tanfovx", C.c_float), ("tanfovy", C.c_float), ("scale_modifier", C.c_float),
+        ("prefiltered", C.c_int32), ("debug", C.c_int32),
+        ("background", C.c_void_p), ("means3D", C.c_void_p), ("shs", C.c_void_p),
+        ("colors_precomp", C.c_void_p), ("opacities", C.c_void_p), ("scales", C.c_void_p),
+        ("rotations", C.c_void_p), ("cov3D_precomp", C.c_void_p), ("viewmatrix", C.c_void_p),
+        ("projmatrix", C.c_void_p), ("campos", C.c_void_p),
+        ("out_color", C.c_void_p), ("out_depth", C.c_void_p), ("radii", C.c_void_p),
+        ("geom_ws", C.c_void_p), ("geom_bytes", C.c_size_t),
+        ("img_ws", C.c_void_p), ("img_bytes", C.c_size_t),
+        ("bin_ws", C.c_void_p), ("bin_bytes", C.c_size_t),
+        ("counts_host", C.c_void_p),
+        ("keys_out", C.c_void_p), ("point_list_out", C.c_void_p),
+    ]
+
+
+class FdgsRasterBackward(C.Structure):
+    _fields_ = [
+        ("P", C.c_int32), ("D", C.c_int32), ("M", C.c_int32), ("W", C.c_int32), ("H", C.c_int32),
+        ("R", C.c_int64),
+        ("tanfovx", C.c_float), ("tanfovy", C.c_float), ("scale_modifier", C.c_float),
+        ("debug", C.c_int32),
+        ("background", C.c_void_p), ("means3D", C.c_void_p), ("shs", C.c_void_p),
+        ("colors_precomp", C.c_void_p), ("scales", C.c_void_p), ("rotations", C.c_void_p),
+        ("cov3D_precomp", C.c_void_p), ("viewmatrix", C.c_void_p), ("projmatrix", C.c_void_p),
+        ("campos", C.c_void_p), ("radii", C.c_void_p),
+        ("geom_ws", C.c_void_p), ("img_ws", C.c_void_p), ("bin_ws", C.c_void_p),
+        ("dL_dpix", C.c_void_p),
+        ("dL_dmeans2D", C.c_void_p), ("dL_dconic", C.c_void_p), ("dL_dopacity", C.c_void_p),
+        ("dL_dcolors", C.c_void_p), ("dL_dmeans3D", C.c_void_p), ("dL_dcov3D", C.c_void_p),
+        ("dL_dsh", C.c_void_p), ("dL_dscales", C.c_void_p), ("dL_drots", C.c_void_p),
+    ]
+
+
+class FdgsDeformNet(C.Structure):
+    _fields_ = [
+        ("levels", C.c_int32), ("channels", C.c_int32), ("width", C.c_int32), ("depth", C.c_int32),
+        ("head_mask", C.c_int32), ("apply_rotation", C.c_int32),
+        ("res", (C.c_int32 * 4) * FDGS_MAX_LEVELS),
+        ("aabb", C.c_float * 6),
+        ("planes", (C.c_void_p * 6) * FDGS_MAX_LEVELS),
+        ("trunk_w", C.c_void_p * 8), ("trunk_b", C.c_void_p * 8),
+        ("head_w1", C.c_void_p * FDGS_NUM_HEADS), ("head_b1", C.c_void_p * FDGS_NUM_HEADS),
+        ("head_w2", C.c_void_p * FDGS_NUM_HEADS), ("head_b2", C.c_void_p * FDGS_NUM_HEADS),
+    ]
+
+
+class FdgsDeformForward(C.Structure):
+    _fields_ = [
+        ("net", FdgsDeformNet),
+        ("P", C.c_int32), ("sh_coeffs", C.c_int32), ("time", C.c_float), ("time_dev", C.c_void_p),
+        ("precision", C.c_int32), ("planes_packed_valid", C.c_int32),
+        ("xyz", C.c_void_p), ("scales", C.c_void_p), ("rotations", C.c_void_p),
+        ("opacity", C.c_void_p), ("shs", C.c_void_p),
+        ("out_xyz", C.c_void_p), ("out_scales", C.c_void_p), ("out_rotations", C.c_void_p),
+        ("out_opacity", C.c_void_p), ("out_shs", C.c_void_p),
+        ("packed_ws", C.c_void_p), ("packed_bytes", C.c_size_t),
+        ("trow_ws", C.c_void_p), ("trow_bytes", C.c_size_t),
+        ("debug", C.c_int32),
+    ]
+
+
+class FdgsDeformBackward(C.Structure):
+    _fields_ = [
+        ("net", FdgsDeformNet),
+        ("P", C.c_int32), ("time", C.c_float), ("time_dev", C.c_void_p), ("precision", C.c_int32),
+        ("xyz", C.c_void_p),
+        ("g_xyz", C.c_void_p), ("g_scales", C.c_void_p), ("g_rotations", C.c_void_p),
+        ("g_opacity", C.c_void_p), ("g_shs", C.c_void_p),
+        ("d_xyz_grid", C.c_void_p),
+        ("d_planes", (C.c_void_p * 6) * FDGS_MAX_LEVELS),
+        ("d_trunk_w", C.c_void_p * 8), ("d_trunk_b", C.c_void_p * 8),
+        ("d_head_w1", C.c_void_p * FDGS_NUM_HEADS), ("d_head_b1", C.c_void_p * FDGS_NUM_HEADS),
+        ("d_head_w2", C.c_void_p * FDGS_NUM_HEADS), ("d_head_b2", C.c_void_p * FDGS_NUM_HEADS),
+        ("packed_ws", C.c_void_p), ("trow_ws", C.c_void_p),
+        ("ws", C.c_void_p), ("ws_bytes", C.c_size_t),
+        ("debug", C.c_int32),
+    ]
+
+
+# every symbol include/fdgs.h declares: name -> (restype, argtypes)
+SYMBOLS = {
+    "fdgs_abi_version": (C.c_int, []),
+    "fdgs_error_string": (C.c_char_p, [C.c_int]),
+    "fdgs_compiled_arch": (C.c_int, []),
+    "fdgs_raster_geom_bytes": (C.c_size_t, [C.c_int]),
+    "fdgs_raster_img_bytes": (C.c_size_t, [C.c_int, C.c_int]),
+    "fdgs_raster_bin_bytes": (C.c_size_t, [C.c_int64]),
+    "fdgs_raster_forward_plan": (C.c_int, [C.POINTER(FdgsRasterForward), C.c_void_p]),
+    "fdgs_raster_forward_render": (C.c_int, [C.POINTER(FdgsRasterForward), C.c_int64, C.c_void_p]),
+    "fdgs_raster_copy_ranges": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
+    "fdgs_raster_backward": (C.c_int, [C.POINTER(FdgsRasterBackward), C.c_void_p]),
+    "fdgs_mark_visible": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "fdgs_deform_packed_bytes": (C.c_size_t, [C.POINTER(FdgsDeformNet)]),
+    "fdgs_deform_trow_bytes": (C.c_size_t, [C.POINTER(FdgsDeformNet)]),
+    "fdgs_deform_forward": (C.c_int, [C.POINTER(FdgsDeformForward), C.c_void_p]),
+    "fdgs_deform_backward_ws_bytes": (C.c_size_t, [C.POINTER(FdgsDeformNet)]),
+    "fdgs_deform_backward": (C.c_int, [C.POINTER(FdgsDeformBackward), C.c_void_p]),
+}
+
+_lib = None
+
+
+def load():
+    """Loads libfdgs.so; raises (never falls back) when it is missing."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            f"{LIB_PATH} not found: the fdgs CUDA library is not built. Run "
+            f"`python {os.path.join(_HERE, 'build.py')}` (needs nvcc); there is no CPU fallback.")
+    lib = C.CDLL(LIB_PATH)
+    for name, (res, args) in SYMBOLS.items():
+        fn = getattr(lib, name)  # AttributeError if the symbol is missing
+        fn.restype = res
+        fn.argtypes = args
+    if lib.fdgs_abi_version() != 1:
+        raise ImportError("libfdgs.so ABI version mismatch")
+    _lib = lib
+    return lib
+
+
+def check(code, what):
+    if code != 0:
+        msg = load().fdgs_error_string(code).decode()
+        raise RuntimeError(f"{what} failed: {msg} (code {code})")
+
+
+def ptr(t):
+    """Device pointer of a torch tensor, or None for an absent/empty tensor."""
+    if t is None or t.numel() == 0:
+        return None
+    return t.data_ptr()

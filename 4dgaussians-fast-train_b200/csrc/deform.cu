@@ -42,7 +42,7 @@ struct Layout {
 static int make_layout(const FdgsDeformNet& n, Layout& lo) {
     if (n.levels < 1 || n.levels > FDGS_MAX_LEVELS) return FDGS_E_BADARG;
     if (!(n.channels == 4 || (n.channels % 8 == 0 && n.channels >= 8 && n.channels <= 64))) return FDGS_E_UNSUPPORTED;
-    if (n.width != 64 && n.width != 128) return FDGS_E_UNSUPPORTED;
+    if (n.width != 32 && n.width != 64 && n.width != 128) return FDGS_E_UNSUPPORTED;
     lo.L = n.levels; lo.C = n.channels; lo.F = n.levels * n.channels; lo.Wn = n.width;
     lo.depth = n.depth < 1 ? 1 : n.depth;
     if (lo.depth > 8) return FDGS_E_UNSUPPORTED;
@@ -96,7 +96,9 @@ __global__ void k_pack_plane(const float* __restrict__ src /*[C][H][W]*/, float*
 }
 
 // time rows: trow[x][c] = wy0 * P[y0][x][c] + wy1 * P[y0+1][x][c]   (packed planes in, per view)
-__global__ void k_time_rows(Layout lo, const float* __restrict__ packed, float* __restrict__ trow, float time) {
+__global__ void k_time_rows(Layout lo, const float* __restrict__ packed, float* __restrict__ trow, float time_h,
+                            const float* __restrict__ time_dev) {
+    const float time = time_dev ? *time_dev : time_h;
     const int l = blockIdx.y / 3, slot = blockIdx.y % 3;
     if (l >= lo.L) return;
     const int k = slot == 0 ? 2 : slot == 1 ? 4 : 5;
@@ -125,9 +127,10 @@ __global__ void k_unpack_spatial(float* __restrict__ dst /*[C][H][W]*/, const fl
 }
 // time planes: only rows y0 and y0+1 receive gradient
 __global__ void k_unpack_time(float* __restrict__ dst /*[C][H][W]*/, const float* __restrict__ gt /*[W][C]*/,
-                              int C, int H, int W, float time) {
+                              int C, int H, int W, float time_h, const float* __restrict__ time_dev) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;      // over C*W
     if (i >= C * W) return;
+    const float time = time_dev ? *time_dev : time_h;
     const int c = i / W, x = i % W;
     const float iy = unnorm_clip(time, H);
     const float y0f = floorf(iy);
@@ -345,7 +348,7 @@ struct FwdIO {
 
 template <int WN>
 __device__ __forceinline__ void trunk_forward(const Layout& lo, const NetPtrs& net, const float* Fs, float* Hs, float* Zs, float* Bs) {
-    constexpr int G = WN / 64;
+    constexpr int G = (WN + 63) / 64;
     const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
     const float* X = Fs;
     int K = lo.F;
@@ -365,9 +368,11 @@ __device__ __forceinline__ void trunk_forward(const Layout& lo, const NetPtrs& n
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
                 const int o = g * 64 + tx * 4 + j;
-                const float bv = net.trunk_b[d][o];
+                if (o < WN) {
+                    const float bv = net.trunk_b[d][o];
 #pragma unroll
-                for (int i = 0; i < 8; ++i) Y[o * TPP + ty * 8 + i] = fmaxf(acc[i][g * 4 + j] + bv, 0.f);
+                    for (int i = 0; i < 8; ++i) Y[o * TPP + ty * 8 + i] = fmaxf(acc[i][g * 4 + j] + bv, 0.f);
+                }
             }
         __syncthreads();
         X = Y; K = WN;
@@ -378,7 +383,7 @@ template <int WN>
 __global__ void __launch_bounds__(NT, 1)
 k_deform_fwd(Layout lo, NetPtrs net, FwdIO io, const float* __restrict__ packed, const float* __restrict__ trow, int ntiles) {
     extern __shared__ __align__(16) float smem[];
-    constexpr int G = WN / 64;
+    constexpr int G = (WN + 63) / 64;
     float* Fs = smem;                         // [F][TPP]   (F <= 128)
     float* Hs = Fs + 128 * TPP;               // [WN][TPP]
     float* Zs = Hs + WN * TPP;                // [WN][TPP]
@@ -407,9 +412,11 @@ k_deform_fwd(Layout lo, NetPtrs net, FwdIO io, const float* __restrict__ packed,
 #pragma unroll
                     for (int j = 0; j < 4; ++j) {
                         const int o = g * 64 + tx * 4 + j;
-                        const float bv = net.b1[h][o];
+                        if (o < WN) {
+                            const float bv = net.b1[h][o];
 #pragma unroll
-                        for (int i = 0; i < 8; ++i) Zs[o * TPP + ty * 8 + i] = fmaxf(acc[i][g * 4 + j] + bv, 0.f);
+                            for (int i = 0; i < 8; ++i) Zs[o * TPP + ty * 8 + i] = fmaxf(acc[i][g * 4 + j] + bv, 0.f);
+                        }
                     }
                 __syncthreads();
             }
@@ -458,10 +465,11 @@ __global__ void __launch_bounds__(NT, 1)
 k_deform_bwd(Layout lo, NetPtrs net, GradPtrs gp, BwdIO io, const float* __restrict__ packed, const float* __restrict__ trow,
              float* __restrict__ gpacked, float* __restrict__ gtrow, int ntiles) {
     extern __shared__ __align__(16) float smem[];
-    constexpr int G = WN / 64;
+    constexpr int G = (WN + 63) / 64;
     float* Fs = smem;                         // [F][TPP]
+    constexpr int HROWS = WN < 128 ? 128 : WN;   // Hs is reused for g_feat [F <= 128][TPP]
     float* Hs = Fs + 128 * TPP;               // [WN][TPP]  relu(h); later g_feat
-    float* Zs = Hs + WN * TPP;                // [WN][TPP]  relu(z) -> g_z ; later g_h
+    float* Zs = Hs + HROWS * TPP;             // [WN][TPP]  relu(z) -> g_z ; later g_h
     float* Gos = Zs + WN * TPP;               // [48][TPP]  upstream grads of the current head
     float* Bs = Gos + 48 * TPP;               // [KC][BP]
     const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
@@ -496,9 +504,11 @@ k_deform_bwd(Layout lo, NetPtrs net, GradPtrs gp, BwdIO io, const float* __restr
 #pragma unroll
                     for (int j = 0; j < 4; ++j) {
                         const int o = g * 64 + tx * 4 + j;
-                        const float bv = net.b1[h][o];
+                        if (o < WN) {
+                            const float bv = net.b1[h][o];
 #pragma unroll
-                        for (int i = 0; i < 8; ++i) Zs[o * TPP + ty * 8 + i] = fmaxf(acc[i][g * 4 + j] + bv, 0.f);
+                            for (int i = 0; i < 8; ++i) Zs[o * TPP + ty * 8 + i] = fmaxf(acc[i][g * 4 + j] + bv, 0.f);
+                        }
                     }
             }
             // stage upstream grads, k-major
@@ -523,10 +533,12 @@ k_deform_bwd(Layout lo, NetPtrs net, GradPtrs gp, BwdIO io, const float* __restr
 #pragma unroll
                     for (int j = 0; j < 4; ++j) {
                         const int o = g * 64 + tx * 4 + j;
+                        if (o < WN) {
 #pragma unroll
-                        for (int i = 0; i < 8; ++i) {
-                            const int a = o * TPP + ty * 8 + i;
-                            Zs[a] = (Zs[a] > 0.f) ? acc[i][g * 4 + j] : 0.f;   // g_z
+                            for (int i = 0; i < 8; ++i) {
+                                const int a = o * TPP + ty * 8 + i;
+                                Zs[a] = (Zs[a] > 0.f) ? acc[i][g * 4 + j] : 0.f;   // g_z
+                            }
                         }
                     }
                 __syncthreads();
@@ -541,10 +553,12 @@ k_deform_bwd(Layout lo, NetPtrs net, GradPtrs gp, BwdIO io, const float* __restr
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
                 const int o = g * 64 + tx * 4 + j;
+                if (o < WN) {
 #pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                    const int a = o * TPP + ty * 8 + i;
-                    Zs[a] = (Hs[a] > 0.f) ? acc_h[i][g * 4 + j] : 0.f;
+                    for (int i = 0; i < 8; ++i) {
+                        const int a = o * TPP + ty * 8 + i;
+                        Zs[a] = (Hs[a] > 0.f) ? acc_h[i][g * 4 + j] : 0.f;
+                    }
                 }
             }
         __syncthreads();
@@ -701,7 +715,7 @@ k_deform_bwd(Layout lo, NetPtrs net, GradPtrs gp, BwdIO io, const float* __restr
 }
 
 template <int WN> constexpr size_t fwd_smem() { return sizeof(float) * (size_t)(128 * TPP + 2 * WN * TPP + KC * BP); }
-template <int WN> constexpr size_t bwd_smem() { return sizeof(float) * (size_t)(128 * TPP + 2 * WN * TPP + 48 * TPP + KC * BP); }
+template <int WN> constexpr size_t bwd_smem() { return sizeof(float) * (size_t)(128 * TPP + (WN < 128 ? 128 : WN) * TPP + WN * TPP + 48 * TPP + KC * BP); }
 
 static void fill_net(const FdgsDeformNet& n, NetPtrs& p) {
     for (int l = 0; l < FDGS_MAX_LEVELS; ++l) for (int k = 0; k < 6; ++k) p.planes[l][k] = n.planes[l][k];
@@ -728,12 +742,19 @@ static int sm_count() {
 
 extern "C" {
 
-size_t fdgs_deform_ws_bytes(const FdgsDeformNet* net) {
+size_t fdgs_deform_packed_bytes(const FdgsDeformNet* net) {
     Layout lo;
     if (!net || make_layout(*net, lo)) return 0;
-    return fdgs_align_up(sizeof(float) * (size_t)lo.plane_floats) + fdgs_align_up(sizeof(float) * (size_t)lo.trow_floats);
+    return fdgs_align_up(sizeof(float) * (size_t)lo.plane_floats);
 }
-size_t fdgs_deform_backward_ws_bytes(const FdgsDeformNet* net) { return fdgs_deform_ws_bytes(net); }
+size_t fdgs_deform_trow_bytes(const FdgsDeformNet* net) {
+    Layout lo;
+    if (!net || make_layout(*net, lo)) return 0;
+    return fdgs_align_up(sizeof(float) * (size_t)lo.trow_floats);
+}
+size_t fdgs_deform_backward_ws_bytes(const FdgsDeformNet* net) {
+    return fdgs_deform_packed_bytes(net) + fdgs_deform_trow_bytes(net);
+}
 
 int fdgs_deform_forward(const FdgsDeformForward* a, void* stream_) {
     if (!a) return FDGS_E_BADARG;
@@ -745,7 +766,8 @@ int fdgs_deform_forward(const FdgsDeformForward* a, void* stream_) {
     if (a->P == 0) return FDGS_OK;
     rc = check_net_ptrs(a->net, lo, !a->planes_packed_valid);
     if (rc) return rc;
-    if (!a->xyz || !a->ws || a->ws_bytes < fdgs_deform_ws_bytes(&a->net)) return a->ws ? FDGS_E_WORKSPACE : FDGS_E_BADARG;
+    if (!a->xyz || !a->packed_ws || !a->trow_ws) return FDGS_E_BADARG;
+    if (a->packed_bytes < fdgs_deform_packed_bytes(&a->net) || a->trow_bytes < fdgs_deform_trow_bytes(&a->net)) return FDGS_E_WORKSPACE;
     const int hm = lo.head_mask;
     if (((hm >> 0) & 1) && !a->out_xyz) return FDGS_E_BADARG;
     if (((hm >> 1) & 1) && (!a->out_scales || !a->scales)) return FDGS_E_BADARG;
@@ -753,8 +775,8 @@ int fdgs_deform_forward(const FdgsDeformForward* a, void* stream_) {
     if (((hm >> 3) & 1) && (!a->out_opacity || !a->opacity)) return FDGS_E_BADARG;
     if (((hm >> 4) & 1) && (!a->out_shs || !a->shs || (a->sh_coeffs != 16 && a->sh_coeffs != 1))) return FDGS_E_BADARG;
 
-    float* packed = (float*)a->ws;
-    float* trow = (float*)((char*)a->ws + fdgs_align_up(sizeof(float) * (size_t)lo.plane_floats));
+    float* packed = (float*)a->packed_ws;
+    float* trow = (float*)a->trow_ws;
     if (!a->planes_packed_valid) {
         for (int l = 0; l < lo.L; ++l)
             for (int k = 0; k < 6; ++k) {
@@ -764,7 +786,7 @@ int fdgs_deform_forward(const FdgsDeformForward* a, void* stream_) {
             }
         FDGS_LAUNCH_CHECK(a->debug, stream);
     }
-    k_time_rows<<<dim3(8, lo.L * 3), 256, 0, stream>>>(lo, packed, trow, a->time);
+    k_time_rows<<<dim3(8, lo.L * 3), 256, 0, stream>>>(lo, packed, trow, a->time, a->time_dev);
     FDGS_LAUNCH_CHECK(a->debug, stream);
 
     NetPtrs np; fill_net(a->net, np);
@@ -778,10 +800,14 @@ int fdgs_deform_forward(const FdgsDeformForward* a, void* stream_) {
         static bool set = false;
         if (!set) { FDGS_CUDA(cudaFuncSetAttribute(k_deform_fwd<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fwd_smem<128>())); set = true; }
         k_deform_fwd<128><<<grid, NT, fwd_smem<128>(), stream>>>(lo, np, io, packed, trow, ntiles);
-    } else {
+    } else if (lo.Wn == 64) {
         static bool set = false;
         if (!set) { FDGS_CUDA(cudaFuncSetAttribute(k_deform_fwd<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fwd_smem<64>())); set = true; }
         k_deform_fwd<64><<<grid, NT, fwd_smem<64>(), stream>>>(lo, np, io, packed, trow, ntiles);
+    } else {
+        static bool set = false;
+        if (!set) { FDGS_CUDA(cudaFuncSetAttribute(k_deform_fwd<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fwd_smem<32>())); set = true; }
+        k_deform_fwd<32><<<grid, NT, fwd_smem<32>(), stream>>>(lo, np, io, packed, trow, ntiles);
     }
     FDGS_LAUNCH_CHECK(a->debug, stream);
     return FDGS_OK;
@@ -798,10 +824,10 @@ int fdgs_deform_backward(const FdgsDeformBackward* a, void* stream_) {
     if (a->P == 0) return FDGS_OK;
     rc = check_net_ptrs(a->net, lo, false);
     if (rc) return rc;
-    if (!a->xyz || !a->fwd_ws || !a->ws || !a->d_xyz_grid) return FDGS_E_BADARG;
+    if (!a->xyz || !a->packed_ws || !a->trow_ws || !a->ws || !a->d_xyz_grid) return FDGS_E_BADARG;
     if (a->ws_bytes < fdgs_deform_backward_ws_bytes(&a->net)) return FDGS_E_WORKSPACE;
-    const float* packed = (const float*)a->fwd_ws;
-    const float* trow = (const float*)((const char*)a->fwd_ws + fdgs_align_up(sizeof(float) * (size_t)lo.plane_floats));
+    const float* packed = (const float*)a->packed_ws;
+    const float* trow = (const float*)a->trow_ws;
     float* gpacked = (float*)a->ws;
     float* gtrow = (float*)((char*)a->ws + fdgs_align_up(sizeof(float) * (size_t)lo.plane_floats));
     FDGS_CUDA(cudaMemsetAsync(a->ws, 0, fdgs_deform_backward_ws_bytes(&a->net), stream));
@@ -823,10 +849,14 @@ int fdgs_deform_backward(const FdgsDeformBackward* a, void* stream_) {
         static bool set = false;
         if (!set) { FDGS_CUDA(cudaFuncSetAttribute(k_deform_bwd<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bwd_smem<128>())); set = true; }
         k_deform_bwd<128><<<grid, NT, bwd_smem<128>(), stream>>>(lo, np, gp, io, packed, trow, gpacked, gtrow, ntiles);
-    } else {
+    } else if (lo.Wn == 64) {
         static bool set = false;
         if (!set) { FDGS_CUDA(cudaFuncSetAttribute(k_deform_bwd<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bwd_smem<64>())); set = true; }
         k_deform_bwd<64><<<grid, NT, bwd_smem<64>(), stream>>>(lo, np, gp, io, packed, trow, gpacked, gtrow, ntiles);
+    } else {
+        static bool set = false;
+        if (!set) { FDGS_CUDA(cudaFuncSetAttribute(k_deform_bwd<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bwd_smem<32>())); set = true; }
+        k_deform_bwd<32><<<grid, NT, bwd_smem<32>(), stream>>>(lo, np, gp, io, packed, trow, gpacked, gtrow, ntiles);
     }
     FDGS_LAUNCH_CHECK(a->debug, stream);
     // scatter the packed plane grads back into the reference layout (+=)
@@ -836,7 +866,7 @@ int fdgs_deform_backward(const FdgsDeformBackward* a, void* stream_) {
             const int W = lo.pw[l][k], H = lo.ph[l][k];
             if (h_tslot[k] >= 0) {
                 const int n = lo.C * W;
-                k_unpack_time<<<(n + 255) / 256, 256, 0, stream>>>(a->d_planes[l][k], gtrow + lo.toff[l][h_tslot[k]], lo.C, H, W, a->time);
+                k_unpack_time<<<(n + 255) / 256, 256, 0, stream>>>(a->d_planes[l][k], gtrow + lo.toff[l][h_tslot[k]], lo.C, H, W, a->time, a->time_dev);
             } else {
                 const int n = lo.C * W * H;
                 k_unpack_spatial<<<(n + 255) / 256, 256, 0, stream>>>(a->d_planes[l][k], gpacked + lo.poff[l][k], lo.C, W * H);

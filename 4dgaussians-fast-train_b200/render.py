@@ -1,0 +1,67 @@
+"""Caller-side glue: mirror of gaussian_renderer.render() (gaussian_renderer/__init__.py:18-138),
+the function that feeds the deformation field's outputs into the rasterizer.  Same return dict.
+
+Differences, none observable in the results:
+  * the per-call `.cuda()` copies of the camera matrices (:45-48) are skipped when the tensors are
+    already on the device;
+  * `time` is passed as one device scalar instead of a [P,1] repeat (:52) — the fused deformation
+    kernel takes one timestamp per view.
+"""
+import math
+
+import torch
+
+from .diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer
+
+
+def render(viewpoint_camera, pc, pipe=None, bg_color=None, scaling_modifier=1.0, override_color=None,
+           stage="fine", cam_type=None):
+    xyz = pc.get_xyz
+    dev = xyz.device
+    screenspace_points = torch.zeros_like(xyz, dtype=xyz.dtype, requires_grad=True, device=dev) + 0
+    try:
+        screenspace_points.retain_grad()
+    except Exception:
+        pass
+    means3D = xyz
+    debug = bool(getattr(pipe, "debug", False)) if pipe is not None else False
+    if cam_type != "PanopticSports":
+        tanfovx = math.tan(viewpoint_camera.FoVx * 0.5)
+        tanfovy = math.tan(viewpoint_camera.FoVy * 0.5)
+        raster_settings = GaussianRasterizationSettings(
+            image_height=int(viewpoint_camera.image_height), image_width=int(viewpoint_camera.image_width),
+            tanfovx=tanfovx, tanfovy=tanfovy, bg=bg_color, scale_modifier=scaling_modifier,
+            viewmatrix=viewpoint_camera.world_view_transform.to(dev),
+            projmatrix=viewpoint_camera.full_proj_transform.to(dev),
+            sh_degree=pc.active_sh_degree, campos=viewpoint_camera.camera_center.to(dev),
+            prefiltered=False, debug=debug)
+        time = viewpoint_camera.time
+    else:
+        raster_settings = viewpoint_camera['camera']
+        time = viewpoint_camera['time']
+    rasterizer = GaussianRasterizer(raster_settings=raster_settings)
+
+    means2D = screenspace_points
+    opacity = pc._opacity
+    shs = pc.get_features
+    scales = pc._scaling
+    rotations = pc._rotation
+    if "coarse" in stage:
+        means3D_final, scales_final, rotations_final, opacity_final, shs_final = means3D, scales, rotations, opacity, shs
+    elif "fine" in stage:
+        means3D_final, scales_final, rotations_final, opacity_final, shs_final = pc._deformation(
+            means3D, scales, rotations, opacity, shs, time)
+    else:
+        raise NotImplementedError
+
+    scales_final = pc.scaling_activation(scales_final)
+    rotations_final = pc.rotation_activation(rotations_final)
+    opacity = pc.opacity_activation(opacity_final)
+
+    colors_precomp = override_color
+    rendered_image, radii, depth = rasterizer(
+        means3D=means3D_final, means2D=means2D, shs=shs_final if colors_precomp is None else None,
+        colors_precomp=colors_precomp, opacities=opacity, scales=scales_final, rotations=rotations_final,
+        cov3D_precomp=None)
+    return {"render": rendered_image, "viewspace_points": screenspace_points, "visibility_filter": radii > 0,
+            "radii": radii, "depth": depth}

@@ -185,8 +185,9 @@ typedef struct FdgsDeformForward {
     int32_t P;
     int32_t sh_coeffs;              /* second dim of shs (16, or 1 with broadcast)   */
     float time;                     /* the view's timestamp (times_sel[:,0] is constant per view)   */
+    const float* time_dev;          /* optional DEVICE scalar overriding `time` (avoids a host sync) */
     int32_t precision;              /* 0 = FP32 (SIMT / 3xTF32-split), 1 = single-pass TF32          */
-    int32_t planes_packed_valid;    /* 1 = ws already holds the packed planes of these parameters   */
+    int32_t planes_packed_valid;    /* 1 = packed_ws already holds the packed planes of these parameters */
     const float* xyz;               /* [P,3] */
     const float* scales;            /* [P,3] */
     const float* rotations;         /* [P,4] */
@@ -200,17 +201,22 @@ typedef struct FdgsDeformForward {
     float* out_rotations;
     float* out_opacity;
     float* out_shs;                 /* [P,16,3] */
-    void* ws; size_t ws_bytes;      /* fdgs_deform_ws_bytes(): packed channel-last planes + per-view time rows */
+    void* packed_ws; size_t packed_bytes; /* fdgs_deform_packed_bytes(): channel-last planes; reusable across
+                                             views until the plane parameters change                     */
+    void* trow_ws;   size_t trow_bytes;   /* fdgs_deform_trow_bytes(): this view's pre-blended time rows;
+                                             must stay alive until the matching backward              */
     int32_t debug;
 } FdgsDeformForward;
 
-size_t fdgs_deform_ws_bytes(const FdgsDeformNet* net);
+size_t fdgs_deform_packed_bytes(const FdgsDeformNet* net);
+size_t fdgs_deform_trow_bytes(const FdgsDeformNet* net);
 int fdgs_deform_forward(const FdgsDeformForward* a, void* stream);
 
 typedef struct FdgsDeformBackward {
     FdgsDeformNet net;
     int32_t P;
     float time;
+    const float* time_dev;          /* optional DEVICE scalar overriding `time` */
     int32_t precision;
     const float* xyz;
     /* upstream grads w.r.t. the five outputs (NULL = head inactive / no grad) */
@@ -229,7 +235,8 @@ typedef struct FdgsDeformBackward {
     float* d_head_b1[FDGS_NUM_HEADS];
     float* d_head_w2[FDGS_NUM_HEADS];
     float* d_head_b2[FDGS_NUM_HEADS];
-    const void* fwd_ws;             /* the forward call's ws (packed planes + time rows of this view) */
+    const void* packed_ws;          /* the forward call's packed planes */
+    const void* trow_ws;            /* the forward call's time rows of this view */
     void* ws; size_t ws_bytes;      /* fdgs_deform_backward_ws_bytes(): packed plane-grad scratch */
     int32_t debug;
 } FdgsDeformBackward;

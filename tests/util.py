@@ -1,0 +1,148 @@
+"""Shared helpers for the test-suite: seeded scenes, decoders for the reference's byte buffers, and
+thin callers of the three rasterizer implementations (ours / reference CUDA build / CPU oracle)."""
+import math
+
+import numpy as np
+import torch
+
+import fdgs  # noqa: F401  (repo-root shim)
+from fdgs import synth
+from fdgs.diff_gaussian_rasterization import GaussianRasterizationSettings, rasterize_debug
+
+
+def scene(P=2000, W=200, H=120, fovx=0.6911, extent=1.3, logscale=-3.0, seed=3, angle=0.3, sh_degree=3, bg=1.0,
+          device="cpu", dist=4.0):
+    """Activated rasterizer inputs of one synthetic view, as FP32 torch tensors."""
+    g = synth.make_gaussians(P, extent=extent, logscale=logscale, sh_degree=3, seed=seed)
+    cam = synth.make_camera(W, H, fovx, angle=angle, dist=dist)
+    d = dict(W=W, H=H, tanfovx=math.tan(cam.FoVx * 0.5), tanfovy=math.tan(cam.FoVy * 0.5),
+             bg=torch.full((3,), float(bg)), means3D=g["xyz"], opacities=torch.sigmoid(g["opacity"]),
+             scales=torch.exp(g["scaling"]), rotations=torch.nn.functional.normalize(g["rotation"]),
+             shs=torch.cat([g["f_dc"], g["f_rest"]], dim=1), viewmatrix=cam.world_view_transform,
+             projmatrix=cam.full_proj_transform, campos=cam.camera_center, sh_degree=sh_degree)
+    return {k: (v.to(device) if isinstance(v, torch.Tensor) else v) for k, v in d.items()}
+
+
+def settings(sc, debug=False, scale_modifier=1.0):
+    return GaussianRasterizationSettings(image_height=sc["H"], image_width=sc["W"], tanfovx=sc["tanfovx"],
+                                         tanfovy=sc["tanfovy"], bg=sc["bg"], scale_modifier=scale_modifier,
+                                         viewmatrix=sc["viewmatrix"], projmatrix=sc["projmatrix"],
+                                         sh_degree=sc["sh_degree"], campos=sc["campos"], prefiltered=False, debug=debug)
+
+
+def ours_forward(sc, **kw):
+    return rasterize_debug(settings(sc, **kw), sc["means3D"], sc["opacities"], shs=sc.get("shs"),
+                           colors_precomp=sc.get("colors_precomp"), scales=sc.get("scales"),
+                           rotations=sc.get("rotations"), cov3D_precomp=sc.get("cov3D_precomp"))
+
+
+def _al(x, a=128):
+    return (x + a - 1) & ~(a - 1)
+
+
+def ref_forward(refC, sc, scale_modifier=1.0):
+    """Runs the UNMODIFIED reference CUDA build (oracle/_ref) and decodes its opaque byte buffers
+    (layouts: RAST/cuda_rasterizer/rasterizer_impl.cu:155-194)."""
+    e = torch.empty(0, device=sc["means3D"].device)
+    g = lambda k: sc[k] if sc.get(k) is not None else e
+    P, W, H = sc["means3D"].shape[0], sc["W"], sc["H"]
+    args = (sc["bg"], sc["means3D"], g("colors_precomp"), sc["opacities"], g("scales"), g("rotations"), scale_modifier,
+            g("cov3D_precomp"), sc["viewmatrix"], sc["projmatrix"], sc["tanfovx"], sc["tanfovy"], H, W, g("shs"),
+            sc["sh_degree"], sc["campos"], False, False)
+    R, color, depth, radii, geomB, binB, imgB = refC.rasterize_gaussians(*args)
+    out = dict(num_rendered=R, color=color, depth=depth, radii=radii, _buffers=(geomB, binB, imgB), _args=args)
+    # geometry buffer
+    base = geomB.data_ptr()
+    off = _al(base) - base
+    def take(nbytes, dtype, shape):
+        nonlocal off
+        off = _al(base + off) - base
+        v = geomB[off:off + nbytes].view(dtype).view(shape)
+        off += nbytes
+        return v
+    out["depths"] = take(4 * P, torch.float32, (P,))
+    out["clamped"] = take(3 * P, torch.uint8, (P, 3))
+    take(4 * P, torch.int32, (P,))
+    out["means2D"] = take(8 * P, torch.float32, (P, 2))
+    out["cov3D"] = take(24 * P, torch.float32, (P, 6))
+    out["conic_opacity"] = take(16 * P, torch.float32, (P, 4))
+    out["rgb"] = take(12 * P, torch.float32, (P, 3))
+    out["tiles_touched"] = take(4 * P, torch.int32, (P,))
+    # image buffer: accum_alpha[N], n_contrib[N], ranges[N] (uint2), N = W*H
+    N = W * H
+    base = imgB.data_ptr(); off = 0
+    def take_i(nbytes, dtype, shape):
+        nonlocal off
+        off = _al(base + off) - base
+        v = imgB[off:off + nbytes].view(dtype).view(shape)
+        off += nbytes
+        return v
+    out["final_T"] = take_i(4 * N, torch.float32, (H, W))
+    out["n_contrib"] = take_i(4 * N, torch.int32, (H, W))
+    T = ((W + 15) // 16) * ((H + 15) // 16)
+    out["ranges"] = take_i(8 * N, torch.int32, (N, 2))[:T]
+    # binning buffer: point_list[R], point_list_unsorted[R], keys[R], keys_unsorted[R]
+    base = binB.data_ptr(); off = 0
+    def take_b(nbytes, dtype, shape):
+        nonlocal off
+        off = _al(base + off) - base
+        v = binB[off:off + nbytes].view(dtype).view(shape)
+        off += nbytes
+        return v
+    if R > 0:
+        out["point_list"] = take_b(4 * R, torch.int32, (R,))
+        take_b(4 * R, torch.int32, (R,))
+        out["keys"] = take_b(8 * R, torch.int64, (R,))
+    else:
+        out["point_list"] = torch.empty(0, dtype=torch.int32, device=color.device)
+        out["keys"] = torch.empty(0, dtype=torch.int64, device=color.device)
+    return out
+
+
+def ref_backward(refC, sc, fwd, grad_color, scale_modifier=1.0):
+    e = torch.empty(0, device=sc["means3D"].device)
+    g = lambda k: sc[k] if sc.get(k) is not None else e
+    geomB, binB, imgB = fwd["_buffers"]
+    res = refC.rasterize_gaussians_backward(sc["bg"], sc["means3D"], fwd["radii"], g("colors_precomp"), g("scales"),
+                                            g("rotations"), scale_modifier, g("cov3D_precomp"), sc["viewmatrix"],
+                                            sc["projmatrix"], sc["tanfovx"], sc["tanfovy"], grad_color, g("shs"),
+                                            sc["sh_degree"], sc["campos"], geomB, fwd["num_rendered"], binB, imgB, False)
+    names = ("means2D", "colors_precomp", "opacities", "means3D", "cov3D", "sh", "scales", "rotations")
+    return dict(zip(names, res))
+
+
+def ours_autograd(sc, grad_color, scale_modifier=1.0):
+    """Forward + backward through the public GaussianRasterizer API; returns (color, radii, depth, grads)."""
+    from fdgs.diff_gaussian_rasterization import GaussianRasterizer
+    leaves = {}
+    for k in ("means3D", "opacities", "scales", "rotations", "shs", "colors_precomp", "cov3D_precomp"):
+        if sc.get(k) is not None:
+            leaves[k] = sc[k].detach().clone().requires_grad_(True)
+    means2D = torch.zeros_like(leaves["means3D"], requires_grad=True)
+    rast = GaussianRasterizer(settings(sc, scale_modifier=scale_modifier))
+    op = leaves["opacities"]
+    color, radii, depth = rast(means3D=leaves["means3D"], means2D=means2D, opacities=op if op.dim() == 2 else op[:, None],
+                               shs=leaves.get("shs"), colors_precomp=leaves.get("colors_precomp"),
+                               scales=leaves.get("scales"), rotations=leaves.get("rotations"),
+                               cov3D_precomp=leaves.get("cov3D_precomp"))
+    color.backward(grad_color)
+    grads = {k: v.grad for k, v in leaves.items()}
+    grads["means2D"] = means2D.grad
+    return color.detach(), radii, depth.detach(), grads
+
+
+def oracle_forward(sc, dL_dpix=None, f64=False, scale_modifier=1.0):
+    import raster_oracle as RO
+    n = lambda k: None if sc.get(k) is None else sc[k].detach().cpu().numpy()
+    return RO.rasterize(W=sc["W"], H=sc["H"], tanfovx=sc["tanfovx"], tanfovy=sc["tanfovy"], bg=n("bg"),
+                        means3D=n("means3D"), opacities=n("opacities"), viewmatrix=n("viewmatrix"),
+                        projmatrix=n("projmatrix"), campos=n("campos"), shs=n("shs"), colors_precomp=n("colors_precomp"),
+                        scales=n("scales"), rotations=n("rotations"), cov3D_precomp=n("cov3D_precomp"),
+                        sh_degree=sc["sh_degree"], scale_modifier=scale_modifier,
+                        dL_dpix=None if dL_dpix is None else dL_dpix.detach().cpu().numpy(), f64=f64)
+
+
+def rel_err(a, b):
+    a = torch.as_tensor(a, dtype=torch.float64).cpu()
+    b = torch.as_tensor(b, dtype=torch.float64).cpu()
+    return float((a - b).abs().max() / (b.abs().max() + 1e-30))
