@@ -103,6 +103,9 @@ SYMBOLS = {
     "fdgs_abi_version": (C.c_int, []),
     "fdgs_error_string": (C.c_char_p, [C.c_int]),
     "fdgs_compiled_arch": (C.c_int, []),
+    "fdgs_profile_enable": (None, [C.c_int]),
+    "fdgs_profile_collect": (C.c_int, [C.c_char_p, C.c_size_t]),
+    "fdgs_launch_count": (C.c_ulonglong, []),
     "fdgs_raster_geom_bytes": (C.c_size_t, [C.c_int]),
     "fdgs_raster_img_bytes": (C.c_size_t, [C.c_int, C.c_int]),
     "fdgs_raster_bin_bytes": (C.c_size_t, [C.c_int64]),
@@ -152,3 +155,22 @@ def ptr(t):
     if t is None or t.numel() == 0:
         return None
     return t.data_ptr()
+
+
+def profile_enable(on=True):
+    load().fdgs_profile_enable(int(bool(on)))
+
+
+def profile_collect():
+    """{kernel_name: (launches, total_ms)} since the last collect (synchronises the device)."""
+    buf = C.create_string_buffer(1 << 16)
+    load().fdgs_profile_collect(buf, len(buf))
+    out = {}
+    for line in buf.value.decode().splitlines():
+        name, n, ms = line.split()
+        out[name] = (int(n), float(ms))
+    return out
+
+
+def launch_count():
+    return int(load().fdgs_launch_count())

@@ -16,6 +16,8 @@
 // the tile structure (128 points x Wn) is the one the tcgen05 path uses.
 #include "fdgs_common.cuh"
 
+#include "prof.cuh"
+
 namespace {
 
 constexpr int TP = 128;      // points per tile
@@ -782,11 +784,15 @@ int fdgs_deform_forward(const FdgsDeformForward* a, void* stream_) {
             for (int k = 0; k < 6; ++k) {
                 const int HW = lo.pw[l][k] * lo.ph[l][k];
                 const int n = HW * lo.C;
+                { FDGS_PROF("k_pack_plane", stream);
                 k_pack_plane<<<(n + 255) / 256, 256, 0, stream>>>(a->net.planes[l][k], packed + lo.poff[l][k], lo.C, HW);
+                }
             }
         FDGS_LAUNCH_CHECK(a->debug, stream);
     }
+    { FDGS_PROF("k_time_rows", stream);
     k_time_rows<<<dim3(8, lo.L * 3), 256, 0, stream>>>(lo, packed, trow, a->time, a->time_dev);
+    }
     FDGS_LAUNCH_CHECK(a->debug, stream);
 
     NetPtrs np; fill_net(a->net, np);
@@ -799,15 +805,21 @@ int fdgs_deform_forward(const FdgsDeformForward* a, void* stream_) {
     if (lo.Wn == 128) {
         static bool set = false;
         if (!set) { FDGS_CUDA(cudaFuncSetAttribute(k_deform_fwd<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fwd_smem<128>())); set = true; }
+        { FDGS_PROF("k_deform_fwd", stream);
         k_deform_fwd<128><<<grid, NT, fwd_smem<128>(), stream>>>(lo, np, io, packed, trow, ntiles);
+        }
     } else if (lo.Wn == 64) {
         static bool set = false;
         if (!set) { FDGS_CUDA(cudaFuncSetAttribute(k_deform_fwd<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fwd_smem<64>())); set = true; }
+        { FDGS_PROF("k_deform_fwd", stream);
         k_deform_fwd<64><<<grid, NT, fwd_smem<64>(), stream>>>(lo, np, io, packed, trow, ntiles);
+        }
     } else {
         static bool set = false;
         if (!set) { FDGS_CUDA(cudaFuncSetAttribute(k_deform_fwd<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fwd_smem<32>())); set = true; }
+        { FDGS_PROF("k_deform_fwd", stream);
         k_deform_fwd<32><<<grid, NT, fwd_smem<32>(), stream>>>(lo, np, io, packed, trow, ntiles);
+        }
     }
     FDGS_LAUNCH_CHECK(a->debug, stream);
     return FDGS_OK;
@@ -848,15 +860,21 @@ int fdgs_deform_backward(const FdgsDeformBackward* a, void* stream_) {
     if (lo.Wn == 128) {
         static bool set = false;
         if (!set) { FDGS_CUDA(cudaFuncSetAttribute(k_deform_bwd<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bwd_smem<128>())); set = true; }
+        { FDGS_PROF("k_deform_bwd", stream);
         k_deform_bwd<128><<<grid, NT, bwd_smem<128>(), stream>>>(lo, np, gp, io, packed, trow, gpacked, gtrow, ntiles);
+        }
     } else if (lo.Wn == 64) {
         static bool set = false;
         if (!set) { FDGS_CUDA(cudaFuncSetAttribute(k_deform_bwd<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bwd_smem<64>())); set = true; }
+        { FDGS_PROF("k_deform_bwd", stream);
         k_deform_bwd<64><<<grid, NT, bwd_smem<64>(), stream>>>(lo, np, gp, io, packed, trow, gpacked, gtrow, ntiles);
+        }
     } else {
         static bool set = false;
         if (!set) { FDGS_CUDA(cudaFuncSetAttribute(k_deform_bwd<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bwd_smem<32>())); set = true; }
+        { FDGS_PROF("k_deform_bwd", stream);
         k_deform_bwd<32><<<grid, NT, bwd_smem<32>(), stream>>>(lo, np, gp, io, packed, trow, gpacked, gtrow, ntiles);
+        }
     }
     FDGS_LAUNCH_CHECK(a->debug, stream);
     // scatter the packed plane grads back into the reference layout (+=)
@@ -866,10 +884,14 @@ int fdgs_deform_backward(const FdgsDeformBackward* a, void* stream_) {
             const int W = lo.pw[l][k], H = lo.ph[l][k];
             if (h_tslot[k] >= 0) {
                 const int n = lo.C * W;
+                { FDGS_PROF("k_unpack_time", stream);
                 k_unpack_time<<<(n + 255) / 256, 256, 0, stream>>>(a->d_planes[l][k], gtrow + lo.toff[l][h_tslot[k]], lo.C, H, W, a->time, a->time_dev);
+                }
             } else {
                 const int n = lo.C * W * H;
+                { FDGS_PROF("k_unpack_spatial", stream);
                 k_unpack_spatial<<<(n + 255) / 256, 256, 0, stream>>>(a->d_planes[l][k], gpacked + lo.poff[l][k], lo.C, W * H);
+                }
             }
         }
     FDGS_LAUNCH_CHECK(a->debug, stream);

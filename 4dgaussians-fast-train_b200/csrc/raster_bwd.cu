@@ -7,6 +7,8 @@
 // (RAST/cuda_rasterizer/rasterizer_impl.cu:343-437, backward.cu:20-557).
 #include "raster_math.cuh"
 
+#include "prof.cuh"
+
 namespace {
 
 constexpr unsigned FULL = 0xffffffffu;
@@ -513,15 +515,19 @@ extern "C" int fdgs_raster_backward(const FdgsRasterBackward* a, void* stream_) 
     FDGS_CUDA(cudaMemsetAsync(a->dL_dcolors, 0, sizeof(float) * 3 * (size_t)P, stream));
     if (a->R > 0) {
         dim3 grid(gx, gy);
+        { FDGS_PROF("k_blend_bwd", stream);
         k_blend_bwd<<<grid, 256, 0, stream>>>(im.ranges, bn.records, a->W, a->H, a->background, im.final_T, im.n_contrib,
                                               a->dL_dpix, a->dL_dmeans2D, a->dL_dconic, a->dL_dopacity, a->dL_dcolors);
+        }
         FDGS_LAUNCH_CHECK(a->debug, stream);
     }
     const float* cov3D_ptr = a->cov3D_precomp ? a->cov3D_precomp : g.cov3D;
+    { FDGS_PROF("k_preprocess_bwd", stream);
     k_preprocess_bwd<<<(P + 255) / 256, 256, 0, stream>>>(
         P, a->D, a->M, a->means3D, a->radii, a->shs, g.clamped, a->scales, a->rotations, a->scale_modifier, cov3D_ptr,
         a->viewmatrix, a->projmatrix, focal_x, focal_y, a->tanfovx, a->tanfovy, a->campos, a->dL_dmeans2D, a->dL_dconic,
         a->dL_dcolors, a->dL_dmeans3D, a->dL_dcov3D, a->dL_dsh, a->dL_dscales, a->dL_drots, 0);
+    }
     FDGS_LAUNCH_CHECK(a->debug, stream);
     return FDGS_OK;
 }

@@ -6,6 +6,7 @@
 // (RAST/cuda_rasterizer/rasterizer_impl.cu:198-339, forward.cu:155-379).
 #include "raster_math.cuh"
 #include <cstdio>
+#include "prof.cuh"
 
 namespace {
 
@@ -519,12 +520,16 @@ int fdgs_raster_forward_plan(const FdgsRasterForward* a, void* stream_) {
     const float focal_x = a->W / (2.0f * a->tanfovx);
     // tile_count, tile_cursor, tile_start, scalars are contiguous: one memset
     FDGS_CUDA(cudaMemsetAsync(im.tile_count, 0, (size_t)((char*)im.scalars - (char*)im.tile_count) + 32, stream));
+    { FDGS_PROF("k_preprocess", stream);
     k_preprocess<<<(a->P + 255) / 256, 256, 0, stream>>>(
         a->P, a->D, a->M, a->means3D, a->scales, a->scale_modifier, a->rotations, a->opacities, a->shs,
         a->cov3D_precomp, a->colors_precomp, a->viewmatrix, a->projmatrix, a->campos, a->W, a->H,
         a->tanfovx, a->tanfovy, focal_x, focal_y, gx, gy, a->prefiltered, a->radii, g, im.tile_count);
+    }
     FDGS_LAUNCH_CHECK(a->debug, stream);
+    { FDGS_PROF("k_tile_scan", stream);
     k_tile_scan<<<1, 1024, 0, stream>>>(T, im.tile_count, im.tile_start, im.ranges, im.scalars, nullptr);
+    }
     FDGS_LAUNCH_CHECK(a->debug, stream);
     FDGS_CUDA(cudaMemcpyAsync(a->counts_host, im.scalars, 2 * sizeof(int32_t), cudaMemcpyDeviceToHost, stream));
     FDGS_CUDA(cudaStreamSynchronize(stream));
@@ -549,26 +554,36 @@ int fdgs_raster_forward_render(const FdgsRasterForward* a, int64_t R, void* stre
     FdgsImg im = FdgsImg::carve(a->img_ws, a->W, a->H);
     FdgsBin bn = FdgsBin::carve(a->bin_ws, R);
     if (R > 0) {
+        { FDGS_PROF("k_scatter", stream);
         k_scatter<<<(a->P + 255) / 256, 256, 0, stream>>>(a->P, a->radii, g, gx, gy, im.tile_start, im.tile_cursor, bn.bucket);
+        }
         FDGS_LAUNCH_CHECK(a->debug, stream);
         const float* colors = a->colors_precomp ? a->colors_precomp : g.rgb;
         const int maxc = a->counts_host[1];
         if (maxc <= 2048) {
+            { FDGS_PROF("k_tile_sort", stream);
             k_tile_sort<2048><<<T, 256, 2048 * 8, stream>>>(im.ranges, bn.bucket, g, colors, bn.records, a->keys_out, a->point_list_out);
+            }
         } else if (maxc <= 8192) {
             static bool attr_set8 = false;
             if (!attr_set8) { FDGS_CUDA(cudaFuncSetAttribute(k_tile_sort<8192>, cudaFuncAttributeMaxDynamicSharedMemorySize, 8192 * 8)); attr_set8 = true; }
+            { FDGS_PROF("k_tile_sort", stream);
             k_tile_sort<8192><<<T, 256, 8192 * 8, stream>>>(im.ranges, bn.bucket, g, colors, bn.records, a->keys_out, a->point_list_out);
+            }
         } else {
             static bool attr_set28 = false;
             if (!attr_set28) { FDGS_CUDA(cudaFuncSetAttribute(k_tile_sort<28672>, cudaFuncAttributeMaxDynamicSharedMemorySize, 28672 * 8)); attr_set28 = true; }
+            { FDGS_PROF("k_tile_sort", stream);
             k_tile_sort<28672><<<T, 256, 28672 * 8, stream>>>(im.ranges, bn.bucket, g, colors, bn.records, a->keys_out, a->point_list_out);
+            }
         }
         FDGS_LAUNCH_CHECK(a->debug, stream);
     }
     dim3 grid(gx, gy);
+    { FDGS_PROF("k_blend_fwd", stream);
     k_blend_fwd<<<grid, 256, 0, stream>>>(im.ranges, bn.records, a->W, a->H, a->background, im.final_T, im.n_contrib,
                                           a->out_color, a->out_depth);
+    }
     FDGS_LAUNCH_CHECK(a->debug, stream);
     return FDGS_OK;
 }
@@ -586,7 +601,10 @@ int fdgs_mark_visible(int P, const float* means3D, const float* viewmatrix, cons
     (void)projmatrix;
     if (P < 0 || (P > 0 && (!means3D || !viewmatrix || !present))) return FDGS_E_BADARG;
     if (P == 0) return FDGS_OK;
+    cudaStream_t stream = (cudaStream_t)stream_;
+    { FDGS_PROF("k_mark_visible", stream);
     k_mark_visible<<<(P + 255) / 256, 256, 0, (cudaStream_t)stream_>>>(P, means3D, viewmatrix, present);
+    }
     FDGS_LAUNCH_CHECK(0, (cudaStream_t)stream_);
     return FDGS_OK;
 }

@@ -43,6 +43,14 @@ const char* fdgs_error_string(int code);
 /* sm_XY the library was compiled for (100 for sm_100a). */
 int fdgs_compiled_arch(void);
 
+/* Optional per-kernel CUDA-event timing (bench/roofline evidence).  enable(1) makes every kernel
+ * launch of the library record a start/stop event pair on its stream; collect() synchronises the
+ * device and writes one "kernel_name launches total_ms" line per kernel into buf, then clears.
+ * fdgs_launch_count() = number of library kernels launched so far in this process.            */
+void fdgs_profile_enable(int on);
+int fdgs_profile_collect(char* buf, size_t n);
+unsigned long long fdgs_launch_count(void);
+
 /* ---- rasterizer workspaces ----------------------------------------------
  * Replaces the three resize-callback byte buffers of the reference
  * (geomBuffer / binningBuffer / imgBuffer, RAST/rasterize_points.cu:27-33,74-79

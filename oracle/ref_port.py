@@ -1,0 +1,239 @@
+"""TEST INFRASTRUCTURE / REFERENCE ARM — the reference's Python hot path restated op-for-op.
+
+/root/reference does not exist on the GPU box and its Python cannot travel, so the reference arm of
+bench.py (`--impl reference`) and the GPU cross-checks use this port.  It issues the SAME ATen ops in the
+same order as the reference (F.grid_sample per plane, products, cat, nn.Linear stacks, the dead poc_fre
+embeddings, the [P,1] time repeat, exp/normalize/sigmoid) and calls the UNMODIFIED reference CUDA
+rasterizer compiled from its own sources (oracle/_ref, see oracle/build_ref.py).  None of the fdgs
+kernels is on this path.  `-m "not gpu"` tests check the deformation port bit-for-bit against the real
+reference module in the authoring container.
+
+  scene/hexplane.py:19-106,109-183        -> normalize_aabb, grid_sample_wrapper, interpolate_ms_features, RefHexPlaneField
+  scene/deformation.py:16-231             -> RefDeformation, ref_deform_network, poc_fre
+  RAST/diff_gaussian_rasterization/__init__.py:44-220 -> _RefRasterize, RefGaussianRasterizer
+  gaussian_renderer/__init__.py:18-138    -> ref_render
+"""
+import itertools
+import math
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+import torch.nn.init as init
+
+
+def normalize_aabb(pts, aabb):
+    return (pts - aabb[0]) * (2.0 / (aabb[1] - aabb[0])) - 1.0
+
+
+def grid_sample_wrapper(grid, coords, align_corners=True):
+    grid_dim = coords.shape[-1]
+    if grid.dim() == grid_dim + 1:
+        grid = grid.unsqueeze(0)
+    if coords.dim() == 2:
+        coords = coords.unsqueeze(0)
+    coords = coords.view([coords.shape[0]] + [1] * (grid_dim - 1) + list(coords.shape[1:]))
+    B, feature_dim = grid.shape[:2]
+    n = coords.shape[-2]
+    interp = F.grid_sample(grid, coords, align_corners=align_corners, mode='bilinear', padding_mode='border')
+    interp = interp.view(B, feature_dim, n).transpose(-1, -2)
+    return interp.squeeze()
+
+
+def init_grid_param(grid_nd, in_dim, out_dim, reso, a=0.1, b=0.5):
+    coo_combs = list(itertools.combinations(range(in_dim), grid_nd))
+    grid_coefs = nn.ParameterList()
+    for coo_comb in coo_combs:
+        p = nn.Parameter(torch.empty([1, out_dim] + [reso[cc] for cc in coo_comb[::-1]]))
+        if in_dim == 4 and 3 in coo_comb:
+            nn.init.ones_(p)
+        else:
+            nn.init.uniform_(p, a=a, b=b)
+        grid_coefs.append(p)
+    return grid_coefs
+
+
+def interpolate_ms_features(pts, ms_grids, grid_dimensions):
+    coo_combs = list(itertools.combinations(range(pts.shape[-1]), grid_dimensions))
+    multi_scale_interp = []
+    for grid in ms_grids:
+        interp_space = 1.
+        for ci, coo_comb in enumerate(coo_combs):
+            feature_dim = grid[ci].shape[1]
+            interp_out_plane = grid_sample_wrapper(grid[ci], pts[..., coo_comb]).view(-1, feature_dim)
+            interp_space = interp_space * interp_out_plane
+        multi_scale_interp.append(interp_space)
+    return torch.cat(multi_scale_interp, dim=-1)
+
+
+class RefHexPlaneField(nn.Module):
+    def __init__(self, bounds, planeconfig, multires):
+        super().__init__()
+        aabb = torch.tensor([[bounds, bounds, bounds], [-bounds, -bounds, -bounds]], dtype=torch.float32)
+        self.aabb = nn.Parameter(aabb, requires_grad=False)
+        self.grid_config = [planeconfig]
+        self.grids = nn.ModuleList()
+        self.feat_dim = 0
+        for res in multires:
+            config = self.grid_config[0].copy()
+            config["resolution"] = [r * res for r in config["resolution"][:3]] + config["resolution"][3:]
+            gp = init_grid_param(config["grid_dimensions"], config["input_coordinate_dim"],
+                                 config["output_coordinate_dim"], config["resolution"])
+            self.feat_dim += gp[-1].shape[1]
+            self.grids.append(gp)
+
+    def set_aabb(self, xyz_max, xyz_min):
+        self.aabb = nn.Parameter(torch.tensor([xyz_max, xyz_min], dtype=torch.float32).to(self.aabb.device),
+                                 requires_grad=False)
+
+    def forward(self, pts, timestamps):
+        pts = normalize_aabb(pts, self.aabb)
+        pts = torch.cat((pts, timestamps), dim=-1)
+        pts = pts.reshape(-1, pts.shape[-1])
+        return interpolate_ms_features(pts, self.grids, self.grid_config[0]["grid_dimensions"])
+
+
+class RefDeformation(nn.Module):
+    def __init__(self, D, W, args):
+        super().__init__()
+        self.D, self.W, self.args = D, W, args
+        self.grid = RefHexPlaneField(args.bounds, args.kplanes_config, args.multires)
+        layers = [nn.Linear(self.grid.feat_dim, W)]
+        for _ in range(D - 1):
+            layers += [nn.ReLU(), nn.Linear(W, W)]
+        self.feature_out = nn.Sequential(*layers)
+        mk = lambda o: nn.Sequential(nn.ReLU(), nn.Linear(W, W), nn.ReLU(), nn.Linear(W, o))
+        self.pos_deform, self.scales_deform, self.rotations_deform = mk(3), mk(3), mk(4)
+        self.opacity_deform, self.shs_deform = mk(1), mk(48)
+
+    def set_aabb(self, xyz_max, xyz_min):
+        self.grid.set_aabb(xyz_max, xyz_min)
+
+    def forward(self, rays_pts_emb, scales_emb, rotations_emb, opacity_emb, shs_emb, time_feature, time_emb):
+        a = self.args
+        hidden = self.feature_out(self.grid(rays_pts_emb[:, :3], time_emb[:, :1]))
+        mask = torch.ones_like(opacity_emb[:, 0]).unsqueeze(-1)
+        pts = rays_pts_emb[:, :3] if a.no_dx else rays_pts_emb[:, :3] * mask + self.pos_deform(hidden)
+        scales = scales_emb[:, :3] if a.no_ds else scales_emb[:, :3] * mask + self.scales_deform(hidden)
+        if a.no_dr:
+            rotations = rotations_emb[:, :4]
+        else:
+            dr = self.rotations_deform(hidden)
+            if a.apply_rotation:
+                q1, q2 = rotations_emb, dr
+                w = q1[:, 0] * q2[:, 0] - q1[:, 1] * q2[:, 1] - q1[:, 2] * q2[:, 2] - q1[:, 3] * q2[:, 3]
+                x = q1[:, 0] * q2[:, 1] + q1[:, 1] * q2[:, 0] + q1[:, 2] * q2[:, 3] - q1[:, 3] * q2[:, 2]
+                y = q1[:, 0] * q2[:, 2] - q1[:, 1] * q2[:, 3] + q1[:, 2] * q2[:, 0] + q1[:, 3] * q2[:, 1]
+                z = q1[:, 0] * q2[:, 3] + q1[:, 1] * q2[:, 2] - q1[:, 2] * q2[:, 1] + q1[:, 3] * q2[:, 0]
+                q3 = torch.stack((w, x, y, z), dim=1)
+                rotations = q3 / torch.norm(q3, dim=1, keepdim=True)
+            else:
+                rotations = rotations_emb[:, :4] + dr
+        opacity = opacity_emb[:, :1] if a.no_do else opacity_emb[:, :1] * mask + self.opacity_deform(hidden)
+        if a.no_dshs:
+            shs = shs_emb
+        else:
+            shs = shs_emb * mask.unsqueeze(-1) + self.shs_deform(hidden).reshape([shs_emb.shape[0], 16, 3])
+        return pts, scales, rotations, opacity, shs
+
+
+def poc_fre(input_data, poc_buf):
+    emb = (input_data.unsqueeze(-1) * poc_buf).flatten(-2)
+    return torch.cat([input_data, emb.sin(), emb.cos()], -1)
+
+
+def initialize_weights(m):
+    if isinstance(m, nn.Linear):
+        init.xavier_uniform_(m.weight, gain=1)
+        if m.bias is not None:
+            init.xavier_uniform_(m.weight, gain=1)
+
+
+class ref_deform_network(nn.Module):
+    def __init__(self, args):
+        super().__init__()
+        times_ch = 2 * args.timebase_pe + 1
+        self.timenet = nn.Sequential(nn.Linear(times_ch, args.timenet_width), nn.ReLU(),
+                                     nn.Linear(args.timenet_width, args.timenet_output))
+        self.deformation_net = RefDeformation(D=args.defor_depth, W=args.net_width, args=args)
+        self.register_buffer('time_poc', torch.FloatTensor([(2 ** i) for i in range(args.timebase_pe)]))
+        self.register_buffer('pos_poc', torch.FloatTensor([(2 ** i) for i in range(args.posebase_pe)]))
+        self.register_buffer('rotation_scaling_poc', torch.FloatTensor([(2 ** i) for i in range(args.scale_rotation_pe)]))
+        self.register_buffer('opacity_poc', torch.FloatTensor([(2 ** i) for i in range(args.opacity_pe)]))
+        self.apply(initialize_weights)
+
+    def forward(self, point, scales=None, rotations=None, opacity=None, shs=None, times_sel=None):
+        point_emb = poc_fre(point, self.pos_poc)                            # dead compute, kept: deformation.py:200-202
+        scales_emb = poc_fre(scales, self.rotation_scaling_poc)
+        rotations_emb = poc_fre(rotations, self.rotation_scaling_poc)
+        return self.deformation_net(point_emb, scales_emb, rotations_emb, opacity, shs, None, times_sel)
+
+
+class _RefRasterize(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, refC, means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, s):
+        args = (s.bg, means3D, colors_precomp, opacities, scales, rotations, s.scale_modifier, cov3Ds_precomp,
+                s.viewmatrix, s.projmatrix, s.tanfovx, s.tanfovy, s.image_height, s.image_width, sh, s.sh_degree,
+                s.campos, s.prefiltered, s.debug)
+        num_rendered, color, depth, radii, geomBuffer, binningBuffer, imgBuffer = refC.rasterize_gaussians(*args)
+        ctx.refC, ctx.s, ctx.num_rendered = refC, s, num_rendered
+        ctx.save_for_backward(colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, geomBuffer,
+                              binningBuffer, imgBuffer)
+        return color, radii, depth
+
+    @staticmethod
+    def backward(ctx, grad_out_color, grad_radii, grad_depth):
+        s = ctx.s
+        colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, geomBuffer, binningBuffer, imgBuffer = ctx.saved_tensors
+        args = (s.bg, means3D, radii, colors_precomp, scales, rotations, s.scale_modifier, cov3Ds_precomp, s.viewmatrix,
+                s.projmatrix, s.tanfovx, s.tanfovy, grad_out_color, sh, s.sh_degree, s.campos, geomBuffer,
+                ctx.num_rendered, binningBuffer, imgBuffer, s.debug)
+        (grad_means2D, grad_colors_precomp, grad_opacities, grad_means3D, grad_cov3Ds_precomp, grad_sh, grad_scales,
+         grad_rotations) = ctx.refC.rasterize_gaussians_backward(*args)
+        return (None, grad_means3D, grad_means2D, grad_sh, grad_colors_precomp, grad_opacities, grad_scales,
+                grad_rotations, grad_cov3Ds_precomp, None)
+
+
+class RefGaussianRasterizer(nn.Module):
+    def __init__(self, refC, raster_settings):
+        super().__init__()
+        self.refC, self.raster_settings = refC, raster_settings
+
+    def forward(self, means3D, means2D, opacities, shs=None, colors_precomp=None, scales=None, rotations=None,
+                cov3D_precomp=None):
+        e = lambda t: torch.Tensor([]) if t is None else t
+        return _RefRasterize.apply(self.refC, means3D, means2D, e(shs), e(colors_precomp), opacities, e(scales),
+                                   e(rotations), e(cov3D_precomp), self.raster_settings)
+
+
+def ref_render(refC, settings_cls, viewpoint_camera, pc, bg_color, scaling_modifier=1.0, stage="fine"):
+    """gaussian_renderer/__init__.py:18-138 with the reference's per-call H2D copies and time repeat."""
+    screenspace_points = torch.zeros_like(pc.get_xyz, dtype=pc.get_xyz.dtype, requires_grad=True, device="cuda") + 0
+    try:
+        screenspace_points.retain_grad()
+    except Exception:
+        pass
+    means3D = pc.get_xyz
+    tanfovx = math.tan(viewpoint_camera.FoVx * 0.5)
+    tanfovy = math.tan(viewpoint_camera.FoVy * 0.5)
+    raster_settings = settings_cls(
+        image_height=int(viewpoint_camera.image_height), image_width=int(viewpoint_camera.image_width),
+        tanfovx=tanfovx, tanfovy=tanfovy, bg=bg_color, scale_modifier=scaling_modifier,
+        viewmatrix=viewpoint_camera.world_view_transform.cuda(), projmatrix=viewpoint_camera.full_proj_transform.cuda(),
+        sh_degree=pc.active_sh_degree, campos=viewpoint_camera.camera_center.cuda(), prefiltered=False, debug=False)
+    time = torch.tensor(viewpoint_camera.time).to(means3D.device).repeat(means3D.shape[0], 1)
+    rasterizer = RefGaussianRasterizer(refC, raster_settings)
+    opacity, shs, scales, rotations = pc._opacity, pc.get_features, pc._scaling, pc._rotation
+    if "coarse" in stage:
+        means3D_final, scales_final, rotations_final, opacity_final, shs_final = means3D, scales, rotations, opacity, shs
+    else:
+        means3D_final, scales_final, rotations_final, opacity_final, shs_final = pc._deformation(
+            means3D, scales, rotations, opacity, shs, time)
+    scales_final = pc.scaling_activation(scales_final)
+    rotations_final = pc.rotation_activation(rotations_final)
+    opacity = pc.opacity_activation(opacity_final)
+    rendered_image, radii, depth = rasterizer(means3D=means3D_final, means2D=screenspace_points, shs=shs_final,
+                                              colors_precomp=None, opacities=opacity, scales=scales_final,
+                                              rotations=rotations_final, cov3D_precomp=None)
+    return {"render": rendered_image, "viewspace_points": screenspace_points, "visibility_filter": radii > 0,
+            "radii": radii, "depth": depth}
