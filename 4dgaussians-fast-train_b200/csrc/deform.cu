@@ -387,7 +387,7 @@ k_deform_fwd(Layout lo, NetPtrs net, FwdIO io, const float* __restrict__ packed,
     extern __shared__ __align__(16) float smem[];
     constexpr int G = (WN + 63) / 64;
     float* Fs = smem;                         // [F][TPP]   (F <= 128)
-    float* Hs = Fs + 128 * TPP;               // [WN][TPP]
+    float* Hs = Fs + lo.F * TPP;              // [WN][TPP]
     float* Zs = Hs + WN * TPP;                // [WN][TPP]
     float* Bs = Zs + WN * TPP;                // [KC][BP]
     const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
@@ -469,8 +469,8 @@ k_deform_bwd(Layout lo, NetPtrs net, GradPtrs gp, BwdIO io, const float* __restr
     extern __shared__ __align__(16) float smem[];
     constexpr int G = (WN + 63) / 64;
     float* Fs = smem;                         // [F][TPP]
-    constexpr int HROWS = WN < 128 ? 128 : WN;   // Hs is reused for g_feat [F <= 128][TPP]
-    float* Hs = Fs + 128 * TPP;               // [WN][TPP]  relu(h); later g_feat
+    const int HROWS = WN < lo.F ? lo.F : WN;  // Hs is reused for g_feat [F][TPP]
+    float* Hs = Fs + lo.F * TPP;              // [WN][TPP]  relu(h); later g_feat
     float* Zs = Hs + HROWS * TPP;             // [WN][TPP]  relu(z) -> g_z ; later g_h
     float* Gos = Zs + WN * TPP;               // [48][TPP]  upstream grads of the current head
     float* Bs = Gos + 48 * TPP;               // [KC][BP]
@@ -716,8 +716,9 @@ k_deform_bwd(Layout lo, NetPtrs net, GradPtrs gp, BwdIO io, const float* __restr
     }
 }
 
-template <int WN> constexpr size_t fwd_smem() { return sizeof(float) * (size_t)(128 * TPP + 2 * WN * TPP + KC * BP); }
-template <int WN> constexpr size_t bwd_smem() { return sizeof(float) * (size_t)(128 * TPP + (WN < 128 ? 128 : WN) * TPP + WN * TPP + 48 * TPP + KC * BP); }
+constexpr size_t SMEM_MAX = 227 * 1024;
+template <int WN> size_t fwd_smem(int F) { return sizeof(float) * (size_t)(F * TPP + 2 * WN * TPP + KC * BP); }
+template <int WN> size_t bwd_smem(int F) { return sizeof(float) * (size_t)(F * TPP + (WN < F ? F : WN) * TPP + WN * TPP + 48 * TPP + KC * BP); }
 
 static void fill_net(const FdgsDeformNet& n, NetPtrs& p) {
     for (int l = 0; l < FDGS_MAX_LEVELS; ++l) for (int k = 0; k < 6; ++k) p.planes[l][k] = n.planes[l][k];
@@ -803,22 +804,25 @@ int fdgs_deform_forward(const FdgsDeformForward* a, void* stream_) {
     const int ntiles = (a->P + TP - 1) / TP;
     const int grid = ntiles < sm_count() ? ntiles : sm_count();
     if (lo.Wn == 128) {
-        static bool set = false;
-        if (!set) { FDGS_CUDA(cudaFuncSetAttribute(k_deform_fwd<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fwd_smem<128>())); set = true; }
+        const size_t sm = fwd_smem<128>(lo.F);
+        if (sm > SMEM_MAX) return FDGS_E_SMEM;
+        FDGS_CUDA(cudaFuncSetAttribute(k_deform_fwd<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
         { FDGS_PROF("k_deform_fwd", stream);
-        k_deform_fwd<128><<<grid, NT, fwd_smem<128>(), stream>>>(lo, np, io, packed, trow, ntiles);
+        k_deform_fwd<128><<<grid, NT, sm, stream>>>(lo, np, io, packed, trow, ntiles);
         }
     } else if (lo.Wn == 64) {
-        static bool set = false;
-        if (!set) { FDGS_CUDA(cudaFuncSetAttribute(k_deform_fwd<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fwd_smem<64>())); set = true; }
+        const size_t sm = fwd_smem<64>(lo.F);
+        if (sm > SMEM_MAX) return FDGS_E_SMEM;
+        FDGS_CUDA(cudaFuncSetAttribute(k_deform_fwd<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
         { FDGS_PROF("k_deform_fwd", stream);
-        k_deform_fwd<64><<<grid, NT, fwd_smem<64>(), stream>>>(lo, np, io, packed, trow, ntiles);
+        k_deform_fwd<64><<<grid, NT, sm, stream>>>(lo, np, io, packed, trow, ntiles);
         }
     } else {
-        static bool set = false;
-        if (!set) { FDGS_CUDA(cudaFuncSetAttribute(k_deform_fwd<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fwd_smem<32>())); set = true; }
+        const size_t sm = fwd_smem<32>(lo.F);
+        if (sm > SMEM_MAX) return FDGS_E_SMEM;
+        FDGS_CUDA(cudaFuncSetAttribute(k_deform_fwd<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
         { FDGS_PROF("k_deform_fwd", stream);
-        k_deform_fwd<32><<<grid, NT, fwd_smem<32>(), stream>>>(lo, np, io, packed, trow, ntiles);
+        k_deform_fwd<32><<<grid, NT, sm, stream>>>(lo, np, io, packed, trow, ntiles);
         }
     }
     FDGS_LAUNCH_CHECK(a->debug, stream);
@@ -858,22 +862,25 @@ int fdgs_deform_backward(const FdgsDeformBackward* a, void* stream_) {
     const int ntiles = (a->P + TP - 1) / TP;
     const int grid = ntiles < sm_count() ? ntiles : sm_count();
     if (lo.Wn == 128) {
-        static bool set = false;
-        if (!set) { FDGS_CUDA(cudaFuncSetAttribute(k_deform_bwd<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bwd_smem<128>())); set = true; }
+        const size_t sm = bwd_smem<128>(lo.F);
+        if (sm > SMEM_MAX) return FDGS_E_SMEM;
+        FDGS_CUDA(cudaFuncSetAttribute(k_deform_bwd<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
         { FDGS_PROF("k_deform_bwd", stream);
-        k_deform_bwd<128><<<grid, NT, bwd_smem<128>(), stream>>>(lo, np, gp, io, packed, trow, gpacked, gtrow, ntiles);
+        k_deform_bwd<128><<<grid, NT, sm, stream>>>(lo, np, gp, io, packed, trow, gpacked, gtrow, ntiles);
         }
     } else if (lo.Wn == 64) {
-        static bool set = false;
-        if (!set) { FDGS_CUDA(cudaFuncSetAttribute(k_deform_bwd<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bwd_smem<64>())); set = true; }
+        const size_t sm = bwd_smem<64>(lo.F);
+        if (sm > SMEM_MAX) return FDGS_E_SMEM;
+        FDGS_CUDA(cudaFuncSetAttribute(k_deform_bwd<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
         { FDGS_PROF("k_deform_bwd", stream);
-        k_deform_bwd<64><<<grid, NT, bwd_smem<64>(), stream>>>(lo, np, gp, io, packed, trow, gpacked, gtrow, ntiles);
+        k_deform_bwd<64><<<grid, NT, sm, stream>>>(lo, np, gp, io, packed, trow, gpacked, gtrow, ntiles);
         }
     } else {
-        static bool set = false;
-        if (!set) { FDGS_CUDA(cudaFuncSetAttribute(k_deform_bwd<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bwd_smem<32>())); set = true; }
+        const size_t sm = bwd_smem<32>(lo.F);
+        if (sm > SMEM_MAX) return FDGS_E_SMEM;
+        FDGS_CUDA(cudaFuncSetAttribute(k_deform_bwd<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
         { FDGS_PROF("k_deform_bwd", stream);
-        k_deform_bwd<32><<<grid, NT, bwd_smem<32>(), stream>>>(lo, np, gp, io, packed, trow, gpacked, gtrow, ntiles);
+        k_deform_bwd<32><<<grid, NT, sm, stream>>>(lo, np, gp, io, packed, trow, gpacked, gtrow, ntiles);
         }
     }
     FDGS_LAUNCH_CHECK(a->debug, stream);

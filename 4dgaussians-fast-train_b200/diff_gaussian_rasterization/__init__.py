@@ -43,6 +43,12 @@ def cpu_deep_copy_tuple(input_tuple):
 
 
 _pinned = {}
+_last_R = 0
+
+
+def last_num_rendered():
+    """num_rendered (R) of the most recent forward call in this process (bench / diagnostics)."""
+    return _last_R
 
 
 def _counts_host(device):
@@ -122,6 +128,8 @@ def _forward_native(bg, means3D, colors_precomp, opacities, scales, rotations, s
         st = _stream()
         L.check(lib.fdgs_raster_forward_plan(C.byref(a), st), "fdgs_raster_forward_plan")
         R = int(counts[0])
+        global _last_R
+        _last_R = R
         binb = torch.empty((lib.fdgs_raster_bin_bytes(R),), dtype=torch.uint8, device=dev)
         a.bin_ws, a.bin_bytes = binb.data_ptr(), binb.numel()
         extras = {}

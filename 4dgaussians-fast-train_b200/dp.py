@@ -1,0 +1,103 @@
+"""View-parallel data parallelism for the training hot path.
+
+The reference renders the B views of a batch in a Python loop and calls one backward on the mean L1 of
+the concatenated images (train.py:197-262); views share only parameters.  Here view i of the batch goes
+to rank i mod G, every rank holds a full replica of the Gaussians + HexPlane + MLP, and the ONE exchange
+step of an iteration is a sum all-reduce of a flat FP32 gradient bucket.
+
+The bucket is allocated once; every parameter's `.grad` (and the view-space gradient accumulator the
+densifier reads, train.py:266-268) is a VIEW into it, so autograd accumulates straight into the bucket
+and there is no pack / unpack pass around the collective.  Parameters that never receive a gradient
+(timenet.*, grid.aabb, disabled heads) are not in the bucket.
+"""
+import torch
+import torch.distributed as dist
+
+
+def shard_views(n_views, rank, world):
+    """Indices of the batch's views owned by `rank` (view i -> rank i mod world)."""
+    return [i for i in range(n_views) if i % world == rank]
+
+
+class GradBucket:
+    """One flat FP32 buffer holding the gradients of `params` plus named extra slots."""
+
+    def __init__(self, params, extra=None, device=None):
+        self.params = [p for p in params if p.requires_grad]
+        if not self.params and not extra:
+            raise ValueError("GradBucket needs at least one tensor")
+        dev = device if device is not None else self.params[0].device
+        sizes = [p.numel() for p in self.params]
+        self.extra_shapes = dict(extra or {})
+        for shape in self.extra_shapes.values():
+            n = 1
+            for s in shape:
+                n *= int(s)
+            sizes.append(n)
+        # 64-float (256 B) aligned slots keep every view vector-load friendly
+        self.offsets = []
+        off = 0
+        for n in sizes:
+            self.offsets.append(off)
+            off += (n + 63) // 64 * 64
+        self.flat = torch.zeros(off, dtype=torch.float32, device=dev)
+        self.views = []
+        for p, o in zip(self.params, self.offsets):
+            v = self.flat[o:o + p.numel()].view(p.shape)
+            self.views.append(v)
+        self.extra = {}
+        for (name, shape), o in zip(self.extra_shapes.items(), self.offsets[len(self.params):]):
+            n = 1
+            for s in shape:
+                n *= int(s)
+            self.extra[name] = self.flat[o:o + n].view(tuple(shape))
+        self.attach()
+
+    def attach(self):
+        """(Re)points every parameter's .grad at its bucket slot."""
+        for p, v in zip(self.params, self.views):
+            p.grad = v
+
+    def zero(self):
+        self.flat.zero_()
+        # an optimizer's zero_grad(set_to_none=True) would have dropped the views
+        for p, v in zip(self.params, self.views):
+            if p.grad is None or p.grad.data_ptr() != v.data_ptr():
+                p.grad = v
+
+    def nbytes(self):
+        return self.flat.numel() * 4
+
+    def all_reduce(self, group=None, async_op=False):
+        """Sum over ranks; a no-op outside an initialised process group or at world size 1."""
+        if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+            return None
+        return dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=group, async_op=async_op)
+
+
+def l1_view_loss(image, gt, n_views_total):
+    """This view's share of the reference's loss: l1_loss(cat(images), cat(gts)) over B equal-size views
+    (utils/loss_utils.py l1_loss = mean|a-b|, train.py:231-244) == sum_i mean|img_i - gt_i| / B."""
+    return (image - gt).abs().mean() / float(n_views_total)
+
+
+def train_iteration(render_fn, pc, cams, gts, bg, bucket, rank=0, world=1, read_loss=False):
+    """One fwd+bwd iteration over the batch `cams` (all B views; this rank renders its shard).
+    Returns (local loss sum as a tensor, max radii, visibility) like train.py:229-232 needs."""
+    B = len(cams)
+    bucket.zero()
+    loss_sum = None
+    radii_max = None
+    for i in shard_views(B, rank, world):
+        out = render_fn(cams[i], pc, bg_color=bg, stage="fine")
+        loss = l1_view_loss(out["render"], gts[i], B)
+        loss.backward()
+        vs = out["viewspace_points"].grad
+        if vs is not None and "viewspace" in bucket.extra:
+            bucket.extra["viewspace"].add_(vs)
+        loss_sum = loss.detach() if loss_sum is None else loss_sum + loss.detach()
+        radii_max = out["radii"] if radii_max is None else torch.maximum(radii_max, out["radii"])
+    bucket.all_reduce()
+    if read_loss and loss_sum is not None:
+        return float(loss_sum), radii_max
+    return loss_sum, radii_max

@@ -1,0 +1,417 @@
+"""bench.py — fwd+bwd train iters/s (and render FPS) of the 4D-Gaussian hot path on N B200s.
+
+One "step" = one training iteration of the BASELINE.json DyNeRF configuration: for each of the B=8 views of
+the batch  deformation fwd -> exp/normalize/sigmoid -> rasterize fwd -> L1 vs a fixed random GT -> backward
+through all of it,  then (N>1) one NCCL all-reduce of the flat gradient bucket.  Views are sharded
+view i -> rank i mod N (strong scaling: the batch is fixed).  Optimizer step, densification, data loading
+and logging are outside the measured unit.
+
+  python bench.py [--gpus N --steps K --warmup W] [--impl fdgs|reference] [--config dynerf]
+
+`--impl reference` runs the reference arm: the reference's PyTorch deformation ops + the UNMODIFIED
+reference CUDA rasterizer compiled from its own sources (oracle/_ref), i.e. what the reference gives on
+this GPU; none of the fdgs kernels is on that path.  See DESIGN.md "measurement".
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for _p in (ROOT, os.path.join(ROOT, "oracle"), os.path.join(ROOT, "tests")):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="fdgs", choices=["fdgs", "reference"])
+    ap.add_argument("--config", default="dynerf")
+    ap.add_argument("--views", type=int, default=0, help="views per batch (default: the config's)")
+    ap.add_argument("--points", type=int, default=0, help="Gaussians (default: the config's)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the render-FPS and per-kernel passes")
+    return ap.parse_args()
+
+
+# ------------------------------------------------------------------------------------------------ clocks
+class ClockSampler:
+    """nvidia-smi sampled every 200 ms DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        self.p = None
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(index), f"--query-gpu={self.Q}",
+                                       "--format=csv,noheader,nounits", "-lms", "200"], stdout=self.f, stderr=subprocess.DEVNULL)
+        except Exception:
+            self.p = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.p is None:
+            return out
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except Exception:
+            self.p.kill()
+        self.f.flush()
+        self.f.seek(0)
+        sm, mx, reasons = [], [], set()
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        for line in self.f.read().splitlines():
+            c = [x.strip() for x in line.split(",")]
+            if len(c) < 7:
+                continue
+            try:
+                sm.append(float(c[0])); mx.append(float(c[1]))
+            except ValueError:
+                continue
+            for n, v in zip(names, c[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        self.f.close()
+        try:
+            os.unlink(self.f.name)
+        except OSError:
+            pass
+        if sm:
+            sm.sort()
+            out.update(sm_mhz=sm[len(sm) // 2], sm_max_mhz=max(mx), reasons=sorted(reasons), samples=len(sm))
+        return out
+
+
+# ------------------------------------------------------------------------------------------------ scene
+def build_scene(cfg_name, impl, dev, views, points):
+    import fdgs  # noqa: F401
+    from fdgs import synth
+    from fdgs.configs import CONFIGS
+    cfg = dict(CONFIGS[cfg_name])
+    if views:
+        cfg["views"] = views
+    if points:
+        cfg["P"] = points
+    args = cfg["args"]()
+    if impl == "fdgs":
+        from fdgs.deformation import deform_network as make_net
+    else:
+        import ref_port
+        make_net = ref_port.ref_deform_network
+    net = synth.seeded_deformation(make_net, args, seed=1234, device=dev)
+    g = synth.make_gaussians(cfg["P"], extent=cfg["extent"], logscale=cfg["logscale"], seed=0, device=dev)
+    pc = synth.SynthGaussians(g, net).to(dev)
+    net.deformation_net.set_aabb(pc._xyz.detach().max(0).values.tolist(), pc._xyz.detach().min(0).values.tolist())
+    B = cfg["views"]
+    cams = synth.make_cameras(cfg["W"], cfg["H"], cfg["fovx"], B, device=dev)
+    gen = torch.Generator().manual_seed(99)
+    gts_host = [torch.rand((3, cfg["H"], cfg["W"]), generator=gen).pin_memory() if dev != "cpu" else
+                torch.rand((3, cfg["H"], cfg["W"]), generator=gen) for _ in range(B)]
+    return cfg, args, pc, net, cams, gts_host
+
+
+def host_cameras(cams):
+    """Pinned host copies of the per-view camera tensors (the e2e path uploads them every step,
+    as gaussian_renderer/__init__.py:45-48 does)."""
+    out = []
+    for c in cams:
+        out.append({k: getattr(c, k).cpu().pin_memory() for k in ("world_view_transform", "full_proj_transform", "camera_center")})
+    return out
+
+
+def upload_camera(cam, host, dev):
+    from types import SimpleNamespace
+    return SimpleNamespace(image_width=cam.image_width, image_height=cam.image_height, FoVx=cam.FoVx, FoVy=cam.FoVy,
+                           time=cam.time, **{k: v.to(dev, non_blocking=True) for k, v in host.items()})
+
+
+def make_bucket(pc, net, dev):
+    from fdgs.dp import GradBucket
+    params = [pc._xyz, pc._scaling, pc._rotation, pc._opacity, pc._features_dc, pc._features_rest]
+    dn = net.deformation_net
+    hm_names = ("pos_deform", "scales_deform", "rotations_deform", "opacity_deform", "shs_deform")
+    a = dn.args
+    active = [not a.no_dx, not a.no_ds, not a.no_dr, not a.no_do, not a.no_dshs]
+    params += [p for planes in dn.grid.grids for p in planes]
+    params += list(dn.feature_out.parameters())
+    for name, on in zip(hm_names, active):
+        if on:
+            params += list(getattr(dn, name).parameters())
+    return GradBucket(params, extra={"viewspace": (pc._xyz.shape[0], 3)}, device=dev)
+
+
+# ------------------------------------------------------------------------------------------------ roofline
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            d = json.load(f)
+        return dict(hbm=float(d["hbm_gbs"]), tensor=float(d.get("bf16_tflops_sustained", d["bf16_tflops"])), src="measured")
+    return dict(hbm=6650.0, tensor=1400.0, src="fallback")   # B200_PROFILING.md fallback
+
+
+def algorithmic_per_launch(kernel, s):
+    """(bound, amount, unit) of ALGORITHMIC traffic/work of one launch of `kernel` for one view of the workload
+    s = dict(P, M, R, HW, T, F, Wn, heads, sum_out, io_bytes).  Figures are stated in DESIGN.md §kernels."""
+    P, M, R, HW, T = s["P"], s["M"], s["R"], s["HW"], s["T"]
+    mlp_fwd_flop = 2.0 * P * (s["F"] * s["Wn"] + s["heads"] * s["Wn"] ** 2 + s["Wn"] * s["sum_out"])
+    table = {
+        "k_preprocess": ("hbm", P * (44 + 12 * M + 75) + 0.0),
+        "k_tile_scan": ("hbm", T * 20.0),
+        "k_scatter": ("hbm", P * 16.0 + R * 8.0),
+        "k_tile_sort": ("hbm", R * (8 + 36 + 48) + 0.0),
+        "k_blend_fwd": ("hbm", R * 48.0 + HW * 24.0 + T * 8.0),
+        "k_blend_bwd": ("hbm", R * 48.0 + HW * 20.0 + T * 8.0 + P * 44.0),
+        "k_preprocess_bwd": ("hbm", P * (301.0 - 192 + 12 * M) + P * (64.0 + 12 * M)),
+        "k_deform_fwd": ("tensor", mlp_fwd_flop),
+        "k_deform_bwd": ("tensor", 2.0 * mlp_fwd_flop),
+    }
+    return table.get(kernel)
+
+
+def roofline_for(prof, shape, peaks):
+    """prof: {kernel: (launches, total_ms)} from the in-library CUDA-event profiler."""
+    if not prof:
+        return None, {}
+    shares = {k: v[1] for k, v in prof.items()}
+    tot = sum(shares.values()) or 1.0
+    top = max(shares, key=shares.get)
+    n, ms = prof[top]
+    alg = algorithmic_per_launch(top, shape)
+    per_kernel = {k: {"launches": v[0], "avg_us": round(1e3 * v[1] / max(v[0], 1), 2), "share": round(v[1] / tot, 4)}
+                  for k, v in sorted(prof.items(), key=lambda kv: -kv[1][1])}
+    if alg is None:
+        return None, per_kernel
+    bound, amount = alg
+    sec = (ms / n) * 1e-3
+    if bound == "hbm":
+        achieved, unit, peak = amount / sec / 1e9, "GB/s", peaks["hbm"]
+    else:
+        achieved, unit, peak = amount / sec / 1e12, "TFLOP/s", peaks["tensor"]
+    return {"kernel": top, "bound": bound, "achieved": round(achieved, 3), "peak": peak, "unit": unit,
+            "frac": round(achieved / peak, 5), "traffic": None, "peak_source": peaks["src"],
+            "avg_launch_us": round(sec * 1e6, 2), "algorithmic_per_launch": amount}, per_kernel
+
+
+# ------------------------------------------------------------------------------------------------ CPU baseline
+def cpu_baseline(cfg, args, n_views):
+    """Bounded sample on the host cores: ONE view of the batch — the reference's PyTorch deformation ops
+    (oracle/ref_port.py, all cores) fwd+bwd plus the CPU rasterizer restatement (oracle/raster_oracle.cpp,
+    FP64 instantiation, 1 core) fwd+bwd — extrapolated to the B-view iteration."""
+    import math
+    import ref_port
+    import raster_oracle
+    from fdgs import synth
+    ncores = os.cpu_count() or 1
+    torch.set_num_threads(ncores)
+    P = cfg["P"]
+    net = synth.seeded_deformation(ref_port.ref_deform_network, args, seed=1234, device="cpu")
+    g = synth.make_gaussians(P, extent=cfg["extent"], logscale=cfg["logscale"], seed=0, device="cpu")
+    net.deformation_net.set_aabb(g["xyz"].max(0).values.tolist(), g["xyz"].min(0).values.tolist())
+    leaves = {k: v.clone().requires_grad_(True) for k, v in g.items()}
+    shs = torch.cat([leaves["f_dc"], leaves["f_rest"]], dim=1)
+    t = torch.full((P, 1), 0.25)
+    t0 = time.perf_counter()
+    outs = net(leaves["xyz"], leaves["scaling"], leaves["rotation"], leaves["opacity"], shs, t)
+    sum(o.sum() for o in outs).backward()
+    t_def = time.perf_counter() - t0
+    cam = synth.make_camera(cfg["W"], cfg["H"], cfg["fovx"], angle=0.0, time=0.25)
+    xyz, sc, rot, op, sh = [o.detach() for o in outs]
+    gen = torch.Generator().manual_seed(5)
+    dpix = torch.randn((3, cfg["H"], cfg["W"]), generator=gen)
+    t0 = time.perf_counter()
+    raster_oracle.rasterize(W=cfg["W"], H=cfg["H"], tanfovx=math.tan(cam.FoVx * 0.5), tanfovy=math.tan(cam.FoVy * 0.5),
+                            bg=torch.ones(3).numpy(), means3D=xyz.numpy(), opacities=torch.sigmoid(op).numpy(),
+                            viewmatrix=cam.world_view_transform.numpy(), projmatrix=cam.full_proj_transform.numpy(),
+                            campos=cam.camera_center.numpy(), shs=sh.numpy(), scales=torch.exp(sc).numpy(),
+                            rotations=torch.nn.functional.normalize(rot).numpy(), sh_degree=3, dL_dpix=dpix.numpy(), f64=True)
+    t_ras = time.perf_counter() - t0
+    per_iter = (t_def + t_ras) * n_views
+    return {"value": round(1.0 / per_iter, 6), "unit": "iters/s", "cores": ncores, "kind": "port",
+            "sample": f"1 of {n_views} views at full size (P={P}, {cfg['W']}x{cfg['H']}): torch deformation fwd+bwd "
+                      f"{t_def:.2f}s on {ncores} threads + C++ raster restatement fwd+bwd {t_ras:.2f}s on 1 thread; x{n_views}",
+            "deform_s_per_view": round(t_def, 3), "raster_s_per_view": round(t_ras, 3)}
+
+
+# ------------------------------------------------------------------------------------------------ main
+def main():
+    a = parse()
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if a.impl == "reference" and rank != 0:
+        return 0          # the reference has no multi-GPU path: rank 0 alone runs the whole batch
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the fdgs hot path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dev = f"cuda:{local_rank}"
+    use_dist = world > 1 and a.impl == "fdgs"
+    if use_dist:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device(dev))
+    eff_world, eff_rank = (world, rank) if use_dist else (1, 0)
+
+    if a.impl == "reference":
+        import build_ref
+        if not build_ref.available():
+            print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref (reference rasterizer built from its own sources) is missing"}))
+            return 0
+        refC = build_ref.load()
+        import ref_port
+        from fdgs.diff_gaussian_rasterization import GaussianRasterizationSettings as SettingsTuple   # plain NamedTuple
+
+        def render_fn(cam, pc, bg_color=None, stage="fine"):
+            return ref_port.ref_render(refC, SettingsTuple, cam, pc, bg_color, stage=stage)
+        launch_count = lambda: 0
+        L = None
+    else:
+        import fdgs  # noqa: F401
+        from fdgs import _lib as L
+        from fdgs.render import render as render_fn
+        L.load()
+        launch_count = L.launch_count
+
+    cfg, args, pc, net, cams, gts_host = build_scene(a.config, a.impl, dev, a.views, a.points)
+    from fdgs.dp import train_iteration, shard_views
+    B = cfg["views"]
+    bucket = make_bucket(pc, net, dev)
+    bg = torch.ones(3, device=dev)
+    gts_dev = [g.to(dev) for g in gts_host]
+    cams_host = host_cameras(cams)
+    mine = shard_views(B, eff_rank, eff_world)
+
+    def barrier():
+        if use_dist:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step_resident():
+        train_iteration(render_fn, pc, cams, gts_dev, bg, bucket, eff_rank, eff_world)
+
+    stage_gt = [None] * B
+
+    def step_e2e():
+        # host -> device: this step's GT images and camera tensors (pinned), device -> host: the loss
+        cs = list(cams)
+        for i in mine:
+            stage_gt[i] = gts_host[i].to(dev, non_blocking=True)
+            cs[i] = upload_camera(cams[i], cams_host[i], dev)
+        loss, _ = train_iteration(render_fn, pc, cs, stage_gt, bg, bucket, eff_rank, eff_world, read_loss=True)
+        return loss
+
+    def timed(fn, steps):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if use_dist:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms)
+
+    for _ in range(max(a.warmup, 3)):
+        step_resident()
+    sampler = ClockSampler(local_rank) if eff_rank == 0 else None
+    n0 = launch_count()
+    ms = timed(step_resident, a.steps)
+    launches = launch_count() - n0
+    clocks = sampler.stop() if sampler else {}
+    for _ in range(2):
+        step_e2e()
+    ms_e2e = timed(step_e2e, a.steps)
+
+    extras = {}
+    roof, per_kernel = None, {}
+    if not a.no_extras:
+        # render FPS: forward only, no autograd (render.py:56-70 of the reference)
+        with torch.no_grad():
+            for i in mine[:1]:
+                render_fn(cams[i], pc, bg_color=bg, stage="fine")
+            nfr = 0
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            barrier(); e0.record()
+            for _ in range(3):
+                for i in mine:
+                    render_fn(cams[i], pc, bg_color=bg, stage="fine"); nfr += 1
+            e1.record(); barrier()
+            fps_ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+            if use_dist:
+                dist.all_reduce(fps_ms, op=dist.ReduceOp.MAX)
+            extras["render_fps"] = round(3 * B / (float(fps_ms) * 1e-3), 2)
+        if L is not None and eff_rank == 0:
+            # per-kernel CUDA-event timing inside the library, on the launching stream
+            L.profile_enable(True)
+            for _ in range(2):
+                step_resident()
+            prof = L.profile_collect()
+            L.profile_enable(False)
+            P = cfg["P"]
+            a_ = args
+            heads_on = [not a_.no_dx, not a_.no_ds, not a_.no_dr, not a_.no_do, not a_.no_dshs]
+            outs = (3, 3, 4, 1, 48)
+            with torch.no_grad():
+                render_fn(cams[mine[0]], pc, bg_color=bg, stage="fine")
+            from fdgs.diff_gaussian_rasterization import last_num_rendered
+            R = last_num_rendered()
+            shape = dict(P=P, M=16, R=R, HW=cfg["W"] * cfg["H"], T=((cfg["W"] + 15) // 16) * ((cfg["H"] + 15) // 16),
+                         F=a_.kplanes_config["output_coordinate_dim"] * len(a_.multires), Wn=a_.net_width,
+                         heads=sum(heads_on), sum_out=sum(o for o, on in zip(outs, heads_on) if on))
+            roof, per_kernel = roofline_for(prof, shape, load_peaks())
+            extras["num_rendered_per_view"] = R
+
+    if eff_rank == 0:
+        P = cfg["P"]
+        h2d = sum(gts_host[i].numel() * 4 + 35 * 4 for i in mine)
+        line = {
+            "metric": "fwd+bwd train iters/s (DyNeRF-shape, 300k G, batch 8 views)", "value": round(a.steps / (ms * 1e-3), 4),
+            "unit": "iters/s", "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
+            "ms_per_step": round(ms / a.steps, 3), "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"{a.config}: {P} Gaussians, {cfg['W']}x{cfg['H']}, batch {B} views, deformation+rasterizer fwd+bwd"
+                                   + (", NCCL grad all-reduce" if use_dist else ""),
+                       "views_per_rank": len(mine), "parallelism": f"view-dp{world}",
+                       "l2": "working set per step >> L2 (>=400 MB per view streamed; inputs larger than L2)",
+                       "grad_bucket_bytes": bucket.nbytes()},
+            "clocks": clocks,
+            "e2e": {"value": round(a.steps / (ms_e2e * 1e-3), 4), "unit": "iters/s", "h2d_bytes_per_step": h2d,
+                    "d2h_bytes_per_step": 4},
+            "gpu_launches": int(launches),
+        }
+        line.update(extras)
+        if a.impl == "reference":
+            line["impl"] = "reference"
+            line["gpu_launches"] = 0
+            line["config"]["reference_arm"] = ("reference PyTorch deformation ops on the GPU + unmodified reference CUDA rasterizer "
+                                               "(oracle/_ref, sm_100); single GPU runs the whole batch")
+            line["e2e"] = {"value": line["e2e"]["value"], "unit": "iters/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4}
+        else:
+            line["roofline"] = roof
+            line["kernels"] = per_kernel
+        if world == 1 and not a.no_cpu_baseline:
+            try:
+                line["cpu_baseline"] = cpu_baseline(cfg, args, B)
+            except Exception as ex:   # the CPU leg must never take the GPU numbers down with it
+                line["cpu_baseline"] = {"error": repr(ex)}
+        print(json.dumps(line), flush=True)
+    if use_dist:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())
