@@ -76,6 +76,7 @@ class FdgsDeformForward(C.Structure):
         ("out_opacity", C.c_void_p), ("out_shs", C.c_void_p),
         ("packed_ws", C.c_void_p), ("packed_bytes", C.c_size_t),
         ("trow_ws", C.c_void_p), ("trow_bytes", C.c_size_t),
+        ("wprep_ws", C.c_void_p), ("wprep_bytes", C.c_size_t),
         ("debug", C.c_int32),
     ]
 
@@ -116,6 +117,7 @@ SYMBOLS = {
     "fdgs_mark_visible": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "fdgs_deform_packed_bytes": (C.c_size_t, [C.POINTER(FdgsDeformNet)]),
     "fdgs_deform_trow_bytes": (C.c_size_t, [C.POINTER(FdgsDeformNet)]),
+    "fdgs_deform_wprep_bytes": (C.c_size_t, [C.POINTER(FdgsDeformNet)]),
     "fdgs_deform_forward": (C.c_int, [C.POINTER(FdgsDeformForward), C.c_void_p]),
     "fdgs_deform_backward_ws_bytes": (C.c_size_t, [C.POINTER(FdgsDeformNet)]),
     "fdgs_deform_backward": (C.c_int, [C.POINTER(FdgsDeformBackward), C.c_void_p]),

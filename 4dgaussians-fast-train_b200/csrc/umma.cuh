@@ -10,8 +10,10 @@
 //     column groups advance by SBO = rows * 16 B, row groups of 8 by LBO = 128 B.
 // A thread that owns one row writes 16-byte vectors at consecutive addresses across the warp (conflict free).
 //
-// 3xTF32: x = hi + lo with hi = x truncated to TF32 (top 19 bits) and lo = x - hi (exact);
-// a*b ~= hi_a*hi_b + lo_a*hi_b + hi_a*lo_b accumulated in FP32 in TMEM (error ~2^-21 per product).
+// 3xTF32: x = hi + lo with hi = x rounded to TF32 and lo = (x - hi) rounded to TF32;
+// a*b ~= hi_a*hi_b + lo_a*hi_b + hi_a*lo_b accumulated in FP32 in TMEM (error ~2^-23 per product).
+// NOTE: the plain no-swizzle MN-major view described above does NOT work for 32-bit operands (the MMA
+// silently produces zeros, measured); MN-major TF32 operands use the swizzled tile32 layout below.
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -31,6 +33,18 @@ __device__ __forceinline__ void split_tf32(float x, float& hi, float& lo) {
     hi = __uint_as_float(__float_as_uint(x) & 0xFFFFE000u);
     lo = x - hi;
 }
+// Round-to-nearest split: hi = rna_tf32(x), lo = rna_tf32(x - hi).  Both are exactly representable in TF32, so
+// the tensor core's truncation of its inputs (measured, tools/umma_probe.cu) is a no-op and the dropped
+// remainder is <= 2^-24 |x|: a 3-pass product is FP32-accurate.
+__device__ __forceinline__ float rna_tf32(float x) {
+    uint32_t u;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(x));
+    return __uint_as_float(u);
+}
+__device__ __forceinline__ void split_tf32_rn(float x, float& hi, float& lo) {
+    hi = rna_tf32(x);
+    lo = rna_tf32(x - hi);
+}
 
 __device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -41,6 +55,9 @@ __device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
 __device__ __forceinline__ void fence_mbar_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
 __device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_addr(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_addr(bar)) : "memory");
 }
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     uint32_t ok;
@@ -99,6 +116,14 @@ __device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t (&v)[16
     asm volatile("tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16};"
                  ::"r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]),
                    "r"(v[8]), "r"(v[9]), "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15]) : "memory");
+}
+__device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&v)[32]) {
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+                 "{%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31,%32};"
+                 ::"r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]),
+                   "r"(v[8]), "r"(v[9]), "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15]),
+                   "r"(v[16]), "r"(v[17]), "r"(v[18]), "r"(v[19]), "r"(v[20]), "r"(v[21]), "r"(v[22]), "r"(v[23]),
+                   "r"(v[24]), "r"(v[25]), "r"(v[26]), "r"(v[27]), "r"(v[28]), "r"(v[29]), "r"(v[30]), "r"(v[31]) : "memory");
 }
 __device__ __forceinline__ void tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 

@@ -127,6 +127,8 @@ class _DeformFunction(torch.autograd.Function):
             a.out_xyz, a.out_scales, a.out_rotations, a.out_opacity, a.out_shs = [L.ptr(t) for t in outs]
             a.packed_ws, a.packed_bytes = packed.data_ptr(), packed.numel()
             a.trow_ws, a.trow_bytes = trow.data_ptr(), trow.numel()
+            wprep = net_mod._wprep(lib, a.net, dev)
+            a.wprep_ws, a.wprep_bytes = wprep.data_ptr(), wprep.numel()
             a.debug = 0
             L.check(lib.fdgs_deform_forward(C.byref(a), C.c_void_p(torch.cuda.current_stream().cuda_stream)),
                     "fdgs_deform_forward")
@@ -205,7 +207,7 @@ class Deformation(nn.Module):
         self.grid = HexPlaneField(args.bounds, args.kplanes_config, args.multires)
         self.args = args
         self.ratio = 0
-        self.precision = 0      # 0: FP32-equivalent, 1: single-pass TF32 (opt-in speed mode)
+        self.precision = 0      # 0: FP32-equivalent (3xTF32 on tcgen05), 1: single-pass TF32, 2: FP32 CUDA-core kernels
         self._packed = None
         self._packed_key = None
         self.create_net()
@@ -291,6 +293,15 @@ class Deformation(nn.Module):
             self._packed_key = None
         self._pending_key = key
         return self._packed, (self._packed_key == key)
+
+    def _wprep(self, lib, net, dev):
+        """Scratch for the tensor-core formatted MLP weights (rewritten by every call)."""
+        n = lib.fdgs_deform_wprep_bytes(C.byref(net))
+        w = getattr(self, "_wprep_ws", None)
+        if w is None or w.numel() < n or w.device != dev:
+            w = torch.empty((max(n, 256),), dtype=torch.uint8, device=dev)
+            self._wprep_ws = w
+        return w
 
     def _mark_packed_valid(self):
         self._packed_key = self._pending_key

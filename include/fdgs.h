@@ -194,7 +194,8 @@ typedef struct FdgsDeformForward {
     int32_t sh_coeffs;              /* second dim of shs (16, or 1 with broadcast)   */
     float time;                     /* the view's timestamp (times_sel[:,0] is constant per view)   */
     const float* time_dev;          /* optional DEVICE scalar overriding `time` (avoids a host sync) */
-    int32_t precision;              /* 0 = FP32 (SIMT / 3xTF32-split), 1 = single-pass TF32          */
+    int32_t precision;              /* 0 = FP32-equivalent (tcgen05 3xTF32 split), 1 = single-pass TF32 (faster, ~1e-3),
+                                       2 = FP32 CUDA-core kernels (no tensor cores)                   */
     int32_t planes_packed_valid;    /* 1 = packed_ws already holds the packed planes of these parameters */
     const float* xyz;               /* [P,3] */
     const float* scales;            /* [P,3] */
@@ -213,11 +214,14 @@ typedef struct FdgsDeformForward {
                                              views until the plane parameters change                     */
     void* trow_ws;   size_t trow_bytes;   /* fdgs_deform_trow_bytes(): this view's pre-blended time rows;
                                              must stay alive until the matching backward              */
+    void* wprep_ws;  size_t wprep_bytes;  /* fdgs_deform_wprep_bytes(): MLP weights split hi/lo and tiled for the
+                                             tensor cores; rewritten by every call (scratch)          */
     int32_t debug;
 } FdgsDeformForward;
 
 size_t fdgs_deform_packed_bytes(const FdgsDeformNet* net);
 size_t fdgs_deform_trow_bytes(const FdgsDeformNet* net);
+size_t fdgs_deform_wprep_bytes(const FdgsDeformNet* net);
 int fdgs_deform_forward(const FdgsDeformForward* a, void* stream);
 
 typedef struct FdgsDeformBackward {
