@@ -114,9 +114,16 @@ def test_forward_vs_cpu_oracle(kw):
     bad = nc != c["n_contrib"].astype(np.int64)
     assert bad.sum() <= max(2, nc.size // 20000)
     ok = torch.tensor(~bad)
-    col_o, col_c = o["color"].cpu()[:, ok], torch.tensor(c["color"])[:, ok]
-    assert util.rel_err(col_o, col_c) < IMG_TOL
-    assert util.rel_err(o["depth"].cpu()[:, ok], torch.tensor(c["depth"])[:, ok]) < IMG_TOL
+    # the same ulp can move one contributor across the alpha < 1/255 skip (forward.cu:336) without changing
+    # n_contrib: such a pixel differs by <= alpha*|colour| ~ 4e-3. Allow the same handful of pixels, bound their
+    # error by that skip size, and hold every other pixel to IMG_TOL.
+    for name in ("color", "depth"):
+        a = o[name].cpu().double()[:, ok]
+        b = torch.tensor(c[name]).double()[:, ok]
+        err = ((a - b).abs() / (b.abs().max() + 1e-30)).max(0).values
+        flips = err >= IMG_TOL
+        assert int(flips.sum()) <= max(2, nc.size // 20000), (name, int(flips.sum()), float(err.max()))
+        assert float(err.max()) < 5e-3, (name, float(err.max()))
 
 
 @pytest.mark.parametrize("kw", [dict(P=1200, W=160, H=96, logscale=-2.6, seed=3), dict(P=300, W=64, H=64, logscale=-1.0, seed=8, bg=0.0)])
