@@ -1,0 +1,117 @@
+"""Host logic of the view-parallel path (fdgs/dp.py) on CPU: world_size-2 `gloo` processes.
+
+The render function is a small differentiable stand-in (no CUDA): what is under test is the sharding rule
+(view i -> rank i mod G), the loss scaling that makes summed shard gradients equal the reference's single
+l1_loss over the concatenated batch (train.py:231-244), the flat bucket whose slots ARE the .grad tensors,
+and the single all-reduce."""
+import os
+import socket
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+import fdgs  # noqa: F401
+from fdgs import dp
+
+
+class _PC(torch.nn.Module):
+    def __init__(self):
+        super().__init__()
+        g = torch.Generator().manual_seed(3)
+        self.a = torch.nn.Parameter(torch.randn(37, 3, generator=g))
+        self.b = torch.nn.Parameter(torch.randn(5, generator=g))
+        self.frozen = torch.nn.Parameter(torch.randn(4, generator=g), requires_grad=False)
+
+
+def _render(cam, pc, bg_color=None, stage="fine"):
+    vs = torch.zeros(37, 3, requires_grad=True)
+    img = (pc.a * cam).sum(0)[:, None, None] * torch.ones(3, 4, 6) + pc.b.sum() * cam + bg_color[:, None, None] + vs.sum() * cam
+    vs.retain_grad()
+    return dict(render=img, viewspace_points=vs, radii=torch.full((37,), int(cam * 10), dtype=torch.int32))
+
+
+def _batch(B):
+    g = torch.Generator().manual_seed(11)
+    cams = [0.3 + 0.2 * i for i in range(B)]
+    gts = [torch.rand(3, 4, 6, generator=g) for _ in range(B)]
+    return cams, gts
+
+
+def _single_process_reference(B):
+    pc = _PC()
+    cams, gts = _batch(B)
+    bg = torch.ones(3)
+    outs = [_render(c, pc, bg)["render"] for c in cams]
+    loss = (torch.cat(outs, 0) - torch.cat(gts, 0)).abs().mean()       # the reference's l1_loss(cat, cat)
+    loss.backward()
+    return float(loss), pc.a.grad.clone(), pc.b.grad.clone()
+
+
+def _worker(rank, world, port, B, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        pc = _PC()
+        bucket = dp.GradBucket(pc.parameters(), extra={"viewspace": (37, 3)}, device="cpu")
+        assert pc.a.grad.data_ptr() == bucket.views[0].data_ptr()
+        cams, gts = _batch(B)
+        loss, radii = dp.train_iteration(_render, pc, cams, gts, torch.ones(3), bucket, rank=rank, world=world)
+        tot = loss.clone()
+        dist.all_reduce(tot)
+        q.put((rank, float(tot), pc.a.grad.clone(), pc.b.grad.clone(), bucket.extra["viewspace"].clone(),
+               int(radii.max()), bucket.nbytes()))
+    finally:
+        dist.destroy_process_group()
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def test_shard_views_rule():
+    assert dp.shard_views(8, 0, 1) == list(range(8))
+    assert dp.shard_views(8, 1, 2) == [1, 3, 5, 7]
+    assert dp.shard_views(8, 3, 4) == [3, 7]
+    assert dp.shard_views(8, 7, 8) == [7]
+    assert dp.shard_views(2, 3, 4) == []          # more ranks than views: the rank idles but still joins the reduce
+    assert sorted(sum((dp.shard_views(5, r, 3) for r in range(3)), [])) == list(range(5))
+
+
+def test_bucket_slots_are_the_grads_and_skip_frozen():
+    pc = _PC()
+    b = dp.GradBucket(pc.parameters(), extra={"viewspace": (37, 3)}, device="cpu")
+    assert len(b.params) == 2 and pc.frozen.grad is None
+    assert all(o % 64 == 0 for o in b.offsets)
+    (pc.a.sum() * 2 + pc.b.sum()).backward()
+    assert float(b.flat.sum()) == pytest.approx(2 * 37 * 3 + 5)
+    pc.a.grad = None                               # what optimizer.zero_grad(set_to_none=True) does
+    b.zero()
+    assert pc.a.grad.data_ptr() == b.views[0].data_ptr() and float(b.flat.abs().sum()) == 0.0
+    assert b.all_reduce() is None                  # no process group: no-op
+
+
+@pytest.mark.parametrize("B", [4, 3])
+def test_world2_gloo_matches_single_process(B):
+    ref_loss, ga, gb = _single_process_reference(B)
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, B, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=120) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    for rank, loss, a, b, vs, rmax, nbytes in res:
+        assert loss == pytest.approx(ref_loss, rel=1e-6)
+        assert torch.allclose(a, ga, rtol=1e-5, atol=1e-7) and torch.allclose(b, gb, rtol=1e-5, atol=1e-7)
+        assert nbytes == 4 * (128 + 64 + 128)      # 111 -> 128, 5 -> 64, 111 -> 128 floats
+    assert torch.equal(res[0][4], res[1][4])       # the view-space accumulator is reduced too
+    assert float(res[0][4].abs().sum()) > 0
