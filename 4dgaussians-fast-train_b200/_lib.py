@@ -95,6 +95,7 @@ class FdgsDeformBackward(C.Structure):
         ("d_head_w2", C.c_void_p * FDGS_NUM_HEADS), ("d_head_b2", C.c_void_p * FDGS_NUM_HEADS),
         ("packed_ws", C.c_void_p), ("trow_ws", C.c_void_p),
         ("ws", C.c_void_p), ("ws_bytes", C.c_size_t),
+        ("scratch", C.c_void_p), ("scratch_bytes", C.c_size_t),
         ("debug", C.c_int32),
     ]
 
@@ -120,6 +121,7 @@ SYMBOLS = {
     "fdgs_deform_wprep_bytes": (C.c_size_t, [C.POINTER(FdgsDeformNet)]),
     "fdgs_deform_forward": (C.c_int, [C.POINTER(FdgsDeformForward), C.c_void_p]),
     "fdgs_deform_backward_ws_bytes": (C.c_size_t, [C.POINTER(FdgsDeformNet)]),
+    "fdgs_deform_backward_scratch_bytes": (C.c_size_t, [C.POINTER(FdgsDeformNet), C.c_int]),
     "fdgs_deform_backward": (C.c_int, [C.POINTER(FdgsDeformBackward), C.c_void_p]),
 }
 

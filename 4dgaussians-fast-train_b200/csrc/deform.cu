@@ -25,6 +25,12 @@ size_t wprep_bytes(const fdgs_deform::Layout& lo);
 bool supported(const fdgs_deform::Layout& lo);
 int forward(const fdgs_deform::Layout& lo, const FdgsDeformForward* a, const float* packed, const float* trow, cudaStream_t stream);
 }
+namespace fdgs_deform_tc_bwd {
+bool supported(const fdgs_deform::Layout& lo);
+size_t scratch_bytes(const fdgs_deform::Layout& lo, int P);
+int backward(const fdgs_deform::Layout& lo, const FdgsDeformBackward* a, const float* packed, const float* trow, float* gpacked,
+             float* gtrow, cudaStream_t stream);
+}
 
 namespace {
 using namespace fdgs_deform;
@@ -633,6 +639,11 @@ size_t fdgs_deform_wprep_bytes(const FdgsDeformNet* net) {
 size_t fdgs_deform_backward_ws_bytes(const FdgsDeformNet* net) {
     return fdgs_deform_packed_bytes(net) + fdgs_deform_trow_bytes(net);
 }
+size_t fdgs_deform_backward_scratch_bytes(const FdgsDeformNet* net, int P) {
+    Layout lo;
+    if (!net || make_layout(*net, lo)) return 0;
+    return fdgs_deform_tc_bwd::scratch_bytes(lo, P);
+}
 
 int fdgs_deform_forward(const FdgsDeformForward* a, void* stream_) {
     if (!a) return FDGS_E_BADARG;
@@ -739,7 +750,10 @@ int fdgs_deform_backward(const FdgsDeformBackward* a, void* stream_) {
         if (((lo.head_mask >> h) & 1) && io.g[h] && (!gp.w1[h] || !gp.b1[h] || !gp.w2[h] || !gp.b2[h])) return FDGS_E_BADARG;
     const int ntiles = (a->P + TP - 1) / TP;
     const int grid = ntiles < sm_count() ? ntiles : sm_count();
-    if (lo.Wn == 128) {
+    if (a->precision != 2 && fdgs_deform_tc_bwd::supported(lo)) {
+        rc = fdgs_deform_tc_bwd::backward(lo, a, packed, trow, gpacked, gtrow, stream);
+        if (rc) return rc;
+    } else if (lo.Wn == 128) {
         const size_t sm = bwd_smem<128>(lo.F);
         if (sm > SMEM_MAX) return FDGS_E_SMEM;
         FDGS_CUDA(cudaFuncSetAttribute(k_deform_bwd<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));

@@ -1,0 +1,882 @@
+// Tensor-core (tcgen05 + TMEM) backward of the fused HexPlane sampler + deformation MLP for sm_100a.
+//
+// Two kernels per view, both 3xTF32 (FP32-accurate), exchanging FP32 activations through a caller-owned
+// scratch buffer in HBM (1.9 GB at P = 300k, Wn = 128, five heads: cheap against 6.5 TB/s):
+//
+//   k_deform_bwd_data   persistent CTA per SM, 128-point tiles, TMEM lane = point (same skeleton as the forward):
+//        feat = sample(planes)            -> S_F            h  = feat W0^T (A smem)     relu(h) -> S_H, smem (hi/lo)
+//        per head j: z = relu(h) W1_j^T (A smem) ; relu(z) -> S_RZ_j ; g_z = (g_o W2_j) [z>0] (CUDA cores) -> S_GZ_j
+//                    and hi/lo into TMEM ;  g_rh += g_z W1_j   (A from TMEM, B = W1_j^T chunks)
+//        g_h = g_rh [h>0] -> S_GH, TMEM ; g_feat = g_h W0 (A from TMEM) ; sampler backward (vector atomics) ; d_xyz
+//   k_deform_bwd_weights   split-K "A^T B over points" GEMMs on MN-major (swizzled tile32) operands:
+//        dW1_j = S_GZ_j^T S_H   db1_j = colsum S_GZ_j      dW2_j^T = S_RZ_j^T g_o_j   db2_j = colsum g_o_j
+//        dW0   = S_GH^T  S_F    db0   = colsum S_GH
+//     one CTA per (job, slice of points); FP32 rows are split hi/lo in registers on their way to shared memory;
+//     partial results are reduced into the caller's gradient buffers with red.global.add.
+//
+// Replaces autograd over scene/deformation.py:45-148 + scene/hexplane.py:73-183 (ATen grid_sampler_2d_backward,
+// addmm backward: ~400 launches per view in the reference).
+#include "deform_common.cuh"
+#include "umma.cuh"
+#include "prof.cuh"
+
+namespace fdgs_deform_tc_bwd {
+using namespace fdgs_deform;
+using namespace fdgs_umma;
+
+constexpr int KCH = 16;            // K columns per streamed weight chunk
+constexpr int NTHREADS = 320;      // 8 sampler/epilogue warps + producer + MMA
+constexpr int NEPI = 256;
+
+struct Plan {
+    int Wn, F, nheads;
+    int heads[FDGS_NUM_HEADS];     // active heads that received an upstream gradient
+    int nchunks_main;              // chunks of 32*Wn floats per tile (W0, then W1_j and W1_j^T per head)
+    int nchunks_gf;                // chunks of 32*F floats (W0^T)
+    long long wprep_floats;
+    // scratch (floats), Pp = ntiles * 128 rows each
+    long long Pp;
+    long long off_wprep, off_F, off_H, off_GH, off_RZ[FDGS_NUM_HEADS], off_GZ[FDGS_NUM_HEADS], total_floats;
+};
+
+static inline bool tc_supported(const Layout& lo) {
+    return lo.depth == 1 && (lo.Wn == 64 || lo.Wn == 128) && lo.F % KCH == 0 && lo.F >= KCH && lo.F <= 64 && lo.C >= 8;
+}
+
+static inline Plan make_plan(const Layout& lo, int P, const bool has_grad[FDGS_NUM_HEADS]) {
+    Plan p;
+    p.Wn = lo.Wn; p.F = lo.F; p.nheads = 0;
+    for (int h = 0; h < FDGS_NUM_HEADS; ++h) if (((lo.head_mask >> h) & 1) && has_grad[h]) p.heads[p.nheads++] = h;
+    for (int h = p.nheads; h < FDGS_NUM_HEADS; ++h) p.heads[h] = 0;
+    p.nchunks_main = lo.F / KCH + p.nheads * 2 * (lo.Wn / KCH);
+    p.nchunks_gf = lo.Wn / KCH;
+    p.wprep_floats = (long long)p.nchunks_main * 32 * lo.Wn + (long long)p.nchunks_gf * 32 * lo.F;
+    const long long ntiles = ((long long)P + TP - 1) / TP;
+    p.Pp = ntiles * TP;
+    auto al = [](long long x) { return (x + 63) & ~63LL; };
+    long long o = 0;
+    p.off_wprep = o; o += al(p.wprep_floats);
+    p.off_F = o;  o += al(p.Pp * lo.F);
+    p.off_H = o;  o += al(p.Pp * lo.Wn);
+    p.off_GH = o; o += al(p.Pp * lo.Wn);
+    for (int j = 0; j < FDGS_NUM_HEADS; ++j) {
+        p.off_RZ[j] = o; if (j < p.nheads) o += al(p.Pp * lo.Wn);
+        p.off_GZ[j] = o; if (j < p.nheads) o += al(p.Pp * lo.Wn);
+    }
+    p.total_floats = o;
+    return p;
+}
+
+// ---- weight formatting ----------------------------------------------------------------------------------------
+// A section is one [N rows][K] operand stored as K/16 chunks; a chunk = hi tile then lo tile, each the canonical
+// K-major tile [4 column groups][N][4] (umma.cuh).  element(n, k) = T ? W[k*ld + n] : W[n*ld + k].
+struct PrepSec { const float* W; int ld, N, K, T; long long off; };
+struct PrepArgs { PrepSec s[2 + 2 * FDGS_NUM_HEADS]; int nsec; };
+
+__global__ void k_deform_wprep_bwd(PrepArgs a, float* __restrict__ out) {
+    for (int si = 0; si < a.nsec; ++si) {
+        const PrepSec s = a.s[si];
+        const int total = s.N * s.K;
+        for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+            int n, k; float w;
+            if (s.T) { k = i / s.N; n = i % s.N; w = s.W[(size_t)k * s.ld + n]; }     // coalesced read either way
+            else     { n = i / s.K; k = i % s.K; w = s.W[(size_t)n * s.ld + k]; }
+            float hi, lo;
+            split_tf32_rn(w, hi, lo);
+            float* c = out + s.off + (long long)(k / KCH) * 32 * s.N;
+            const int o = tile_off(n, k % KCH, s.N);
+            c[o] = hi;
+            c[16 * s.N + o] = lo;
+        }
+    }
+}
+
+struct Net {
+    const float* wprep;
+    const float* b0;
+    const float* b1[FDGS_NUM_HEADS];
+    const float* w2[FDGS_NUM_HEADS];       // original [out][Wn]
+};
+
+struct IO {
+    int P;
+    const float* xyz;
+    const float* g[FDGS_NUM_HEADS];        // upstream grads [P][out]
+    float* d_xyz;
+    float *S_F, *S_H, *S_GH;
+    float* S_RZ[FDGS_NUM_HEADS];           // indexed by plan slot j
+    float* S_GZ[FDGS_NUM_HEADS];
+};
+
+struct Smem {
+    int slots;
+    int off_hs_hi, off_hs_lo, off_w2, off_b0, off_b1, off_red, off_bars, off_ring;
+    size_t bytes;
+};
+
+static inline Smem make_smem(const Layout& lo) {
+    Smem s;
+    auto al = [](int x) { return (x + 255) & ~255; };
+    const int Wn = lo.Wn;
+    int o = 0;
+    s.off_hs_hi = o; o += al(128 * Wn);        // relu(h) hi, K-major canonical tile; feat hi aliases its head
+    s.off_hs_lo = o; o += al(128 * Wn);
+    s.off_w2 = o; o += al(60 * Wn);            // 59 rows + 1 pad row (small heads read up to 4 rows)
+    s.off_b0 = o; o += al(Wn);
+    s.off_b1 = o; o += al(FDGS_NUM_HEADS * Wn);
+    s.off_red = o; o += al(2 * 128 * 3);
+    s.off_bars = o; o += 256;
+    s.off_ring = o;
+    const int slot_floats = 32 * Wn;
+    const int budget = (227 * 1024 - 1024) / 4 - o;
+    s.slots = budget / slot_floats;
+    if (s.slots > 8) s.slots = 8;
+    s.bytes = (size_t)(o + s.slots * slot_floats) * 4 + 1024;
+    return s;
+}
+
+__device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
+
+// TMEM column map (512 columns): accumulator (trunk h, head z, g_feat), g_z / g_h hi, lo, g_relu_h accumulator
+constexpr uint32_t TM_ACC = 0, TM_GHI = 128, TM_GLO = 256, TM_GRH = 384;
+constexpr int B_WFULL = 0, B_WEMPTY = 8, B_FEATFULL = 16, B_ACCFULL = 17, B_HFULL = 18, B_GZFULL = 19, B_GRHFULL = 20,
+              B_GHFULL = 21, B_GFFULL = 22, B_COUNT = 23;
+
+__device__ __forceinline__ int w2_row0(int h) { return h == 0 ? 0 : h == 1 ? 3 : h == 2 ? 6 : h == 3 ? 10 : 11; }
+
+// ---- sampler backward for 4 channels [c0, c0+4) of level l of one point -------------------------------------
+// df = dL/dfeat of those channels.  Recomputes the six bilinear samples, scatters dL/dplane with vector atomics
+// into the channel-last gradient planes / time rows, and accumulates dL/dq (normalised coordinates) into dq[3].
+__device__ __forceinline__ void sample_bwd4(const Layout& lo, int l, const float q[4], const float* __restrict__ packed,
+                                            const float* __restrict__ trow, float* __restrict__ gpacked,
+                                            float* __restrict__ gtrow, int c0, const float (&df)[4], float (&dq)[3]) {
+    const int C = lo.C;
+    float s[6][4], gx_c[6][4], gy_c[6][4], gmx[6], gmy[6];
+    int x0a[6], y0a[6];
+    float wx0a[6], wx1a[6], wy0a[6], wy1a[6];
+    bool xina[6], yina[6];
+    const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+    for (int k = 0; k < 6; ++k) {
+        const int a = pa_of(k);
+        const int W = lo.pw[l][k];
+        const float ix = unnorm_clip(q[a], W, &gmx[k]);
+        const float x0f = floorf(ix);
+        const int x0 = (int)x0f;
+        const float wx0 = (x0f + 1.f) - ix, wx1 = ix - x0f;
+        const bool xin = x0 + 1 < W;
+        x0a[k] = x0; wx0a[k] = wx0; wx1a[k] = wx1; xina[k] = xin;
+        if (k == 2 || k == 4 || k == 5) {
+            const float* T = trow + lo.toff[l][k == 2 ? 0 : (k == 4 ? 1 : 2)] + c0;
+            const float4 v0 = *reinterpret_cast<const float4*>(T + (size_t)x0 * C);
+            const float4 v1 = xin ? *reinterpret_cast<const float4*>(T + (size_t)(x0 + 1) * C) : z4;
+            const float a0[4] = {v0.x, v0.y, v0.z, v0.w}, a1[4] = {v1.x, v1.y, v1.z, v1.w};
+#pragma unroll
+            for (int c = 0; c < 4; ++c) { s[k][c] = a0[c] * wx0 + a1[c] * wx1; gx_c[k][c] = a1[c] - a0[c]; gy_c[k][c] = 0.f; }
+            gmy[k] = 0.f; y0a[k] = 0; wy0a[k] = 0.f; wy1a[k] = 0.f; yina[k] = false;
+        } else {
+            const int b = pb_of(k);
+            const int H = lo.ph[l][k];
+            const float iy = unnorm_clip(q[b], H, &gmy[k]);
+            const float y0f = floorf(iy);
+            const int y0 = (int)y0f;
+            const float wy0 = (y0f + 1.f) - iy, wy1 = iy - y0f;
+            const bool yin = y0 + 1 < H;
+            y0a[k] = y0; wy0a[k] = wy0; wy1a[k] = wy1; yina[k] = yin;
+            const float* Pp = packed + lo.poff[l][k] + c0;
+            const size_t o00 = ((size_t)y0 * W + x0) * C;
+            const float4 v00 = *reinterpret_cast<const float4*>(Pp + o00);
+            const float4 v01 = xin ? *reinterpret_cast<const float4*>(Pp + o00 + C) : z4;
+            const float4 v10 = yin ? *reinterpret_cast<const float4*>(Pp + o00 + (size_t)W * C) : z4;
+            const float4 v11 = (xin && yin) ? *reinterpret_cast<const float4*>(Pp + o00 + (size_t)W * C + C) : z4;
+            const float a00[4] = {v00.x, v00.y, v00.z, v00.w}, a01[4] = {v01.x, v01.y, v01.z, v01.w};
+            const float a10[4] = {v10.x, v10.y, v10.z, v10.w}, a11[4] = {v11.x, v11.y, v11.z, v11.w};
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                s[k][c] = a00[c] * (wx0 * wy0) + a01[c] * (wx1 * wy0) + a10[c] * (wx0 * wy1) + a11[c] * (wx1 * wy1);
+                gx_c[k][c] = (a01[c] - a00[c]) * wy0 + (a11[c] - a10[c]) * wy1;
+                gy_c[k][c] = (a10[c] - a00[c]) * wx0 + (a11[c] - a01[c]) * wx1;
+            }
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < 6; ++k) {
+        float ds[4];
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            float pr = df[c];
+#pragma unroll
+            for (int j = 0; j < 6; ++j) if (j != k) pr *= s[j][c];
+            ds[c] = pr;
+        }
+        float gx = 0.f, gy = 0.f;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) { gx += ds[c] * gx_c[k][c]; gy += ds[c] * gy_c[k][c]; }
+        dq[pa_of(k)] += gx * gmx[k];
+        if (!(k == 2 || k == 4 || k == 5)) dq[pb_of(k)] += gy * gmy[k];
+        const int W = lo.pw[l][k];
+        if (k == 2 || k == 4 || k == 5) {
+            float* T = gtrow + lo.toff[l][k == 2 ? 0 : (k == 4 ? 1 : 2)] + c0;
+            atomicAdd(reinterpret_cast<float4*>(T + (size_t)x0a[k] * C),
+                      make_float4(ds[0] * wx0a[k], ds[1] * wx0a[k], ds[2] * wx0a[k], ds[3] * wx0a[k]));
+            if (xina[k])
+                atomicAdd(reinterpret_cast<float4*>(T + (size_t)(x0a[k] + 1) * C),
+                          make_float4(ds[0] * wx1a[k], ds[1] * wx1a[k], ds[2] * wx1a[k], ds[3] * wx1a[k]));
+        } else {
+            float* Gp = gpacked + lo.poff[l][k] + c0;
+            const size_t o00 = ((size_t)y0a[k] * W + x0a[k]) * C;
+            const float nw = wx0a[k] * wy0a[k], ne = wx1a[k] * wy0a[k], sw = wx0a[k] * wy1a[k], se = wx1a[k] * wy1a[k];
+            atomicAdd(reinterpret_cast<float4*>(Gp + o00), make_float4(ds[0] * nw, ds[1] * nw, ds[2] * nw, ds[3] * nw));
+            if (xina[k])
+                atomicAdd(reinterpret_cast<float4*>(Gp + o00 + C), make_float4(ds[0] * ne, ds[1] * ne, ds[2] * ne, ds[3] * ne));
+            if (yina[k])
+                atomicAdd(reinterpret_cast<float4*>(Gp + o00 + (size_t)W * C), make_float4(ds[0] * sw, ds[1] * sw, ds[2] * sw, ds[3] * sw));
+            if (xina[k] && yina[k])
+                atomicAdd(reinterpret_cast<float4*>(Gp + o00 + (size_t)W * C + C), make_float4(ds[0] * se, ds[1] * se, ds[2] * se, ds[3] * se));
+        }
+    }
+}
+
+// ---- head epilogue: z = relu(acc + b1); g_z = (g_o W2)[z > 0]; scratch stores; g_z hi/lo -> TMEM ---------------------
+// NOP = compile-time bound on the head's output width (4 for dx/ds/dr/do, 48 for dshs); NH = columns per thread.
+template <int NOP, int NH, int WN>
+__device__ __forceinline__ void head_epilogue(uint32_t lane_base, int col0, int NO, bool valid, const float* __restrict__ gsrc,
+                                              const float* __restrict__ b1s, const float* __restrict__ w2s,
+                                              float* __restrict__ rz_row, float* __restrict__ gz_row) {
+    float go[NOP];
+#pragma unroll
+    for (int o = 0; o < NOP; ++o) go[o] = 0.f;
+    if (valid) {
+        if (NOP == 48) {
+#pragma unroll
+            for (int o = 0; o < 48; o += 4) {
+                const float4 v = *reinterpret_cast<const float4*>(gsrc + o);
+                go[o] = v.x; go[o + 1] = v.y; go[o + 2] = v.z; go[o + 3] = v.w;
+            }
+        } else {
+#pragma unroll
+            for (int o = 0; o < NOP; ++o) if (o < NO) go[o] = gsrc[o];
+        }
+    }
+#pragma unroll 1
+    for (int c0 = 0; c0 < NH; c0 += 16) {
+        uint32_t v[16];
+        tmem_ld16(lane_base + TM_ACC + col0 + c0, v);
+        tmem_wait_ld();
+        float z[16], gr[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) { z[j] = fmaxf(__uint_as_float(v[j]) + b1s[col0 + c0 + j], 0.f); gr[j] = 0.f; }
+#pragma unroll
+        for (int o = 0; o < NOP; ++o) {
+            const float g = go[o];
+            const float* w = w2s + o * WN + col0 + c0;
+#pragma unroll
+            for (int j = 0; j < 16; j += 4) {
+                const float4 w4 = *reinterpret_cast<const float4*>(w + j);
+                gr[j] = fmaf(g, w4.x, gr[j]); gr[j + 1] = fmaf(g, w4.y, gr[j + 1]);
+                gr[j + 2] = fmaf(g, w4.z, gr[j + 2]); gr[j + 3] = fmaf(g, w4.w, gr[j + 3]);
+            }
+        }
+        uint32_t hi[16], lw[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+            gr[j] = z[j] > 0.f ? gr[j] : 0.f;
+            float a, b;
+            split_tf32_rn(gr[j], a, b);
+            hi[j] = __float_as_uint(a); lw[j] = __float_as_uint(b);
+        }
+#pragma unroll
+        for (int j = 0; j < 16; j += 4) {
+            *reinterpret_cast<float4*>(rz_row + col0 + c0 + j) = make_float4(z[j], z[j + 1], z[j + 2], z[j + 3]);
+            *reinterpret_cast<float4*>(gz_row + col0 + c0 + j) = make_float4(gr[j], gr[j + 1], gr[j + 2], gr[j + 3]);
+        }
+        tmem_st16(lane_base + TM_GHI + col0 + c0, hi);
+        tmem_st16(lane_base + TM_GLO + col0 + c0, lw);
+    }
+    tmem_wait_st();
+}
+
+// =====================================================================================================================
+template <int WN>
+__global__ void __launch_bounds__(NTHREADS, 1)
+k_deform_bwd_data(Layout lo, Plan plan, Smem sp, Net net, IO io, const float* __restrict__ packed,
+                  const float* __restrict__ trow, float* __restrict__ gpacked, float* __restrict__ gtrow, int ntiles)
+{
+    extern __shared__ uint8_t smem_raw[];
+    float* sm = reinterpret_cast<float*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    float* HS_hi = sm + sp.off_hs_hi;
+    float* HS_lo = sm + sp.off_hs_lo;
+    float* F_hi = HS_hi;                       // the feat tile lives in the head of the relu(h) buffers
+    float* F_lo = HS_lo;
+    float* W2s = sm + sp.off_w2;
+    float* B0s = sm + sp.off_b0;
+    float* B1s = sm + sp.off_b1;
+    float* red = sm + sp.off_red;
+    float* ring = sm + sp.off_ring;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(sm + sp.off_bars);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + B_COUNT + 2);
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int S = sp.slots;
+    constexpr int NH = WN / 2;
+    constexpr int SLOT = 32 * WN;
+    const int F = lo.F;
+
+    if (tid == 0) {
+        for (int i = 0; i < B_COUNT; ++i) mbar_init(&bars[i], 1);
+        fence_mbar_init();
+    }
+    if (warp == 9) tmem_alloc(tmem_slot, 512);
+    if (tid < NEPI) {
+        for (int i = tid; i < 60 * WN; i += NEPI) W2s[i] = 0.f;
+        for (int i = tid; i < WN; i += NEPI) B0s[i] = net.b0[i];
+    }
+    __syncthreads();
+    if (tid < NEPI) {
+        for (int j = 0; j < plan.nheads; ++j) {
+            const int h = plan.heads[j];
+            const int NO = head_out(h);
+            for (int i = tid; i < WN; i += NEPI) B1s[h * WN + i] = net.b1[h][i];
+            for (int i = tid; i < NO * WN; i += NEPI) W2s[w2_row0(h) * WN + i] = net.w2[h][i];
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_slot;
+
+    if (warp == 8) {
+        // ===== producer: the same chunk sequence for every tile ===========================================
+        if (lane == 0) {
+            uint32_t g = 0;
+            const int nch = plan.nchunks_main + plan.nchunks_gf;
+            for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x)
+                for (int c = 0; c < nch; ++c, ++g) {
+                    const uint32_t slot = g % S;
+                    const bool gf = c >= plan.nchunks_main;
+                    const uint32_t bytes = (gf ? 32 * F : SLOT) * 4;
+                    const float* src = net.wprep + (gf ? (size_t)plan.nchunks_main * SLOT + (size_t)(c - plan.nchunks_main) * 32 * F
+                                                       : (size_t)c * SLOT);
+                    mbar_wait(&bars[B_WEMPTY + slot], ((g / S) & 1) ^ 1);
+                    mbar_expect_tx(&bars[B_WFULL + slot], bytes);
+                    bulk_g2s(ring + (size_t)slot * SLOT, src, bytes, &bars[B_WFULL + slot]);
+                }
+        }
+        __syncwarp();
+    } else if (warp == 9) {
+        // ===== MMA issuer ===================================================================================
+        if (lane == 0) {
+            const uint32_t idesc = make_idesc_tf32(128, WN, 0, 0);
+            const uint32_t idesc_gf = make_idesc_tf32(128, F, 0, 0);
+            uint32_t g = 0, ph_feat = 0, ph_h = 0, ph_gz = 0, ph_gh = 0;
+            for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+                // trunk: ACC = feat . W0^T
+                mbar_wait(&bars[B_FEATFULL], ph_feat); ph_feat ^= 1;
+                tc_fence_after();
+                for (int c = 0; c < F / KCH; ++c, ++g) {
+                    const uint32_t slot = g % S;
+                    mbar_wait(&bars[B_WFULL + slot], (g / S) & 1);
+                    tc_fence_after();
+                    const float* bh = ring + (size_t)slot * SLOT;
+                    const float* bl = bh + 16 * WN;
+#pragma unroll
+                    for (int ks = 0; ks < 2; ++ks) {
+                        const int k = c * KCH + ks * 8;
+                        const int first = (c == 0 && ks == 0) ? 0 : 1;
+                        mma_tf32_ss(tmem + TM_ACC, desc_kmajor(F_lo, 128, k), desc_kmajor(bh, WN, ks * 8), idesc, first);
+                        mma_tf32_ss(tmem + TM_ACC, desc_kmajor(F_hi, 128, k), desc_kmajor(bl, WN, ks * 8), idesc, 1);
+                        mma_tf32_ss(tmem + TM_ACC, desc_kmajor(F_hi, 128, k), desc_kmajor(bh, WN, ks * 8), idesc, 1);
+                    }
+                    mma_commit(&bars[B_WEMPTY + slot]);
+                }
+                mma_commit(&bars[B_ACCFULL]);
+                mbar_wait(&bars[B_HFULL], ph_h); ph_h ^= 1;
+                tc_fence_after();
+                for (int i = 0; i < plan.nheads; ++i) {
+                    // z_i: ACC = relu(h) . W1^T      (A from shared memory)
+                    for (int c = 0; c < WN / KCH; ++c, ++g) {
+                        const uint32_t slot = g % S;
+                        mbar_wait(&bars[B_WFULL + slot], (g / S) & 1);
+                        tc_fence_after();
+                        const float* bh = ring + (size_t)slot * SLOT;
+                        const float* bl = bh + 16 * WN;
+#pragma unroll
+                        for (int ks = 0; ks < 2; ++ks) {
+                            const int k = c * KCH + ks * 8;
+                            const int first = (c == 0 && ks == 0) ? 0 : 1;
+                            mma_tf32_ss(tmem + TM_ACC, desc_kmajor(HS_lo, 128, k), desc_kmajor(bh, WN, ks * 8), idesc, first);
+                            mma_tf32_ss(tmem + TM_ACC, desc_kmajor(HS_hi, 128, k), desc_kmajor(bl, WN, ks * 8), idesc, 1);
+                            mma_tf32_ss(tmem + TM_ACC, desc_kmajor(HS_hi, 128, k), desc_kmajor(bh, WN, ks * 8), idesc, 1);
+                        }
+                        mma_commit(&bars[B_WEMPTY + slot]);
+                    }
+                    mma_commit(&bars[B_ACCFULL]);
+                    // g_relu_h += g_z . W1          (A from TMEM, B = W1^T chunks)
+                    mbar_wait(&bars[B_GZFULL], ph_gz); ph_gz ^= 1;
+                    tc_fence_after();
+                    for (int c = 0; c < WN / KCH; ++c, ++g) {
+                        const uint32_t slot = g % S;
+                        mbar_wait(&bars[B_WFULL + slot], (g / S) & 1);
+                        tc_fence_after();
+                        const float* bh = ring + (size_t)slot * SLOT;
+                        const float* bl = bh + 16 * WN;
+#pragma unroll
+                        for (int ks = 0; ks < 2; ++ks) {
+                            const uint32_t k = (uint32_t)(c * KCH + ks * 8);
+                            const int first = (i == 0 && c == 0 && ks == 0) ? 0 : 1;
+                            mma_tf32_ts(tmem + TM_GRH, tmem + TM_GLO + k, desc_kmajor(bh, WN, ks * 8), idesc, first);
+                            mma_tf32_ts(tmem + TM_GRH, tmem + TM_GHI + k, desc_kmajor(bl, WN, ks * 8), idesc, 1);
+                            mma_tf32_ts(tmem + TM_GRH, tmem + TM_GHI + k, desc_kmajor(bh, WN, ks * 8), idesc, 1);
+                        }
+                        mma_commit(&bars[B_WEMPTY + slot]);
+                    }
+                }
+                mma_commit(&bars[B_GRHFULL]);
+                // g_feat: ACC[0, F) = g_h . W0       (A from TMEM, B = W0^T chunks, N = F)
+                mbar_wait(&bars[B_GHFULL], ph_gh); ph_gh ^= 1;
+                tc_fence_after();
+                for (int c = 0; c < WN / KCH; ++c, ++g) {
+                    const uint32_t slot = g % S;
+                    mbar_wait(&bars[B_WFULL + slot], (g / S) & 1);
+                    tc_fence_after();
+                    const float* bh = ring + (size_t)slot * SLOT;
+                    const float* bl = bh + 16 * F;
+#pragma unroll
+                    for (int ks = 0; ks < 2; ++ks) {
+                        const uint32_t k = (uint32_t)(c * KCH + ks * 8);
+                        const int first = (c == 0 && ks == 0) ? 0 : 1;
+                        mma_tf32_ts(tmem + TM_ACC, tmem + TM_GLO + k, desc_kmajor(bh, F, ks * 8), idesc_gf, first);
+                        mma_tf32_ts(tmem + TM_ACC, tmem + TM_GHI + k, desc_kmajor(bl, F, ks * 8), idesc_gf, 1);
+                        mma_tf32_ts(tmem + TM_ACC, tmem + TM_GHI + k, desc_kmajor(bh, F, ks * 8), idesc_gf, 1);
+                    }
+                    mma_commit(&bars[B_WEMPTY + slot]);
+                }
+                mma_commit(&bars[B_GFFULL]);
+            }
+        }
+        __syncwarp();
+    } else {
+        // ===== sampler + epilogues: thread = point row `row`, column half `hf` ==========================
+        const int row = tid & 127, hf = tid >> 7;
+        const uint32_t lane_base = tmem + ((uint32_t)((warp & 3) * 32) << 16);
+        const int col0 = hf * NH;
+        uint32_t ph_acc = 0, ph_grh = 0, ph_gf = 0;
+        const int C = lo.C, CH = C >> 1;
+        for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+            const int p = tile * TP + row;
+            const bool valid = p < io.P;
+            float q[4] = {0.f, 0.f, 0.f, 0.f};
+            if (valid) point_coords(lo, io.xyz, p, 0.f, q);
+            // ---- HexPlane sampling -> feat tile (hi / lo) + scratch ----------------------------------------
+            for (int l = 0; l < lo.L; ++l)
+                for (int cc = 0; cc < CH; cc += 4) {
+                    const int c0 = hf * CH + cc;
+                    float prod[4] = {0.f, 0.f, 0.f, 0.f};
+                    if (valid) sample_level<4>(lo, l, q, packed, trow, c0, prod);
+                    float4 hi, lw;
+                    split_tf32_rn(prod[0], hi.x, lw.x); split_tf32_rn(prod[1], hi.y, lw.y);
+                    split_tf32_rn(prod[2], hi.z, lw.z); split_tf32_rn(prod[3], hi.w, lw.w);
+                    const int o = tile_off(row, l * C + c0, 128);
+                    *reinterpret_cast<float4*>(F_hi + o) = hi;
+                    *reinterpret_cast<float4*>(F_lo + o) = lw;
+                    *reinterpret_cast<float4*>(io.S_F + (size_t)p * F + l * C + c0) = make_float4(prod[0], prod[1], prod[2], prod[3]);
+                }
+            fence_async_smem();
+            epi_bar();
+            if (tid == 0) mbar_arrive(&bars[B_FEATFULL]);
+
+            // ---- trunk epilogue: relu(h + b0) -> scratch, shared memory hi / lo; gate bits kept in registers ------
+            mbar_wait(&bars[B_ACCFULL], ph_acc); ph_acc ^= 1;
+            tc_fence_after();
+            uint32_t gate[NH / 32];
+#pragma unroll
+            for (int c0 = 0; c0 < NH; c0 += 32) {
+                uint32_t v[32];
+                tmem_ld32(lane_base + TM_ACC + col0 + c0, v);
+                tmem_wait_ld();
+                uint32_t m = 0;
+#pragma unroll
+                for (int j = 0; j < 32; j += 4) {
+                    float x[4], a[4], b[4];
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        x[u] = fmaxf(__uint_as_float(v[j + u]) + B0s[col0 + c0 + j + u], 0.f);
+                        m |= (x[u] > 0.f ? 1u : 0u) << (j + u);
+                        split_tf32_rn(x[u], a[u], b[u]);
+                    }
+                    const int o = tile_off(row, col0 + c0 + j, 128);
+                    *reinterpret_cast<float4*>(HS_hi + o) = make_float4(a[0], a[1], a[2], a[3]);
+                    *reinterpret_cast<float4*>(HS_lo + o) = make_float4(b[0], b[1], b[2], b[3]);
+                    *reinterpret_cast<float4*>(io.S_H + (size_t)p * WN + col0 + c0 + j) = make_float4(x[0], x[1], x[2], x[3]);
+                }
+                gate[c0 / 32] = m;
+            }
+            fence_async_smem();
+            tc_fence_before();
+            epi_bar();
+            if (tid == 0) mbar_arrive(&bars[B_HFULL]);
+
+            // ---- heads ---------------------------------------------------------------------------------------------
+            for (int i = 0; i < plan.nheads; ++i) {
+                const int h = plan.heads[i];
+                const int NO = head_out(h);
+                mbar_wait(&bars[B_ACCFULL], ph_acc); ph_acc ^= 1;
+                tc_fence_after();
+                const float* gsrc = io.g[h] + (size_t)(valid ? p : 0) * NO;
+                float* rz_row = io.S_RZ[i] + (size_t)p * WN;
+                float* gz_row = io.S_GZ[i] + (size_t)p * WN;
+                if (h == FDGS_HEAD_SHS)
+                    head_epilogue<48, NH, WN>(lane_base, col0, NO, valid, gsrc, B1s + h * WN, W2s + w2_row0(h) * WN, rz_row, gz_row);
+                else
+                    head_epilogue<4, NH, WN>(lane_base, col0, NO, valid, gsrc, B1s + h * WN, W2s + w2_row0(h) * WN, rz_row, gz_row);
+                tc_fence_before();
+                epi_bar();
+                if (tid == 0) mbar_arrive(&bars[B_GZFULL]);
+            }
+
+            // ---- g_h = g_relu_h [h > 0] -> scratch, TMEM hi / lo -----------------------------------------------------
+            mbar_wait(&bars[B_GRHFULL], ph_grh); ph_grh ^= 1;
+            tc_fence_after();
+#pragma unroll
+            for (int c0 = 0; c0 < NH; c0 += 16) {
+                uint32_t v[16], hi[16], lw[16];
+                tmem_ld16(lane_base + TM_GRH + col0 + c0, v);
+                tmem_wait_ld();
+                const uint32_t m = gate[c0 / 32] >> (c0 & 31);
+                float gh[16];
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                    gh[j] = ((m >> j) & 1u) ? __uint_as_float(v[j]) : 0.f;
+                    float a, b;
+                    split_tf32_rn(gh[j], a, b);
+                    hi[j] = __float_as_uint(a); lw[j] = __float_as_uint(b);
+                }
+#pragma unroll
+                for (int j = 0; j < 16; j += 4)
+                    *reinterpret_cast<float4*>(io.S_GH + (size_t)p * WN + col0 + c0 + j) = make_float4(gh[j], gh[j + 1], gh[j + 2], gh[j + 3]);
+                tmem_st16(lane_base + TM_GHI + col0 + c0, hi);
+                tmem_st16(lane_base + TM_GLO + col0 + c0, lw);
+            }
+            tmem_wait_st();
+            tc_fence_before();
+            epi_bar();
+            if (tid == 0) mbar_arrive(&bars[B_GHFULL]);
+
+            // ---- g_feat -> sampler backward -----------------------------------------------------------------------------
+            mbar_wait(&bars[B_GFFULL], ph_gf); ph_gf ^= 1;
+            tc_fence_after();
+            float dq[3] = {0.f, 0.f, 0.f};
+            for (int l = 0; l < lo.L; ++l)
+                for (int cc = 0; cc < CH; cc += 4) {
+                    const int c0 = hf * CH + cc;
+                    uint32_t v[4];
+                    tmem_ld4(lane_base + TM_ACC + (uint32_t)(l * C + c0), v);      // warp-uniform address: all lanes execute
+                    tmem_wait_ld();
+                    const float df[4] = {__uint_as_float(v[0]), __uint_as_float(v[1]), __uint_as_float(v[2]), __uint_as_float(v[3])};
+                    if (valid) sample_bwd4(lo, l, q, packed, trow, gpacked, gtrow, c0, df, dq);
+                }
+            red[(hf * TP + row) * 3 + 0] = dq[0];
+            red[(hf * TP + row) * 3 + 1] = dq[1];
+            red[(hf * TP + row) * 3 + 2] = dq[2];
+            tc_fence_before();
+            epi_bar();
+            if (hf == 0 && valid) {
+#pragma unroll
+                for (int a = 0; a < 3; ++a) {
+                    const float mx = lo.aabb[a], mn = lo.aabb[3 + a];
+                    io.d_xyz[3 * (size_t)p + a] = (red[row * 3 + a] + red[(TP + row) * 3 + a]) * (2.0f / (mn - mx));
+                }
+            }
+            epi_bar();          // `red` and the feat/relu(h) buffers are free again
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    if (warp == 9) tmem_free(tmem, 512);
+}
+
+// =====================================================================================================================
+// Weight gradients: C[m][n] (+)= sum_p A[p][m] * B[p][n]   (M = 128 zero-padded, N = nb rounded up to 16)
+struct WJob {
+    const float* A; int lda, ma, rowsA;      // A [rowsA valid rows][lda]; columns >= ma read as 0
+    const float* B; int ldb, nb, rowsB;
+    float* C; int ldc, transposed;           // transposed: C[n * ldc + m]
+    float* biasA;                            // += column sums of A [ma]   (or null)
+    float* biasB;                            // += column sums of B [nb]   (or null)
+    int slices;                              // CTAs sharing this job
+};
+constexpr int MAXJOBS = 2 * FDGS_NUM_HEADS + 1;
+struct WArgs { WJob j[MAXJOBS]; int njobs; long long rows; };   // rows = Pp (multiple of 128)
+
+constexpr int WK = 32;             // points per stage
+constexpr int WSTAGES = 3;
+constexpr int W_THREADS = 288;     // 8 staging/epilogue warps + MMA warp
+constexpr int WB_FULL = 0, WB_EMPTY = 4, WB_DONE = 8;
+
+__device__ __forceinline__ float4 load4(const float* __restrict__ base, int ld, long long r, int c, int ncols, long long nrows) {
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (r >= nrows || c >= ncols) return v;
+    const float* p = base + (size_t)r * ld + c;
+    if ((ld & 3) == 0 && c + 3 < ncols) return *reinterpret_cast<const float4*>(p);
+    v.x = p[0];
+    if (c + 1 < ncols) v.y = p[1];
+    if (c + 2 < ncols) v.z = p[2];
+    if (c + 3 < ncols) v.w = p[3];
+    return v;
+}
+
+__global__ void __launch_bounds__(W_THREADS, 1)
+k_deform_bwd_weights(WArgs args)
+{
+    extern __shared__ uint8_t smem_raw[];
+    float* sm = reinterpret_cast<float*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    __shared__ __align__(8) uint64_t bars[12];
+    __shared__ uint32_t tmem_slot;
+    __shared__ float csumA[128], csumB[128];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    // which job / slice am I
+    int jb = 0, first = 0;
+    for (; jb < args.njobs; ++jb) { if ((int)blockIdx.x < first + args.j[jb].slices) break; first += args.j[jb].slices; }
+    if (jb >= args.njobs) return;
+    const WJob J = args.j[jb];
+    const int slice = blockIdx.x - first;
+    const long long nst = args.rows / WK;                         // stages in the whole point range
+    const long long s_begin = nst * slice / J.slices, s_end = nst * (slice + 1) / J.slices;
+    const int N16 = (J.nb + 15) & ~15;
+    const int nblkB = (J.nb + 31) >> 5;                           // 32-column blocks of B actually staged
+    // stage layout (floats): A_hi[4][32][32], A_lo, B_hi[nblkB][32][32], B_lo
+    const int stage_floats = 2 * 4096 + 2 * nblkB * 1024;
+
+    if (tid == 0) {
+        for (int i = 0; i < 12; ++i) mbar_init(&bars[i], i >= WB_FULL && i < WB_FULL + WSTAGES ? 8 : 1);
+        fence_mbar_init();
+    }
+    if (tid < 128) { csumA[tid] = 0.f; csumB[tid] = 0.f; }
+    if (warp == 8) tmem_alloc(&tmem_slot, 128);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = tmem_slot;
+
+    if (warp == 8) {
+        if (lane == 0) {
+            const uint32_t idesc = make_idesc_tf32(128, N16, 1, 1);
+            uint32_t g = 0;
+            for (long long s = s_begin; s < s_end; ++s, ++g) {
+                const uint32_t slot = g % WSTAGES;
+                mbar_wait(&bars[WB_FULL + slot], (g / WSTAGES) & 1);
+                tc_fence_after();
+                const float* Ah = sm + (size_t)slot * stage_floats;
+                const float* Al = Ah + 4096;
+                const float* Bh = Al + 4096;
+                const float* Bl = Bh + nblkB * 1024;
+#pragma unroll
+                for (int p = 0; p < WK; p += 8) {
+                    const int acc = (g == 0 && p == 0) ? 0 : 1;
+                    mma_tf32_ss(tmem, desc_mn32(Al, WK, p, 0), desc_mn32(Bh, WK, p, 0), idesc, acc);
+                    mma_tf32_ss(tmem, desc_mn32(Ah, WK, p, 0), desc_mn32(Bl, WK, p, 0), idesc, 1);
+                    mma_tf32_ss(tmem, desc_mn32(Ah, WK, p, 0), desc_mn32(Bh, WK, p, 0), idesc, 1);
+                }
+                mma_commit(&bars[WB_EMPTY + slot]);
+            }
+            mma_commit(&bars[WB_DONE]);
+        }
+        __syncwarp();
+    } else {
+        // ---- staging: thread owns float4 column group cgA of A (rows rA + 8 i) and cgB of B ----------------
+        const int cgA = tid & 31, rA = tid >> 5;
+        const int gpr = nblkB * 8;                                 // float4 groups per B row (8, 16 or 32)
+        const int cgB = tid % gpr, rB = tid / gpr, rstepB = 256 / gpr;
+        float sa[4] = {0.f, 0.f, 0.f, 0.f}, sb[4] = {0.f, 0.f, 0.f, 0.f};
+        uint32_t g = 0;
+        for (long long s = s_begin; s < s_end; ++s, ++g) {
+            const uint32_t slot = g % WSTAGES;
+            const long long r0 = s * WK;
+            float4 va[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) va[i] = load4(J.A, J.lda, r0 + rA + 8 * i, cgA * 4, J.ma, J.rowsA);
+            mbar_wait(&bars[WB_EMPTY + slot], ((g / WSTAGES) & 1) ^ 1);
+            float* Ah = sm + (size_t)slot * stage_floats;
+            float* Al = Ah + 4096;
+            float* Bh = Al + 4096;
+            float* Bl = Bh + nblkB * 1024;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int r = rA + 8 * i;
+                float4 hi, lw;
+                split_tf32_rn(va[i].x, hi.x, lw.x); split_tf32_rn(va[i].y, hi.y, lw.y);
+                split_tf32_rn(va[i].z, hi.z, lw.z); split_tf32_rn(va[i].w, hi.w, lw.w);
+                sa[0] += va[i].x; sa[1] += va[i].y; sa[2] += va[i].z; sa[3] += va[i].w;
+                const int o = tile32_off(r, cgA * 4, WK);
+                *reinterpret_cast<float4*>(Ah + o) = hi;
+                *reinterpret_cast<float4*>(Al + o) = lw;
+            }
+            for (int r = rB; r < WK; r += rstepB) {
+                const float4 v = load4(J.B, J.ldb, r0 + r, cgB * 4, J.nb, J.rowsB);
+                float4 hi, lw;
+                split_tf32_rn(v.x, hi.x, lw.x); split_tf32_rn(v.y, hi.y, lw.y);
+                split_tf32_rn(v.z, hi.z, lw.z); split_tf32_rn(v.w, hi.w, lw.w);
+                sb[0] += v.x; sb[1] += v.y; sb[2] += v.z; sb[3] += v.w;
+                const int o = tile32_off(r, cgB * 4, WK);
+                *reinterpret_cast<float4*>(Bh + o) = hi;
+                *reinterpret_cast<float4*>(Bl + o) = lw;
+            }
+            fence_async_smem();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&bars[WB_FULL + slot]);
+        }
+        // ---- bias gradients ------------------------------------------------------------------------------------
+        if (J.biasA) {
+#pragma unroll
+            for (int u = 0; u < 4; ++u) atomicAdd(&csumA[cgA * 4 + u], sa[u]);
+        }
+        if (J.biasB) {
+#pragma unroll
+            for (int u = 0; u < 4; ++u) if (cgB * 4 + u < 128) atomicAdd(&csumB[cgB * 4 + u], sb[u]);
+        }
+        asm volatile("bar.sync 1, 256;" ::: "memory");
+        if (tid < 128) {
+            if (J.biasA && tid < J.ma) atomicAdd(&J.biasA[tid], csumA[tid]);
+            if (J.biasB && tid < J.nb) atomicAdd(&J.biasB[tid], csumB[tid]);
+        }
+        // ---- accumulator -> global (+=) ----------------------------------------------------------------------------
+        mbar_wait(&bars[WB_DONE], 0);
+        tc_fence_after();
+        if (s_end > s_begin) {
+            const int m = (warp & 3) * 32 + lane;
+            const uint32_t lane_base = tmem + ((uint32_t)((warp & 3) * 32) << 16);
+            const int half = N16 / 2 >= 8 ? ((N16 / 2 + 7) & ~7) : 8;
+            const int nb0 = (warp >> 2) ? half : 0, nb1 = (warp >> 2) ? N16 : (half < N16 ? half : N16);
+            for (int c0 = nb0; c0 < nb1; c0 += 8) {
+                uint32_t v[8];
+                tmem_ld8(lane_base + c0, v);
+                tmem_wait_ld();
+                if (m < J.ma) {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        const int n = c0 + j;
+                        if (n < J.nb) atomicAdd(J.transposed ? &J.C[(size_t)n * J.ldc + m] : &J.C[(size_t)m * J.ldc + n], __uint_as_float(v[j]));
+                    }
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    if (warp == 8) tmem_free(tmem, 128);
+}
+
+// =====================================================================================================================
+static int sm_count() {
+    static int n = 0;
+    if (!n) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev); if (n <= 0) n = 148; }
+    return n;
+}
+
+bool supported(const Layout& lo) { return tc_supported(lo); }
+
+size_t scratch_bytes(const Layout& lo, int P) {
+    if (!tc_supported(lo) || P <= 0) return 0;
+    bool all[FDGS_NUM_HEADS] = {true, true, true, true, true};
+    const Plan p = make_plan(lo, P, all);
+    return fdgs_align_up(sizeof(float) * (size_t)p.total_floats);
+}
+
+// gpacked / gtrow: zeroed channel-last plane-gradient scratch (as in the CUDA-core path).
+int backward(const Layout& lo, const FdgsDeformBackward* a, const float* packed, const float* trow, float* gpacked, float* gtrow,
+             cudaStream_t stream) {
+    const float* gsrc[FDGS_NUM_HEADS] = {a->g_xyz, a->g_scales, a->g_rotations, a->g_opacity, a->g_shs};
+    bool has[FDGS_NUM_HEADS];
+    for (int h = 0; h < FDGS_NUM_HEADS; ++h) has[h] = gsrc[h] != nullptr;
+    const Plan plan = make_plan(lo, a->P, has);
+    if (plan.nheads == 0) {
+        FDGS_CUDA(cudaMemsetAsync(a->d_xyz_grid, 0, sizeof(float) * 3 * (size_t)a->P, stream));
+        return FDGS_OK;
+    }
+    if (!a->scratch || a->scratch_bytes < sizeof(float) * (size_t)plan.total_floats) return FDGS_E_WORKSPACE;
+    const Smem sp = make_smem(lo);
+    if (sp.slots < 3) return FDGS_E_SMEM;
+    float* S = (float*)a->scratch;
+    const int Wn = lo.Wn, F = lo.F;
+
+    // 1. weights -> hi/lo K-major chunks in consumption order: W0 | per head (W1, W1^T) | W0^T
+    PrepArgs pa;
+    int ns = 0;
+    long long off = 0;
+    pa.s[ns++] = PrepSec{a->net.trunk_w[0], F, Wn, F, 0, off}; off += (long long)(F / KCH) * 32 * Wn;
+    for (int j = 0; j < plan.nheads; ++j) {
+        const float* w1 = a->net.head_w1[plan.heads[j]];
+        pa.s[ns++] = PrepSec{w1, Wn, Wn, Wn, 0, off}; off += (long long)(Wn / KCH) * 32 * Wn;
+        pa.s[ns++] = PrepSec{w1, Wn, Wn, Wn, 1, off}; off += (long long)(Wn / KCH) * 32 * Wn;      // (n = h, k = z) = W1[z][h]
+    }
+    pa.s[ns++] = PrepSec{a->net.trunk_w[0], F, F, Wn, 1, off}; off += (long long)(Wn / KCH) * 32 * F;  // (n = f, k = h) = W0[h][f]
+    pa.nsec = ns;
+    if (off != plan.wprep_floats) return FDGS_E_BADARG;
+    { FDGS_PROF("k_deform_wprep_bwd", stream);
+    k_deform_wprep_bwd<<<96, 256, 0, stream>>>(pa, S + plan.off_wprep);
+    }
+    FDGS_LAUNCH_CHECK(a->debug, stream);
+
+    // 2. data gradients
+    Net net;
+    net.wprep = S + plan.off_wprep; net.b0 = a->net.trunk_b[0];
+    for (int h = 0; h < FDGS_NUM_HEADS; ++h) { net.b1[h] = a->net.head_b1[h]; net.w2[h] = a->net.head_w2[h]; }
+    IO io;
+    io.P = a->P; io.xyz = a->xyz; io.d_xyz = a->d_xyz_grid;
+    for (int h = 0; h < FDGS_NUM_HEADS; ++h) io.g[h] = gsrc[h];
+    io.S_F = S + plan.off_F; io.S_H = S + plan.off_H; io.S_GH = S + plan.off_GH;
+    for (int j = 0; j < FDGS_NUM_HEADS; ++j) { io.S_RZ[j] = S + plan.off_RZ[j]; io.S_GZ[j] = S + plan.off_GZ[j]; }
+    const int ntiles = (a->P + TP - 1) / TP;
+    const int grid = ntiles < sm_count() ? ntiles : sm_count();
+    if (Wn == 128) {
+        FDGS_CUDA(cudaFuncSetAttribute(k_deform_bwd_data<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sp.bytes));
+        { FDGS_PROF("k_deform_bwd_data", stream);
+        k_deform_bwd_data<128><<<grid, NTHREADS, sp.bytes, stream>>>(lo, plan, sp, net, io, packed, trow, gpacked, gtrow, ntiles);
+        }
+    } else {
+        FDGS_CUDA(cudaFuncSetAttribute(k_deform_bwd_data<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sp.bytes));
+        { FDGS_PROF("k_deform_bwd_data", stream);
+        k_deform_bwd_data<64><<<grid, NTHREADS, sp.bytes, stream>>>(lo, plan, sp, net, io, packed, trow, gpacked, gtrow, ntiles);
+        }
+    }
+    FDGS_LAUNCH_CHECK(a->debug, stream);
+
+    // 3. weight gradients: jobs x point slices, one CTA each
+    WArgs wa;
+    int nj = 0;
+    float* dw1[FDGS_NUM_HEADS] = {a->d_head_w1[0], a->d_head_w1[1], a->d_head_w1[2], a->d_head_w1[3], a->d_head_w1[4]};
+    double cost[MAXJOBS];
+    for (int j = 0; j < plan.nheads; ++j) {
+        const int h = plan.heads[j];
+        const int NO = head_out(h);
+        wa.j[nj] = WJob{io.S_GZ[j], Wn, Wn, (int)plan.Pp, io.S_H, Wn, Wn, (int)plan.Pp, dw1[h], Wn, 0, a->d_head_b1[h], nullptr, 1};
+        cost[nj++] = 2.0 * Wn;
+        wa.j[nj] = WJob{io.S_RZ[j], Wn, Wn, (int)plan.Pp, gsrc[h], NO, NO, a->P, a->d_head_w2[h], Wn, 1, nullptr, a->d_head_b2[h], 1};
+        cost[nj++] = Wn + NO + 16.0;
+    }
+    wa.j[nj] = WJob{io.S_GH, Wn, Wn, (int)plan.Pp, io.S_F, F, F, (int)plan.Pp, a->d_trunk_w[0], F, 0, a->d_trunk_b[0], nullptr, 1};
+    cost[nj++] = Wn + F + 16.0;
+    wa.njobs = nj; wa.rows = plan.Pp;
+    // distribute the SMs over the jobs in proportion to the bytes they stream
+    double tot = 0; for (int i = 0; i < nj; ++i) tot += cost[i];
+    const long long nst = plan.Pp / WK;
+    int used = 0;
+    for (int i = 0; i < nj; ++i) {
+        int s = (int)(cost[i] / tot * sm_count());
+        if (s < 1) s = 1;
+        if ((long long)s > nst) s = (int)nst;
+        wa.j[i].slices = s; used += s;
+    }
+    for (int i = 0; used < sm_count() && i < nj; i += 2) if (wa.j[i].slices < nst) { wa.j[i].slices++; used++; }
+    const int nblk_max = (Wn + 31) / 32;
+    const size_t wsm = (size_t)WSTAGES * (2 * 4096 + 2 * nblk_max * 1024) * 4 + 1024;
+    FDGS_CUDA(cudaFuncSetAttribute(k_deform_bwd_weights, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wsm));
+    { FDGS_PROF("k_deform_bwd_weights", stream);
+    k_deform_bwd_weights<<<used, W_THREADS, wsm, stream>>>(wa);
+    }
+    FDGS_LAUNCH_CHECK(a->debug, stream);
+    return FDGS_OK;
+}
+
+}  // namespace fdgs_deform_tc_bwd

@@ -173,6 +173,9 @@ class _DeformFunction(torch.autograd.Function):
             ws = torch.empty((lib.fdgs_deform_backward_ws_bytes(C.byref(a.net)),), dtype=torch.uint8, device=dev)
             a.packed_ws, a.trow_ws = packed.data_ptr(), trow.data_ptr()
             a.ws, a.ws_bytes = ws.data_ptr(), ws.numel()
+            scratch = mod._bwd_scratch(lib, a.net, P, dev) if int(mod.precision) != 2 else None
+            if scratch is not None:
+                a.scratch, a.scratch_bytes = scratch.data_ptr(), scratch.numel()
             a.debug = 0
             L.check(lib.fdgs_deform_backward(C.byref(a), C.c_void_p(torch.cuda.current_stream().cuda_stream)),
                     "fdgs_deform_backward")
@@ -301,6 +304,19 @@ class Deformation(nn.Module):
         if w is None or w.numel() < n or w.device != dev:
             w = torch.empty((max(n, 256),), dtype=torch.uint8, device=dev)
             self._wprep_ws = w
+        return w
+
+    def _bwd_scratch(self, lib, net, P, dev):
+        """Scratch of the tensor-core backward (activations exchanged between its two kernels; dead after the call,
+        so one buffer serves every view).  None when this net runs the CUDA-core backward."""
+        n = lib.fdgs_deform_backward_scratch_bytes(C.byref(net), int(P))
+        if n == 0:
+            return None
+        w = getattr(self, "_bwd_scratch_ws", None)
+        if w is None or w.numel() < n or w.device != dev:
+            self._bwd_scratch_ws = None
+            w = torch.empty((n,), dtype=torch.uint8, device=dev)
+            self._bwd_scratch_ws = w
         return w
 
     def _mark_packed_valid(self):

@@ -250,10 +250,15 @@ typedef struct FdgsDeformBackward {
     const void* packed_ws;          /* the forward call's packed planes */
     const void* trow_ws;            /* the forward call's time rows of this view */
     void* ws; size_t ws_bytes;      /* fdgs_deform_backward_ws_bytes(): packed plane-grad scratch */
+    void* scratch; size_t scratch_bytes; /* fdgs_deform_backward_scratch_bytes(net, P): FP32 activations exchanged between
+                                       the two tensor-core backward kernels + formatted weights; contents are dead
+                                       after the call (reuse it across views).  Required unless precision == 2 or the
+                                       function returns 0 for this net (then the CUDA-core kernel runs).            */
     int32_t debug;
 } FdgsDeformBackward;
 
 size_t fdgs_deform_backward_ws_bytes(const FdgsDeformNet* net);
+size_t fdgs_deform_backward_scratch_bytes(const FdgsDeformNet* net, int P);
 int fdgs_deform_backward(const FdgsDeformBackward* a, void* stream);
 
 #ifdef __cplusplus
