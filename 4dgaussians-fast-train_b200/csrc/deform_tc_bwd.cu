@@ -688,42 +688,67 @@ k_deform_bwd_weights(WArgs args)
         const int gpr = nblkB * 8;                                 // float4 groups per B row (8, 16 or 32)
         const int cgB = tid % gpr, rB = tid / gpr, rstepB = 256 / gpr;
         float sa[4] = {0.f, 0.f, 0.f, 0.f}, sb[4] = {0.f, 0.f, 0.f, 0.f};
-        uint32_t g = 0;
-        for (long long s = s_begin; s < s_end; ++s, ++g) {
-            const uint32_t slot = g % WSTAGES;
+        // B rows per thread per stage: 32 * gpr / 256 = gpr / 8 (1, 2 or 4)
+        const int nrb = gpr >> 3;
+        // register prefetch, PF stages ahead (global latency ~1 us >> one stage of split + store work)
+        constexpr int PF = 2;
+        float4 va[PF][4], vb[PF][4];
+        auto issue = [&](long long s, float4 (&a4)[4], float4 (&b4)[4]) {
             const long long r0 = s * WK;
-            float4 va[4];
 #pragma unroll
-            for (int i = 0; i < 4; ++i) va[i] = load4(J.A, J.lda, r0 + rA + 8 * i, cgA * 4, J.ma, J.rowsA);
-            mbar_wait(&bars[WB_EMPTY + slot], ((g / WSTAGES) & 1) ^ 1);
-            float* Ah = sm + (size_t)slot * stage_floats;
-            float* Al = Ah + 4096;
-            float* Bh = Al + 4096;
-            float* Bl = Bh + nblkB * 1024;
+            for (int i = 0; i < 4; ++i) a4[i] = load4(J.A, J.lda, r0 + rA + 8 * i, cgA * 4, J.ma, J.rowsA);
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                const int r = rA + 8 * i;
-                float4 hi, lw;
-                split_tf32_rn(va[i].x, hi.x, lw.x); split_tf32_rn(va[i].y, hi.y, lw.y);
-                split_tf32_rn(va[i].z, hi.z, lw.z); split_tf32_rn(va[i].w, hi.w, lw.w);
-                sa[0] += va[i].x; sa[1] += va[i].y; sa[2] += va[i].z; sa[3] += va[i].w;
-                const int o = tile32_off(r, cgA * 4, WK);
-                *reinterpret_cast<float4*>(Ah + o) = hi;
-                *reinterpret_cast<float4*>(Al + o) = lw;
+            for (int i = 0; i < 4; ++i)
+                b4[i] = (i < nrb) ? load4(J.B, J.ldb, r0 + rB + rstepB * i, cgB * 4, J.nb, J.rowsB) : make_float4(0.f, 0.f, 0.f, 0.f);
+        };
+#pragma unroll
+        for (int u = 0; u < PF; ++u) {
+            if (s_begin + u < s_end) issue(s_begin + u, va[u], vb[u]);
+        }
+        uint32_t g = 0;
+        for (long long s0 = s_begin; s0 < s_end; s0 += PF) {
+#pragma unroll
+            for (int u = 0; u < PF; ++u) {
+                const long long s = s0 + u;
+                if (s >= s_end) break;
+                const uint32_t slot = g % WSTAGES;
+                mbar_wait(&bars[WB_EMPTY + slot], ((g / WSTAGES) & 1) ^ 1);
+                float* Ah = sm + (size_t)slot * stage_floats;
+                float* Al = Ah + 4096;
+                float* Bh = Al + 4096;
+                float* Bl = Bh + nblkB * 1024;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const int r = rA + 8 * i;
+                    const float4 v = va[u][i];
+                    float4 hi, lw;
+                    split_tf32_rn(v.x, hi.x, lw.x); split_tf32_rn(v.y, hi.y, lw.y);
+                    split_tf32_rn(v.z, hi.z, lw.z); split_tf32_rn(v.w, hi.w, lw.w);
+                    sa[0] += v.x; sa[1] += v.y; sa[2] += v.z; sa[3] += v.w;
+                    const int o = tile32_off(r, cgA * 4, WK);
+                    *reinterpret_cast<float4*>(Ah + o) = hi;
+                    *reinterpret_cast<float4*>(Al + o) = lw;
+                }
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    if (i < nrb) {
+                        const int r = rB + rstepB * i;
+                        const float4 v = vb[u][i];
+                        float4 hi, lw;
+                        split_tf32_rn(v.x, hi.x, lw.x); split_tf32_rn(v.y, hi.y, lw.y);
+                        split_tf32_rn(v.z, hi.z, lw.z); split_tf32_rn(v.w, hi.w, lw.w);
+                        sb[0] += v.x; sb[1] += v.y; sb[2] += v.z; sb[3] += v.w;
+                        const int o = tile32_off(r, cgB * 4, WK);
+                        *reinterpret_cast<float4*>(Bh + o) = hi;
+                        *reinterpret_cast<float4*>(Bl + o) = lw;
+                    }
+                }
+                if (s + PF < s_end) issue(s + PF, va[u], vb[u]);
+                fence_async_smem();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&bars[WB_FULL + slot]);
+                ++g;
             }
-            for (int r = rB; r < WK; r += rstepB) {
-                const float4 v = load4(J.B, J.ldb, r0 + r, cgB * 4, J.nb, J.rowsB);
-                float4 hi, lw;
-                split_tf32_rn(v.x, hi.x, lw.x); split_tf32_rn(v.y, hi.y, lw.y);
-                split_tf32_rn(v.z, hi.z, lw.z); split_tf32_rn(v.w, hi.w, lw.w);
-                sb[0] += v.x; sb[1] += v.y; sb[2] += v.z; sb[3] += v.w;
-                const int o = tile32_off(r, cgB * 4, WK);
-                *reinterpret_cast<float4*>(Bh + o) = hi;
-                *reinterpret_cast<float4*>(Bl + o) = lw;
-            }
-            fence_async_smem();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&bars[WB_FULL + slot]);
         }
         // ---- bias gradients ------------------------------------------------------------------------------------
         if (J.biasA) {
