@@ -15,7 +15,7 @@ HEADERS = ["fdgs_common.cuh", "raster_math.cuh", "prof.cuh", "deform_common.cuh"
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     "-Xcompiler", "-fPIC", "-DFDGS_ARCH=100",
-]
+] + os.environ.get("FDGS_EXTRA_NVCC", "").split()
 
 
 def _newer(a, b):

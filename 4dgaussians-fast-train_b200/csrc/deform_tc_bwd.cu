@@ -19,6 +19,7 @@
 #include "deform_common.cuh"
 #include "umma.cuh"
 #include "prof.cuh"
+#include <cstdio>
 
 namespace fdgs_deform_tc_bwd {
 using namespace fdgs_deform;
@@ -136,6 +137,17 @@ static inline Smem make_smem(const Layout& lo) {
 }
 
 __device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
+
+// Optional phase timing of CTA 0 / thread 0 (build with -DFDGS_PHASE_TIMING; prints cycle totals at kernel end).
+#ifdef FDGS_PHASE_TIMING
+#define PT_DECL long long pt_[12] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0}; long long pt_t = clock64();
+#define PT(i) { const long long n_ = clock64(); pt_[i] += n_ - pt_t; pt_t = n_; }
+#define PT_PRINT if (blockIdx.x == 0 && tid == 0) printf("bwd_data phases (cycles, CTA0): sample %lld | wait_trunk %lld | trunk_epi %lld | wait_z %lld | head_epi %lld | wait_grh %lld | gh_epi %lld | wait_gf %lld | samp_bwd %lld | tail %lld\n", pt_[0], pt_[1], pt_[2], pt_[3], pt_[4], pt_[5], pt_[6], pt_[7], pt_[8], pt_[9]);
+#else
+#define PT_DECL
+#define PT(i)
+#define PT_PRINT
+#endif
 
 // TMEM column map (512 columns): accumulator (trunk h, head z, g_feat), g_z / g_h hi, lo, g_relu_h accumulator
 constexpr uint32_t TM_ACC = 0, TM_GHI = 128, TM_GLO = 256, TM_GRH = 384;
@@ -461,6 +473,7 @@ k_deform_bwd_data(Layout lo, Plan plan, Smem sp, Net net, IO io, const float* __
         const int col0 = hf * NH;
         uint32_t ph_acc = 0, ph_grh = 0, ph_gf = 0;
         const int C = lo.C, CH = C >> 1;
+        PT_DECL
         for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
             const int p = tile * TP + row;
             const bool valid = p < io.P;
@@ -483,10 +496,12 @@ k_deform_bwd_data(Layout lo, Plan plan, Smem sp, Net net, IO io, const float* __
             fence_async_smem();
             epi_bar();
             if (tid == 0) mbar_arrive(&bars[B_FEATFULL]);
+            PT(0)
 
             // ---- trunk epilogue: relu(h + b0) -> scratch, shared memory hi / lo; gate bits kept in registers ------
             mbar_wait(&bars[B_ACCFULL], ph_acc); ph_acc ^= 1;
             tc_fence_after();
+            PT(1)
             uint32_t gate[NH / 32];
 #pragma unroll
             for (int c0 = 0; c0 < NH; c0 += 32) {
@@ -514,6 +529,7 @@ k_deform_bwd_data(Layout lo, Plan plan, Smem sp, Net net, IO io, const float* __
             tc_fence_before();
             epi_bar();
             if (tid == 0) mbar_arrive(&bars[B_HFULL]);
+            PT(2)
 
             // ---- heads ---------------------------------------------------------------------------------------------
             for (int i = 0; i < plan.nheads; ++i) {
@@ -521,6 +537,7 @@ k_deform_bwd_data(Layout lo, Plan plan, Smem sp, Net net, IO io, const float* __
                 const int NO = head_out(h);
                 mbar_wait(&bars[B_ACCFULL], ph_acc); ph_acc ^= 1;
                 tc_fence_after();
+                PT(3)
                 const float* gsrc = io.g[h] + (size_t)(valid ? p : 0) * NO;
                 float* rz_row = io.S_RZ[i] + (size_t)p * WN;
                 float* gz_row = io.S_GZ[i] + (size_t)p * WN;
@@ -531,11 +548,13 @@ k_deform_bwd_data(Layout lo, Plan plan, Smem sp, Net net, IO io, const float* __
                 tc_fence_before();
                 epi_bar();
                 if (tid == 0) mbar_arrive(&bars[B_GZFULL]);
+                PT(4)
             }
 
             // ---- g_h = g_relu_h [h > 0] -> scratch, TMEM hi / lo -----------------------------------------------------
             mbar_wait(&bars[B_GRHFULL], ph_grh); ph_grh ^= 1;
             tc_fence_after();
+            PT(5)
 #pragma unroll
             for (int c0 = 0; c0 < NH; c0 += 16) {
                 uint32_t v[16], hi[16], lw[16];
@@ -560,10 +579,12 @@ k_deform_bwd_data(Layout lo, Plan plan, Smem sp, Net net, IO io, const float* __
             tc_fence_before();
             epi_bar();
             if (tid == 0) mbar_arrive(&bars[B_GHFULL]);
+            PT(6)
 
             // ---- g_feat -> sampler backward -----------------------------------------------------------------------------
             mbar_wait(&bars[B_GFFULL], ph_gf); ph_gf ^= 1;
             tc_fence_after();
+            PT(7)
             float dq[3] = {0.f, 0.f, 0.f};
             for (int l = 0; l < lo.L; ++l)
                 for (int cc = 0; cc < CH; cc += 4) {
@@ -574,6 +595,7 @@ k_deform_bwd_data(Layout lo, Plan plan, Smem sp, Net net, IO io, const float* __
                     const float df[4] = {__uint_as_float(v[0]), __uint_as_float(v[1]), __uint_as_float(v[2]), __uint_as_float(v[3])};
                     if (valid) sample_bwd4(lo, l, q, packed, trow, gpacked, gtrow, c0, df, dq);
                 }
+            PT(8)
             red[(hf * TP + row) * 3 + 0] = dq[0];
             red[(hf * TP + row) * 3 + 1] = dq[1];
             red[(hf * TP + row) * 3 + 2] = dq[2];
@@ -587,7 +609,9 @@ k_deform_bwd_data(Layout lo, Plan plan, Smem sp, Net net, IO io, const float* __
                 }
             }
             epi_bar();          // `red` and the feat/relu(h) buffers are free again
+            PT(9)
         }
+        PT_PRINT
     }
     tc_fence_before();
     __syncthreads();
@@ -688,18 +712,41 @@ k_deform_bwd_weights(WArgs args)
         const int gpr = nblkB * 8;                                 // float4 groups per B row (8, 16 or 32)
         const int cgB = tid % gpr, rB = tid / gpr, rstepB = 256 / gpr;
         float sa[4] = {0.f, 0.f, 0.f, 0.f}, sb[4] = {0.f, 0.f, 0.f, 0.f};
-        // B rows per thread per stage: 32 * gpr / 256 = gpr / 8 (1, 2 or 4)
-        const int nrb = gpr >> 3;
-        // register prefetch, PF stages ahead (global latency ~1 us >> one stage of split + store work)
-        constexpr int PF = 2;
+        const int nrb = gpr >> 3;                                  // B rows per thread per stage (1, 2 or 4)
+        // Fast path (every scratch operand): rows padded to the stage size and 16-byte aligned rows, so a thread's
+        // loads are unconditional float4s from a pointer that advances by a constant; only g_o (ld = 1, 3, 4, 48 with
+        // P valid rows) takes the checked path.
+        const bool fastA = (J.lda & 3) == 0 && J.rowsA >= args.rows && (J.ma & 3) == 0;
+        const bool fastB = (J.ldb & 3) == 0 && J.rowsB >= args.rows && (J.nb & 3) == 0;
+        const bool onA = cgA * 4 < J.ma, onB = cgB * 4 < J.nb;
+        const bool wantA = J.biasA != nullptr, wantB = J.biasB != nullptr;
+        const size_t strideA = (size_t)8 * J.lda, strideB = (size_t)rstepB * J.ldb;
+        const float* pA = J.A + ((size_t)s_begin * WK + rA) * J.lda + cgA * 4;
+        const float* pB = J.B + ((size_t)s_begin * WK + rB) * J.ldb + cgB * 4;
+        int oA[4], oB[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { oA[i] = tile32_off(rA + 8 * i, cgA * 4, WK); oB[i] = tile32_off((rB + rstepB * i) & (WK - 1), cgB * 4, WK); }
+        constexpr int PF = 2;                                      // register prefetch depth (global latency ~1 us)
         float4 va[PF][4], vb[PF][4];
+        const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
         auto issue = [&](long long s, float4 (&a4)[4], float4 (&b4)[4]) {
-            const long long r0 = s * WK;
+            const size_t ds = (size_t)(s - s_begin) * WK;
+            if (fastA) {
+                const float* q = pA + ds * J.lda;
 #pragma unroll
-            for (int i = 0; i < 4; ++i) a4[i] = load4(J.A, J.lda, r0 + rA + 8 * i, cgA * 4, J.ma, J.rowsA);
+                for (int i = 0; i < 4; ++i) a4[i] = onA ? *reinterpret_cast<const float4*>(q + i * strideA) : z4;
+            } else {
 #pragma unroll
-            for (int i = 0; i < 4; ++i)
-                b4[i] = (i < nrb) ? load4(J.B, J.ldb, r0 + rB + rstepB * i, cgB * 4, J.nb, J.rowsB) : make_float4(0.f, 0.f, 0.f, 0.f);
+                for (int i = 0; i < 4; ++i) a4[i] = load4(J.A, J.lda, s * WK + rA + 8 * i, cgA * 4, J.ma, J.rowsA);
+            }
+            if (fastB) {
+                const float* q = pB + ds * J.ldb;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) b4[i] = (i < nrb && onB) ? *reinterpret_cast<const float4*>(q + i * strideB) : z4;
+            } else {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) b4[i] = (i < nrb) ? load4(J.B, J.ldb, s * WK + rB + rstepB * i, cgB * 4, J.nb, J.rowsB) : z4;
+            }
         };
 #pragma unroll
         for (int u = 0; u < PF; ++u) {
@@ -714,33 +761,28 @@ k_deform_bwd_weights(WArgs args)
                 const uint32_t slot = g % WSTAGES;
                 mbar_wait(&bars[WB_EMPTY + slot], ((g / WSTAGES) & 1) ^ 1);
                 float* Ah = sm + (size_t)slot * stage_floats;
-                float* Al = Ah + 4096;
-                float* Bh = Al + 4096;
-                float* Bl = Bh + nblkB * 1024;
+                float* Bh = Ah + 8192;
+                const int lofsB = nblkB * 1024;
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {
-                    const int r = rA + 8 * i;
                     const float4 v = va[u][i];
                     float4 hi, lw;
                     split_tf32_rn(v.x, hi.x, lw.x); split_tf32_rn(v.y, hi.y, lw.y);
                     split_tf32_rn(v.z, hi.z, lw.z); split_tf32_rn(v.w, hi.w, lw.w);
-                    sa[0] += v.x; sa[1] += v.y; sa[2] += v.z; sa[3] += v.w;
-                    const int o = tile32_off(r, cgA * 4, WK);
-                    *reinterpret_cast<float4*>(Ah + o) = hi;
-                    *reinterpret_cast<float4*>(Al + o) = lw;
+                    if (wantA) { sa[0] += v.x; sa[1] += v.y; sa[2] += v.z; sa[3] += v.w; }
+                    *reinterpret_cast<float4*>(Ah + oA[i]) = hi;
+                    *reinterpret_cast<float4*>(Ah + 4096 + oA[i]) = lw;
                 }
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {
                     if (i < nrb) {
-                        const int r = rB + rstepB * i;
                         const float4 v = vb[u][i];
                         float4 hi, lw;
                         split_tf32_rn(v.x, hi.x, lw.x); split_tf32_rn(v.y, hi.y, lw.y);
                         split_tf32_rn(v.z, hi.z, lw.z); split_tf32_rn(v.w, hi.w, lw.w);
-                        sb[0] += v.x; sb[1] += v.y; sb[2] += v.z; sb[3] += v.w;
-                        const int o = tile32_off(r, cgB * 4, WK);
-                        *reinterpret_cast<float4*>(Bh + o) = hi;
-                        *reinterpret_cast<float4*>(Bl + o) = lw;
+                        if (wantB) { sb[0] += v.x; sb[1] += v.y; sb[2] += v.z; sb[3] += v.w; }
+                        *reinterpret_cast<float4*>(Bh + oB[i]) = hi;
+                        *reinterpret_cast<float4*>(Bh + lofsB + oB[i]) = lw;
                     }
                 }
                 if (s + PF < s_end) issue(s + PF, va[u], vb[u]);
