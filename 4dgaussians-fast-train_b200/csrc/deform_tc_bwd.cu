@@ -299,8 +299,8 @@ __device__ __forceinline__ void head_epilogue(uint32_t lane_base, int col0, int 
         }
 #pragma unroll
         for (int j = 0; j < 16; j += 4) {
-            *reinterpret_cast<float4*>(rz_row + col0 + c0 + j) = make_float4(z[j], z[j + 1], z[j + 2], z[j + 3]);
-            *reinterpret_cast<float4*>(gz_row + col0 + c0 + j) = make_float4(gr[j], gr[j + 1], gr[j + 2], gr[j + 3]);
+            __stcs(reinterpret_cast<float4*>(rz_row + ((col0 + c0 + j) >> 2) * 512), make_float4(z[j], z[j + 1], z[j + 2], z[j + 3]));
+            __stcs(reinterpret_cast<float4*>(gz_row + ((col0 + c0 + j) >> 2) * 512), make_float4(gr[j], gr[j + 1], gr[j + 2], gr[j + 3]));
         }
         tmem_st16(lane_base + TM_GHI + col0 + c0, hi);
         tmem_st16(lane_base + TM_GLO + col0 + c0, lw);
@@ -491,7 +491,8 @@ k_deform_bwd_data(Layout lo, Plan plan, Smem sp, Net net, IO io, const float* __
                     const int o = tile_off(row, l * C + c0, 128);
                     *reinterpret_cast<float4*>(F_hi + o) = hi;
                     *reinterpret_cast<float4*>(F_lo + o) = lw;
-                    *reinterpret_cast<float4*>(io.S_F + (size_t)p * F + l * C + c0) = make_float4(prod[0], prod[1], prod[2], prod[3]);
+                    __stcs(reinterpret_cast<float4*>(io.S_F + (size_t)tile * TP * F + (((l * C + c0) >> 2) * TP + row) * 4),
+                           make_float4(prod[0], prod[1], prod[2], prod[3]));
                 }
             fence_async_smem();
             epi_bar();
@@ -521,7 +522,8 @@ k_deform_bwd_data(Layout lo, Plan plan, Smem sp, Net net, IO io, const float* __
                     const int o = tile_off(row, col0 + c0 + j, 128);
                     *reinterpret_cast<float4*>(HS_hi + o) = make_float4(a[0], a[1], a[2], a[3]);
                     *reinterpret_cast<float4*>(HS_lo + o) = make_float4(b[0], b[1], b[2], b[3]);
-                    *reinterpret_cast<float4*>(io.S_H + (size_t)p * WN + col0 + c0 + j) = make_float4(x[0], x[1], x[2], x[3]);
+                    __stcs(reinterpret_cast<float4*>(io.S_H + (size_t)tile * TP * WN + (((col0 + c0 + j) >> 2) * TP + row) * 4),
+                           make_float4(x[0], x[1], x[2], x[3]));
                 }
                 gate[c0 / 32] = m;
             }
@@ -539,8 +541,8 @@ k_deform_bwd_data(Layout lo, Plan plan, Smem sp, Net net, IO io, const float* __
                 tc_fence_after();
                 PT(3)
                 const float* gsrc = io.g[h] + (size_t)(valid ? p : 0) * NO;
-                float* rz_row = io.S_RZ[i] + (size_t)p * WN;
-                float* gz_row = io.S_GZ[i] + (size_t)p * WN;
+                float* rz_row = io.S_RZ[i] + (size_t)tile * TP * WN + row * 4;      // blocked: + (col >> 2) * 512
+                float* gz_row = io.S_GZ[i] + (size_t)tile * TP * WN + row * 4;
                 if (h == FDGS_HEAD_SHS)
                     head_epilogue<48, NH, WN>(lane_base, col0, NO, valid, gsrc, B1s + h * WN, W2s + w2_row0(h) * WN, rz_row, gz_row);
                 else
@@ -571,7 +573,8 @@ k_deform_bwd_data(Layout lo, Plan plan, Smem sp, Net net, IO io, const float* __
                 }
 #pragma unroll
                 for (int j = 0; j < 16; j += 4)
-                    *reinterpret_cast<float4*>(io.S_GH + (size_t)p * WN + col0 + c0 + j) = make_float4(gh[j], gh[j + 1], gh[j + 2], gh[j + 3]);
+                    __stcs(reinterpret_cast<float4*>(io.S_GH + (size_t)tile * TP * WN + (((col0 + c0 + j) >> 2) * TP + row) * 4),
+                           make_float4(gh[j], gh[j + 1], gh[j + 2], gh[j + 3]));
                 tmem_st16(lane_base + TM_GHI + col0 + c0, hi);
                 tmem_st16(lane_base + TM_GLO + col0 + c0, lw);
             }
@@ -628,6 +631,7 @@ struct WJob {
     float* biasA;                            // += column sums of A [ma]   (or null)
     float* biasB;                            // += column sums of B [nb]   (or null)
     int slices;                              // CTAs sharing this job
+    int blkA, blkB;                          // operand stored tile-blocked: [tile][col/4][128 rows][4] (scratch layout)
 };
 constexpr int MAXJOBS = 2 * FDGS_NUM_HEADS + 1;
 struct WArgs { WJob j[MAXJOBS]; int njobs; long long rows; };   // rows = Pp (multiple of 128)
@@ -707,45 +711,59 @@ k_deform_bwd_weights(WArgs args)
         }
         __syncwarp();
     } else {
-        // ---- staging: thread owns float4 column group cgA of A (rows rA + 8 i) and cgB of B ----------------
-        const int cgA = tid & 31, rA = tid >> 5;
-        const int gpr = nblkB * 8;                                 // float4 groups per B row (8, 16 or 32)
-        const int cgB = tid % gpr, rB = tid / gpr, rstepB = 256 / gpr;
-        float sa[4] = {0.f, 0.f, 0.f, 0.f}, sb[4] = {0.f, 0.f, 0.f, 0.f};
-        const int nrb = gpr >> 3;                                  // B rows per thread per stage (1, 2 or 4)
-        // Fast path (every scratch operand): rows padded to the stage size and 16-byte aligned rows, so a thread's
-        // loads are unconditional float4s from a pointer that advances by a constant; only g_o (ld = 1, 3, 4, 48 with
-        // P valid rows) takes the checked path.
-        const bool fastA = (J.lda & 3) == 0 && J.rowsA >= args.rows && (J.ma & 3) == 0;
-        const bool fastB = (J.ldb & 3) == 0 && J.rowsB >= args.rows && (J.nb & 3) == 0;
+        // ---- staging ------------------------------------------------------------------------------------------
+        // Blocked (scratch) operands: a warp instruction covers 4 column groups x 8 rows = four 128-byte runs; the
+        // column group of a thread is the same in every pass and stage (its column sums stay in registers).
+        // Row-major operands (g_o: ld = 1, 3, 4, 48, P valid rows) take the checked path.
+        const int gprB = nblkB * 8;                                 // float4 groups per staged B row (8, 16 or 32)
+        const int nrb = gprB >> 3;                                  // B float4s per thread per stage (1, 2 or 4)
+        const int sub = lane >> 3, row8 = lane & 7;
+        int cgA, cgB, rowA[4], rowB[4];
+        {
+            const int u0 = warp * 4 + sub;
+            cgA = u0;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) rowA[i] = i * 8 + row8;
+            if (J.blkB) {
+                cgB = u0 % gprB;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) rowB[i] = (((i * 32 + u0) / gprB) * 8 + row8) & (WK - 1);
+            } else {
+                cgB = tid % gprB;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) rowB[i] = (tid / gprB + (256 / gprB) * i) & (WK - 1);
+            }
+        }
+        if (!J.blkA) { cgA = tid & 31;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) rowA[i] = (tid >> 5) + 8 * i; }
         const bool onA = cgA * 4 < J.ma, onB = cgB * 4 < J.nb;
         const bool wantA = J.biasA != nullptr, wantB = J.biasB != nullptr;
-        const size_t strideA = (size_t)8 * J.lda, strideB = (size_t)rstepB * J.ldb;
-        const float* pA = J.A + ((size_t)s_begin * WK + rA) * J.lda + cgA * 4;
-        const float* pB = J.B + ((size_t)s_begin * WK + rB) * J.ldb + cgB * 4;
         int oA[4], oB[4];
 #pragma unroll
-        for (int i = 0; i < 4; ++i) { oA[i] = tile32_off(rA + 8 * i, cgA * 4, WK); oB[i] = tile32_off((rB + rstepB * i) & (WK - 1), cgB * 4, WK); }
+        for (int i = 0; i < 4; ++i) { oA[i] = tile32_off(rowA[i], cgA * 4, WK); oB[i] = tile32_off(rowB[i], cgB * 4, WK); }
+        float sa[4] = {0.f, 0.f, 0.f, 0.f}, sb[4] = {0.f, 0.f, 0.f, 0.f};
         constexpr int PF = 2;                                      // register prefetch depth (global latency ~1 us)
         float4 va[PF][4], vb[PF][4];
         const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
         auto issue = [&](long long s, float4 (&a4)[4], float4 (&b4)[4]) {
-            const size_t ds = (size_t)(s - s_begin) * WK;
-            if (fastA) {
-                const float* q = pA + ds * J.lda;
+            const size_t tile = (size_t)(s >> 2);                  // 128-row tile, 32-row quarter
+            const int r0 = (int)(s & 3) * WK;
+            if (J.blkA) {
+                const float* q = J.A + tile * 128 * J.lda + (size_t)(cgA * 128 + r0) * 4;
 #pragma unroll
-                for (int i = 0; i < 4; ++i) a4[i] = onA ? *reinterpret_cast<const float4*>(q + i * strideA) : z4;
+                for (int i = 0; i < 4; ++i) a4[i] = onA ? __ldcs(reinterpret_cast<const float4*>(q + rowA[i] * 4)) : z4;
             } else {
 #pragma unroll
-                for (int i = 0; i < 4; ++i) a4[i] = load4(J.A, J.lda, s * WK + rA + 8 * i, cgA * 4, J.ma, J.rowsA);
+                for (int i = 0; i < 4; ++i) a4[i] = load4(J.A, J.lda, s * WK + rowA[i], cgA * 4, J.ma, J.rowsA);
             }
-            if (fastB) {
-                const float* q = pB + ds * J.ldb;
+            if (J.blkB) {
+                const float* q = J.B + tile * 128 * J.ldb + (size_t)(cgB * 128 + r0) * 4;
 #pragma unroll
-                for (int i = 0; i < 4; ++i) b4[i] = (i < nrb && onB) ? *reinterpret_cast<const float4*>(q + i * strideB) : z4;
+                for (int i = 0; i < 4; ++i) b4[i] = (i < nrb && onB) ? __ldcs(reinterpret_cast<const float4*>(q + rowB[i] * 4)) : z4;
             } else {
 #pragma unroll
-                for (int i = 0; i < 4; ++i) b4[i] = (i < nrb) ? load4(J.B, J.ldb, s * WK + rB + rstepB * i, cgB * 4, J.nb, J.rowsB) : z4;
+                for (int i = 0; i < 4; ++i) b4[i] = (i < nrb) ? load4(J.B, J.ldb, s * WK + rowB[i], cgB * 4, J.nb, J.rowsB) : z4;
             }
         };
 #pragma unroll
@@ -917,12 +935,12 @@ int backward(const Layout& lo, const FdgsDeformBackward* a, const float* packed,
     for (int j = 0; j < plan.nheads; ++j) {
         const int h = plan.heads[j];
         const int NO = head_out(h);
-        wa.j[nj] = WJob{io.S_GZ[j], Wn, Wn, (int)plan.Pp, io.S_H, Wn, Wn, (int)plan.Pp, dw1[h], Wn, 0, a->d_head_b1[h], nullptr, 1};
+        wa.j[nj] = WJob{io.S_GZ[j], Wn, Wn, (int)plan.Pp, io.S_H, Wn, Wn, (int)plan.Pp, dw1[h], Wn, 0, a->d_head_b1[h], nullptr, 1, 1, 1};
         cost[nj++] = 2.0 * Wn;
-        wa.j[nj] = WJob{io.S_RZ[j], Wn, Wn, (int)plan.Pp, gsrc[h], NO, NO, a->P, a->d_head_w2[h], Wn, 1, nullptr, a->d_head_b2[h], 1};
+        wa.j[nj] = WJob{io.S_RZ[j], Wn, Wn, (int)plan.Pp, gsrc[h], NO, NO, a->P, a->d_head_w2[h], Wn, 1, nullptr, a->d_head_b2[h], 1, 1, 0};
         cost[nj++] = Wn + NO + 16.0;
     }
-    wa.j[nj] = WJob{io.S_GH, Wn, Wn, (int)plan.Pp, io.S_F, F, F, (int)plan.Pp, a->d_trunk_w[0], F, 0, a->d_trunk_b[0], nullptr, 1};
+    wa.j[nj] = WJob{io.S_GH, Wn, Wn, (int)plan.Pp, io.S_F, F, F, (int)plan.Pp, a->d_trunk_w[0], F, 0, a->d_trunk_b[0], nullptr, 1, 1, 1};
     cost[nj++] = Wn + F + 16.0;
     wa.njobs = nj; wa.rows = plan.Pp;
     // distribute the SMs over the jobs in proportion to the bytes they stream
