@@ -299,8 +299,8 @@ __device__ __forceinline__ void head_epilogue(uint32_t lane_base, int col0, int 
         }
 #pragma unroll
         for (int j = 0; j < 16; j += 4) {
-            __stcs(reinterpret_cast<float4*>(rz_row + ((col0 + c0 + j) >> 2) * 512), make_float4(z[j], z[j + 1], z[j + 2], z[j + 3]));
-            __stcs(reinterpret_cast<float4*>(gz_row + ((col0 + c0 + j) >> 2) * 512), make_float4(gr[j], gr[j + 1], gr[j + 2], gr[j + 3]));
+            __stcs(reinterpret_cast<float4*>(rz_row + ((col0 + c0 + j) >> 2) * 128), make_float4(z[j], z[j + 1], z[j + 2], z[j + 3]));
+            __stcs(reinterpret_cast<float4*>(gz_row + ((col0 + c0 + j) >> 2) * 128), make_float4(gr[j], gr[j + 1], gr[j + 2], gr[j + 3]));
         }
         tmem_st16(lane_base + TM_GHI + col0 + c0, hi);
         tmem_st16(lane_base + TM_GLO + col0 + c0, lw);
@@ -491,7 +491,7 @@ k_deform_bwd_data(Layout lo, Plan plan, Smem sp, Net net, IO io, const float* __
                     const int o = tile_off(row, l * C + c0, 128);
                     *reinterpret_cast<float4*>(F_hi + o) = hi;
                     *reinterpret_cast<float4*>(F_lo + o) = lw;
-                    __stcs(reinterpret_cast<float4*>(io.S_F + (size_t)tile * TP * F + (((l * C + c0) >> 2) * TP + row) * 4),
+                    __stcs(reinterpret_cast<float4*>(io.S_F + (size_t)tile * TP * F + (row >> 5) * 32 * F + (((l * C + c0) >> 2) * 32 + (row & 31)) * 4),
                            make_float4(prod[0], prod[1], prod[2], prod[3]));
                 }
             fence_async_smem();
@@ -522,7 +522,7 @@ k_deform_bwd_data(Layout lo, Plan plan, Smem sp, Net net, IO io, const float* __
                     const int o = tile_off(row, col0 + c0 + j, 128);
                     *reinterpret_cast<float4*>(HS_hi + o) = make_float4(a[0], a[1], a[2], a[3]);
                     *reinterpret_cast<float4*>(HS_lo + o) = make_float4(b[0], b[1], b[2], b[3]);
-                    __stcs(reinterpret_cast<float4*>(io.S_H + (size_t)tile * TP * WN + (((col0 + c0 + j) >> 2) * TP + row) * 4),
+                    __stcs(reinterpret_cast<float4*>(io.S_H + (size_t)tile * TP * WN + (row >> 5) * 32 * WN + (((col0 + c0 + j) >> 2) * 32 + (row & 31)) * 4),
                            make_float4(x[0], x[1], x[2], x[3]));
                 }
                 gate[c0 / 32] = m;
@@ -541,8 +541,9 @@ k_deform_bwd_data(Layout lo, Plan plan, Smem sp, Net net, IO io, const float* __
                 tc_fence_after();
                 PT(3)
                 const float* gsrc = io.g[h] + (size_t)(valid ? p : 0) * NO;
-                float* rz_row = io.S_RZ[i] + (size_t)tile * TP * WN + row * 4;      // blocked: + (col >> 2) * 512
-                float* gz_row = io.S_GZ[i] + (size_t)tile * TP * WN + row * 4;
+                // blocked scratch: [tile][row / 32][col / 4][row % 32][4]  ->  + (col >> 2) * 128
+                float* rz_row = io.S_RZ[i] + (size_t)tile * TP * WN + (row >> 5) * 32 * WN + (row & 31) * 4;
+                float* gz_row = io.S_GZ[i] + (size_t)tile * TP * WN + (row >> 5) * 32 * WN + (row & 31) * 4;
                 if (h == FDGS_HEAD_SHS)
                     head_epilogue<48, NH, WN>(lane_base, col0, NO, valid, gsrc, B1s + h * WN, W2s + w2_row0(h) * WN, rz_row, gz_row);
                 else
@@ -573,7 +574,7 @@ k_deform_bwd_data(Layout lo, Plan plan, Smem sp, Net net, IO io, const float* __
                 }
 #pragma unroll
                 for (int j = 0; j < 16; j += 4)
-                    __stcs(reinterpret_cast<float4*>(io.S_GH + (size_t)tile * TP * WN + (((col0 + c0 + j) >> 2) * TP + row) * 4),
+                    __stcs(reinterpret_cast<float4*>(io.S_GH + (size_t)tile * TP * WN + (row >> 5) * 32 * WN + (((col0 + c0 + j) >> 2) * 32 + (row & 31)) * 4),
                            make_float4(gh[j], gh[j + 1], gh[j + 2], gh[j + 3]));
                 tmem_st16(lane_base + TM_GHI + col0 + c0, hi);
                 tmem_st16(lane_base + TM_GLO + col0 + c0, lw);
@@ -631,15 +632,17 @@ struct WJob {
     float* biasA;                            // += column sums of A [ma]   (or null)
     float* biasB;                            // += column sums of B [nb]   (or null)
     int slices;                              // CTAs sharing this job
-    int blkA, blkB;                          // operand stored tile-blocked: [tile][col/4][128 rows][4] (scratch layout)
+    int blkA, blkB;                          // operand in the blocked scratch layout [row/32][col/4][row%32][4]: the 32 rows
+                                             // of a stage are one contiguous run of 32*ld floats (one bulk copy)
 };
 constexpr int MAXJOBS = 2 * FDGS_NUM_HEADS + 1;
 struct WArgs { WJob j[MAXJOBS]; int njobs; long long rows; };   // rows = Pp (multiple of 128)
 
 constexpr int WK = 32;             // points per stage
-constexpr int WSTAGES = 3;
-constexpr int W_THREADS = 288;     // 8 staging/epilogue warps + MMA warp
-constexpr int WB_FULL = 0, WB_EMPTY = 4, WB_DONE = 8;
+constexpr int TSTAGES = 2;         // formatted (hi/lo tile32) operand stages feeding the tensor core
+constexpr int RSTAGES = 3;         // raw FP32 stages filled by bulk async copies
+constexpr int W_THREADS = 320;     // 8 staging/epilogue warps + MMA warp + bulk-copy producer warp
+constexpr int WB_TFULL = 0, WB_TEMPTY = 2, WB_RFULL = 4, WB_REMPTY = 7, WB_DONE = 10, WB_COUNT = 11;
 
 __device__ __forceinline__ float4 load4(const float* __restrict__ base, int ld, long long r, int c, int ncols, long long nrows) {
     float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -653,30 +656,37 @@ __device__ __forceinline__ float4 load4(const float* __restrict__ base, int ld, 
     return v;
 }
 
+// Pipeline per CTA:  producer warp: cp.async.bulk of the stage's 32 rows of A (and B) -> raw ring (mbarrier tx bytes)
+//                    8 staging warps: raw (or, for row-major g_o, global) -> TF32 hi/lo split -> swizzled tile32 stage
+//                    MMA thread: 4 x 3 tcgen05.mma (K = 8 points each) per stage into one TMEM accumulator
 __global__ void __launch_bounds__(W_THREADS, 1)
 k_deform_bwd_weights(WArgs args)
 {
     extern __shared__ uint8_t smem_raw[];
     float* sm = reinterpret_cast<float*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-    __shared__ __align__(8) uint64_t bars[12];
+    __shared__ __align__(8) uint64_t bars[WB_COUNT + 1];
     __shared__ uint32_t tmem_slot;
     __shared__ float csumA[128], csumB[128];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    // which job / slice am I
     int jb = 0, first = 0;
     for (; jb < args.njobs; ++jb) { if ((int)blockIdx.x < first + args.j[jb].slices) break; first += args.j[jb].slices; }
     if (jb >= args.njobs) return;
     const WJob J = args.j[jb];
     const int slice = blockIdx.x - first;
-    const long long nst = args.rows / WK;                         // stages in the whole point range
+    const long long nst = args.rows / WK;
     const long long s_begin = nst * slice / J.slices, s_end = nst * (slice + 1) / J.slices;
     const int N16 = (J.nb + 15) & ~15;
-    const int nblkB = (J.nb + 31) >> 5;                           // 32-column blocks of B actually staged
-    // stage layout (floats): A_hi[4][32][32], A_lo, B_hi[nblkB][32][32], B_lo
-    const int stage_floats = 2 * 4096 + 2 * nblkB * 1024;
+    const int nblkB = (J.nb + 31) >> 5;
+    const int stage_floats = 2 * 4096 + 2 * nblkB * 1024;         // A_hi[4][32][32], A_lo, B_hi[nblkB][32][32], B_lo
+    const int rawA_f = 32 * J.lda, rawB_f = J.blkB ? 32 * J.ldb : 0;
+    const int raw_floats = (rawA_f + rawB_f + 255) & ~255;
+    float* raw0 = sm + (size_t)TSTAGES * stage_floats;
 
     if (tid == 0) {
-        for (int i = 0; i < 12; ++i) mbar_init(&bars[i], i >= WB_FULL && i < WB_FULL + WSTAGES ? 8 : 1);
+        for (int i = 0; i < WB_COUNT; ++i) {
+            const bool eight = (i >= WB_TFULL && i < WB_TFULL + TSTAGES) || (i >= WB_REMPTY && i < WB_REMPTY + RSTAGES);
+            mbar_init(&bars[i], eight ? 8 : 1);
+        }
         fence_mbar_init();
     }
     if (tid < 128) { csumA[tid] = 0.f; csumB[tid] = 0.f; }
@@ -686,13 +696,29 @@ k_deform_bwd_weights(WArgs args)
     tc_fence_after();
     const uint32_t tmem = tmem_slot;
 
-    if (warp == 8) {
+    if (warp == 9) {
+        // ===== producer ====================================================================================
+        if (lane == 0) {
+            uint32_t g = 0;
+            const uint32_t bytes = (uint32_t)(rawA_f + rawB_f) * 4;
+            for (long long s = s_begin; s < s_end; ++s, ++g) {
+                const uint32_t slot = g % RSTAGES;
+                mbar_wait(&bars[WB_REMPTY + slot], ((g / RSTAGES) & 1) ^ 1);
+                mbar_expect_tx(&bars[WB_RFULL + slot], bytes);
+                float* dst = raw0 + (size_t)slot * raw_floats;
+                bulk_g2s(dst, J.A + (size_t)s * rawA_f, (uint32_t)rawA_f * 4, &bars[WB_RFULL + slot]);
+                if (rawB_f) bulk_g2s(dst + rawA_f, J.B + (size_t)s * rawB_f, (uint32_t)rawB_f * 4, &bars[WB_RFULL + slot]);
+            }
+        }
+        __syncwarp();
+    } else if (warp == 8) {
+        // ===== MMA issuer ==================================================================================
         if (lane == 0) {
             const uint32_t idesc = make_idesc_tf32(128, N16, 1, 1);
             uint32_t g = 0;
             for (long long s = s_begin; s < s_end; ++s, ++g) {
-                const uint32_t slot = g % WSTAGES;
-                mbar_wait(&bars[WB_FULL + slot], (g / WSTAGES) & 1);
+                const uint32_t slot = g % TSTAGES;
+                mbar_wait(&bars[WB_TFULL + slot], (g / TSTAGES) & 1);
                 tc_fence_after();
                 const float* Ah = sm + (size_t)slot * stage_floats;
                 const float* Al = Ah + 4096;
@@ -705,124 +731,104 @@ k_deform_bwd_weights(WArgs args)
                     mma_tf32_ss(tmem, desc_mn32(Ah, WK, p, 0), desc_mn32(Bl, WK, p, 0), idesc, 1);
                     mma_tf32_ss(tmem, desc_mn32(Ah, WK, p, 0), desc_mn32(Bh, WK, p, 0), idesc, 1);
                 }
-                mma_commit(&bars[WB_EMPTY + slot]);
+                mma_commit(&bars[WB_TEMPTY + slot]);
             }
             mma_commit(&bars[WB_DONE]);
         }
         __syncwarp();
     } else {
-        // ---- staging ------------------------------------------------------------------------------------------
-        // Blocked (scratch) operands: a warp instruction covers 4 column groups x 8 rows = four 128-byte runs; the
-        // column group of a thread is the same in every pass and stage (its column sums stay in registers).
-        // Row-major operands (g_o: ld = 1, 3, 4, 48, P valid rows) take the checked path.
+        // ===== staging =====================================================================================
+        // A warp instruction covers 4 column groups x 8 rows; a thread's column group is the same in every pass
+        // and stage, so its column sums (bias gradients) stay in registers.
         const int gprB = nblkB * 8;                                 // float4 groups per staged B row (8, 16 or 32)
         const int nrb = gprB >> 3;                                  // B float4s per thread per stage (1, 2 or 4)
         const int sub = lane >> 3, row8 = lane & 7;
-        int cgA, cgB, rowA[4], rowB[4];
-        {
-            const int u0 = warp * 4 + sub;
-            cgA = u0;
+        const int u0 = warp * 4 + sub;
+        const int cgA = u0;
+        int cgB, rowA[4], rowB[4];
 #pragma unroll
-            for (int i = 0; i < 4; ++i) rowA[i] = i * 8 + row8;
-            if (J.blkB) {
-                cgB = u0 % gprB;
+        for (int i = 0; i < 4; ++i) rowA[i] = i * 8 + row8;
+        if (J.blkB) {
+            cgB = u0 % gprB;
 #pragma unroll
-                for (int i = 0; i < 4; ++i) rowB[i] = (((i * 32 + u0) / gprB) * 8 + row8) & (WK - 1);
-            } else {
-                cgB = tid % gprB;
+            for (int i = 0; i < 4; ++i) rowB[i] = (((i * 32 + u0) / gprB) * 8 + row8) & (WK - 1);
+        } else {
+            cgB = tid % gprB;
 #pragma unroll
-                for (int i = 0; i < 4; ++i) rowB[i] = (tid / gprB + (256 / gprB) * i) & (WK - 1);
-            }
+            for (int i = 0; i < 4; ++i) rowB[i] = (tid / gprB + (256 / gprB) * i) & (WK - 1);
         }
-        if (!J.blkA) { cgA = tid & 31;
-#pragma unroll
-            for (int i = 0; i < 4; ++i) rowA[i] = (tid >> 5) + 8 * i; }
         const bool onA = cgA * 4 < J.ma, onB = cgB * 4 < J.nb;
         const bool wantA = J.biasA != nullptr, wantB = J.biasB != nullptr;
         int oA[4], oB[4];
 #pragma unroll
         for (int i = 0; i < 4; ++i) { oA[i] = tile32_off(rowA[i], cgA * 4, WK); oB[i] = tile32_off(rowB[i], cgB * 4, WK); }
         float sa[4] = {0.f, 0.f, 0.f, 0.f}, sb[4] = {0.f, 0.f, 0.f, 0.f};
-        constexpr int PF = 2;                                      // register prefetch depth (global latency ~1 us)
-        float4 va[PF][4], vb[PF][4];
         const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
-        auto issue = [&](long long s, float4 (&a4)[4], float4 (&b4)[4]) {
-            const size_t tile = (size_t)(s >> 2);                  // 128-row tile, 32-row quarter
-            const int r0 = (int)(s & 3) * WK;
-            if (J.blkA) {
-                const float* q = J.A + tile * 128 * J.lda + (size_t)(cgA * 128 + r0) * 4;
+        float4 vbn[4] = {z4, z4, z4, z4};                           // row-major B: one stage of register prefetch
+        auto issueB = [&](long long s) {
 #pragma unroll
-                for (int i = 0; i < 4; ++i) a4[i] = onA ? __ldcs(reinterpret_cast<const float4*>(q + rowA[i] * 4)) : z4;
-            } else {
-#pragma unroll
-                for (int i = 0; i < 4; ++i) a4[i] = load4(J.A, J.lda, s * WK + rowA[i], cgA * 4, J.ma, J.rowsA);
-            }
-            if (J.blkB) {
-                const float* q = J.B + tile * 128 * J.ldb + (size_t)(cgB * 128 + r0) * 4;
-#pragma unroll
-                for (int i = 0; i < 4; ++i) b4[i] = (i < nrb && onB) ? __ldcs(reinterpret_cast<const float4*>(q + rowB[i] * 4)) : z4;
-            } else {
-#pragma unroll
-                for (int i = 0; i < 4; ++i) b4[i] = (i < nrb) ? load4(J.B, J.ldb, s * WK + rowB[i], cgB * 4, J.nb, J.rowsB) : z4;
-            }
+            for (int i = 0; i < 4; ++i) vbn[i] = (i < nrb) ? load4(J.B, J.ldb, s * WK + rowB[i], cgB * 4, J.nb, J.rowsB) : z4;
         };
-#pragma unroll
-        for (int u = 0; u < PF; ++u) {
-            if (s_begin + u < s_end) issue(s_begin + u, va[u], vb[u]);
-        }
+        if (!J.blkB && s_begin < s_end) issueB(s_begin);
         uint32_t g = 0;
-        for (long long s0 = s_begin; s0 < s_end; s0 += PF) {
+        for (long long s = s_begin; s < s_end; ++s, ++g) {
+            const uint32_t rslot = g % RSTAGES, tslot = g % TSTAGES;
+            const float* rawA = raw0 + (size_t)rslot * raw_floats;
+            const float* rawB = rawA + rawA_f;
+            float4 va[4], vb[4];
+            mbar_wait(&bars[WB_RFULL + rslot], (g / RSTAGES) & 1);
 #pragma unroll
-            for (int u = 0; u < PF; ++u) {
-                const long long s = s0 + u;
-                if (s >= s_end) break;
-                const uint32_t slot = g % WSTAGES;
-                mbar_wait(&bars[WB_EMPTY + slot], ((g / WSTAGES) & 1) ^ 1);
-                float* Ah = sm + (size_t)slot * stage_floats;
-                float* Bh = Ah + 8192;
-                const int lofsB = nblkB * 1024;
+            for (int i = 0; i < 4; ++i) va[i] = onA ? *reinterpret_cast<const float4*>(rawA + (cgA * 32 + rowA[i]) * 4) : z4;
+            if (J.blkB) {
 #pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    const float4 v = va[u][i];
-                    float4 hi, lw;
-                    split_tf32_rn(v.x, hi.x, lw.x); split_tf32_rn(v.y, hi.y, lw.y);
-                    split_tf32_rn(v.z, hi.z, lw.z); split_tf32_rn(v.w, hi.w, lw.w);
-                    if (wantA) { sa[0] += v.x; sa[1] += v.y; sa[2] += v.z; sa[3] += v.w; }
-                    *reinterpret_cast<float4*>(Ah + oA[i]) = hi;
-                    *reinterpret_cast<float4*>(Ah + 4096 + oA[i]) = lw;
-                }
+                for (int i = 0; i < 4; ++i) vb[i] = (i < nrb && onB) ? *reinterpret_cast<const float4*>(rawB + (cgB * 32 + rowB[i]) * 4) : z4;
+            } else {
 #pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    if (i < nrb) {
-                        const float4 v = vb[u][i];
-                        float4 hi, lw;
-                        split_tf32_rn(v.x, hi.x, lw.x); split_tf32_rn(v.y, hi.y, lw.y);
-                        split_tf32_rn(v.z, hi.z, lw.z); split_tf32_rn(v.w, hi.w, lw.w);
-                        if (wantB) { sb[0] += v.x; sb[1] += v.y; sb[2] += v.z; sb[3] += v.w; }
-                        *reinterpret_cast<float4*>(Bh + oB[i]) = hi;
-                        *reinterpret_cast<float4*>(Bh + lofsB + oB[i]) = lw;
-                    }
-                }
-                if (s + PF < s_end) issue(s + PF, va[u], vb[u]);
-                fence_async_smem();
-                __syncwarp();
-                if (lane == 0) mbar_arrive(&bars[WB_FULL + slot]);
-                ++g;
+                for (int i = 0; i < 4; ++i) vb[i] = vbn[i];
+                if (s + 1 < s_end) issueB(s + 1);
             }
+            float4 ahi[4], alo[4], bhi[4], blo[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                split_tf32_rn(va[i].x, ahi[i].x, alo[i].x); split_tf32_rn(va[i].y, ahi[i].y, alo[i].y);
+                split_tf32_rn(va[i].z, ahi[i].z, alo[i].z); split_tf32_rn(va[i].w, ahi[i].w, alo[i].w);
+                if (wantA) { sa[0] += va[i].x; sa[1] += va[i].y; sa[2] += va[i].z; sa[3] += va[i].w; }
+                split_tf32_rn(vb[i].x, bhi[i].x, blo[i].x); split_tf32_rn(vb[i].y, bhi[i].y, blo[i].y);
+                split_tf32_rn(vb[i].z, bhi[i].z, blo[i].z); split_tf32_rn(vb[i].w, bhi[i].w, blo[i].w);
+                if (wantB) { sb[0] += vb[i].x; sb[1] += vb[i].y; sb[2] += vb[i].z; sb[3] += vb[i].w; }
+            }
+            __syncwarp();                                            // every lane has consumed its raw values
+            if (lane == 0) mbar_arrive(&bars[WB_REMPTY + rslot]);
+            mbar_wait(&bars[WB_TEMPTY + tslot], ((g / TSTAGES) & 1) ^ 1);
+            float* Ah = sm + (size_t)tslot * stage_floats;
+            float* Bh = Ah + 8192;
+            const int lofsB = nblkB * 1024;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                *reinterpret_cast<float4*>(Ah + oA[i]) = ahi[i];
+                *reinterpret_cast<float4*>(Ah + 4096 + oA[i]) = alo[i];
+                if (i < nrb) {
+                    *reinterpret_cast<float4*>(Bh + oB[i]) = bhi[i];
+                    *reinterpret_cast<float4*>(Bh + lofsB + oB[i]) = blo[i];
+                }
+            }
+            fence_async_smem();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&bars[WB_TFULL + tslot]);
         }
         // ---- bias gradients ------------------------------------------------------------------------------------
-        if (J.biasA) {
+        if (wantA && onA) {
 #pragma unroll
             for (int u = 0; u < 4; ++u) atomicAdd(&csumA[cgA * 4 + u], sa[u]);
         }
-        if (J.biasB) {
+        if (wantB && onB) {
 #pragma unroll
-            for (int u = 0; u < 4; ++u) if (cgB * 4 + u < 128) atomicAdd(&csumB[cgB * 4 + u], sb[u]);
+            for (int u = 0; u < 4; ++u) atomicAdd(&csumB[cgB * 4 + u], sb[u]);
         }
         asm volatile("bar.sync 1, 256;" ::: "memory");
         if (tid < 128) {
-            if (J.biasA && tid < J.ma) atomicAdd(&J.biasA[tid], csumA[tid]);
-            if (J.biasB && tid < J.nb) atomicAdd(&J.biasB[tid], csumB[tid]);
+            if (wantA && tid < J.ma) atomicAdd(&J.biasA[tid], csumA[tid]);
+            if (wantB && tid < J.nb) atomicAdd(&J.biasB[tid], csumB[tid]);
         }
         // ---- accumulator -> global (+=) ----------------------------------------------------------------------------
         mbar_wait(&bars[WB_DONE], 0);
@@ -936,12 +942,12 @@ int backward(const Layout& lo, const FdgsDeformBackward* a, const float* packed,
         const int h = plan.heads[j];
         const int NO = head_out(h);
         wa.j[nj] = WJob{io.S_GZ[j], Wn, Wn, (int)plan.Pp, io.S_H, Wn, Wn, (int)plan.Pp, dw1[h], Wn, 0, a->d_head_b1[h], nullptr, 1, 1, 1};
-        cost[nj++] = 2.0 * Wn;
+        cost[nj++] = 1.0;
         wa.j[nj] = WJob{io.S_RZ[j], Wn, Wn, (int)plan.Pp, gsrc[h], NO, NO, a->P, a->d_head_w2[h], Wn, 1, nullptr, a->d_head_b2[h], 1, 1, 0};
-        cost[nj++] = Wn + NO + 16.0;
+        cost[nj++] = NO > 4 ? 0.85 : 0.8;       // per-stage cost is instruction-, not byte-bound (measured)
     }
     wa.j[nj] = WJob{io.S_GH, Wn, Wn, (int)plan.Pp, io.S_F, F, F, (int)plan.Pp, a->d_trunk_w[0], F, 0, a->d_trunk_b[0], nullptr, 1, 1, 1};
-    cost[nj++] = Wn + F + 16.0;
+    cost[nj++] = 0.65;
     wa.njobs = nj; wa.rows = plan.Pp;
     // distribute the SMs over the jobs in proportion to the bytes they stream
     double tot = 0; for (int i = 0; i < nj; ++i) tot += cost[i];
@@ -955,7 +961,7 @@ int backward(const Layout& lo, const FdgsDeformBackward* a, const float* packed,
     }
     for (int i = 0; used < sm_count() && i < nj; i += 2) if (wa.j[i].slices < nst) { wa.j[i].slices++; used++; }
     const int nblk_max = (Wn + 31) / 32;
-    const size_t wsm = (size_t)WSTAGES * (2 * 4096 + 2 * nblk_max * 1024) * 4 + 1024;
+    const size_t wsm = ((size_t)TSTAGES * (2 * 4096 + 2 * nblk_max * 1024) + (size_t)RSTAGES * (64 * Wn)) * 4 + 1024;
     FDGS_CUDA(cudaFuncSetAttribute(k_deform_bwd_weights, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wsm));
     { FDGS_PROF("k_deform_bwd_weights", stream);
     k_deform_bwd_weights<<<used, W_THREADS, wsm, stream>>>(wa);

@@ -37,9 +37,9 @@ __device__ __forceinline__ void split_tf32(float x, float& hi, float& lo) {
 // the tensor core's truncation of its inputs (measured, tools/umma_probe.cu) is a no-op and the dropped
 // remainder is <= 2^-24 |x|: a 3-pass product is FP32-accurate.
 __device__ __forceinline__ float rna_tf32(float x) {
-    uint32_t u;
-    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(x));
-    return __uint_as_float(u);
+    // cvt.rna.tf32.f32 is emulated on sm_100a (IADD 0x1000, |x| < inf test, select, mask = 4 instructions); the
+    // inf/nan guard is dropped here: add half an ulp of the 10-bit mantissa to the magnitude, then truncate.
+    return __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xFFFFE000u);
 }
 __device__ __forceinline__ void split_tf32_rn(float x, float& hi, float& lo) {
     hi = rna_tf32(x);
