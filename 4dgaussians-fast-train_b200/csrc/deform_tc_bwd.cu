@@ -473,27 +473,39 @@ k_deform_bwd_data(Layout lo, Plan plan, Smem sp, Net net, IO io, const float* __
         const int col0 = hf * NH;
         uint32_t ph_acc = 0, ph_grh = 0, ph_gf = 0;
         const int C = lo.C, CH = C >> 1;
+        // sampler mapping (see below): LP lanes per point, IPT channel quads per lane, PPW points per warp
+        const int items = F >> 2;
+        const int LP = (items & 7) == 0 ? 8 : 4, IPT = items / LP, PPW = 32 / LP, SPASS = TP / (8 * PPW);
+        const int sg = lane / LP, sq = lane % LP;
         PT_DECL
         for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
             const int p = tile * TP + row;
             const bool valid = p < io.P;
-            float q[4] = {0.f, 0.f, 0.f, 0.f};
-            if (valid) point_coords(lo, io.xyz, p, 0.f, q);
             // ---- HexPlane sampling -> feat tile (hi / lo) + scratch ----------------------------------------
-            for (int l = 0; l < lo.L; ++l)
-                for (int cc = 0; cc < CH; cc += 4) {
-                    const int c0 = hf * CH + cc;
+            // Sampler mapping: LP adjacent lanes share one point and take consecutive channel quads, so a warp-wide
+            // gather touches 32/LP points x (64-byte taps) instead of 32 unrelated lines (the L1 tag stage, one line
+            // per cycle, bounded the old thread-per-point mapping).
+            for (int pass = 0; pass < SPASS; ++pass) {
+                const int srow = pass * (8 * PPW) + warp * PPW + sg;
+                const int sp_ = tile * TP + srow;
+                const bool sval = sp_ < io.P;
+                float q[4] = {0.f, 0.f, 0.f, 0.f};
+                if (sval) point_coords(lo, io.xyz, sp_, 0.f, q);
+                for (int it = 0; it < IPT; ++it) {
+                    const int item = sq + it * LP;
+                    const int l = (item * 4) / C, c0 = (item * 4) % C;
                     float prod[4] = {0.f, 0.f, 0.f, 0.f};
-                    if (valid) sample_level<4>(lo, l, q, packed, trow, c0, prod);
+                    if (sval) sample_level<4>(lo, l, q, packed, trow, c0, prod);
                     float4 hi, lw;
                     split_tf32_rn(prod[0], hi.x, lw.x); split_tf32_rn(prod[1], hi.y, lw.y);
                     split_tf32_rn(prod[2], hi.z, lw.z); split_tf32_rn(prod[3], hi.w, lw.w);
-                    const int o = tile_off(row, l * C + c0, 128);
+                    const int o = tile_off(srow, item * 4, 128);
                     *reinterpret_cast<float4*>(F_hi + o) = hi;
                     *reinterpret_cast<float4*>(F_lo + o) = lw;
-                    __stcs(reinterpret_cast<float4*>(io.S_F + (size_t)tile * TP * F + (row >> 5) * 32 * F + (((l * C + c0) >> 2) * 32 + (row & 31)) * 4),
+                    __stcs(reinterpret_cast<float4*>(io.S_F + (size_t)tile * TP * F + (srow >> 5) * 32 * F + (item * 32 + (srow & 31)) * 4),
                            make_float4(prod[0], prod[1], prod[2], prod[3]));
                 }
+            }
             fence_async_smem();
             epi_bar();
             if (tid == 0) mbar_arrive(&bars[B_FEATFULL]);
@@ -589,30 +601,49 @@ k_deform_bwd_data(Layout lo, Plan plan, Smem sp, Net net, IO io, const float* __
             mbar_wait(&bars[B_GFFULL], ph_gf); ph_gf ^= 1;
             tc_fence_after();
             PT(7)
-            float dq[3] = {0.f, 0.f, 0.f};
+            // accumulator rows (TMEM lane = point) -> shared memory, so that the sampler mapping can read any point
+            float* GF = HS_hi;                                       // every MMA that read relu(h) has completed
             for (int l = 0; l < lo.L; ++l)
                 for (int cc = 0; cc < CH; cc += 4) {
-                    const int c0 = hf * CH + cc;
+                    const int c0 = l * C + hf * CH + cc;
                     uint32_t v[4];
-                    tmem_ld4(lane_base + TM_ACC + (uint32_t)(l * C + c0), v);      // warp-uniform address: all lanes execute
+                    tmem_ld4(lane_base + TM_ACC + (uint32_t)c0, v);                // warp-uniform address: all lanes execute
                     tmem_wait_ld();
-                    const float df[4] = {__uint_as_float(v[0]), __uint_as_float(v[1]), __uint_as_float(v[2]), __uint_as_float(v[3])};
-                    if (valid) sample_bwd4(lo, l, q, packed, trow, gpacked, gtrow, c0, df, dq);
+                    *reinterpret_cast<float4*>(GF + tile_off(row, c0, 128)) =
+                        make_float4(__uint_as_float(v[0]), __uint_as_float(v[1]), __uint_as_float(v[2]), __uint_as_float(v[3]));
                 }
-            PT(8)
-            red[(hf * TP + row) * 3 + 0] = dq[0];
-            red[(hf * TP + row) * 3 + 1] = dq[1];
-            red[(hf * TP + row) * 3 + 2] = dq[2];
             tc_fence_before();
             epi_bar();
-            if (hf == 0 && valid) {
+            for (int pass = 0; pass < SPASS; ++pass) {
+                const int srow = pass * (8 * PPW) + warp * PPW + sg;
+                const int sp_ = tile * TP + srow;
+                const bool sval = sp_ < io.P;
+                float q[4] = {0.f, 0.f, 0.f, 0.f};
+                if (sval) point_coords(lo, io.xyz, sp_, 0.f, q);
+                float dq[3] = {0.f, 0.f, 0.f};
+                for (int it = 0; it < IPT; ++it) {
+                    const int item = sq + it * LP;
+                    const int l = (item * 4) / C, c0 = (item * 4) % C;
+                    const float4 d4 = *reinterpret_cast<const float4*>(GF + tile_off(srow, item * 4, 128));
+                    const float df[4] = {d4.x, d4.y, d4.z, d4.w};
+                    if (sval) sample_bwd4(lo, l, q, packed, trow, gpacked, gtrow, c0, df, dq);
+                }
 #pragma unroll
                 for (int a = 0; a < 3; ++a) {
-                    const float mx = lo.aabb[a], mn = lo.aabb[3 + a];
-                    io.d_xyz[3 * (size_t)p + a] = (red[row * 3 + a] + red[(TP + row) * 3 + a]) * (2.0f / (mn - mx));
+                    dq[a] += __shfl_xor_sync(0xffffffffu, dq[a], 1);
+                    dq[a] += __shfl_xor_sync(0xffffffffu, dq[a], 2);
+                    if (LP == 8) dq[a] += __shfl_xor_sync(0xffffffffu, dq[a], 4);
+                }
+                if (sq == 0 && sval) {
+#pragma unroll
+                    for (int a = 0; a < 3; ++a) {
+                        const float mx = lo.aabb[a], mn = lo.aabb[3 + a];
+                        io.d_xyz[3 * (size_t)sp_ + a] = dq[a] * (2.0f / (mn - mx));
+                    }
                 }
             }
-            epi_bar();          // `red` and the feat/relu(h) buffers are free again
+            PT(8)
+            epi_bar();          // the feat / relu(h) / g_feat buffer is free again
             PT(9)
         }
         PT_PRINT
