@@ -32,7 +32,8 @@ constexpr int NEPI = 256;
 struct Plan {
     int Wn, F, nheads;
     int heads[FDGS_NUM_HEADS];     // active heads that received an upstream gradient
-    int nchunks_main;              // chunks of 32*Wn floats per tile (W0, then W1_j and W1_j^T per head)
+    int nchunks_main;              // chunks of 32*Wn floats per tile: W0, then per head W1_j, W2_j^T (K padded to 16), W1_j^T
+    int k2chunks[FDGS_NUM_HEADS];  // W2_j^T chunks of plan slot j: 1 (out <= 4) or 3 (out = 48)
     int nchunks_gf;                // chunks of 32*F floats (W0^T)
     long long wprep_floats;
     // scratch (floats), Pp = ntiles * 128 rows each
@@ -50,6 +51,10 @@ static inline Plan make_plan(const Layout& lo, int P, const bool has_grad[FDGS_N
     for (int h = 0; h < FDGS_NUM_HEADS; ++h) if (((lo.head_mask >> h) & 1) && has_grad[h]) p.heads[p.nheads++] = h;
     for (int h = p.nheads; h < FDGS_NUM_HEADS; ++h) p.heads[h] = 0;
     p.nchunks_main = lo.F / KCH + p.nheads * 2 * (lo.Wn / KCH);
+    for (int j = 0; j < FDGS_NUM_HEADS; ++j) {
+        p.k2chunks[j] = j < p.nheads ? (head_out(p.heads[j]) + KCH - 1) / KCH : 0;
+        p.nchunks_main += p.k2chunks[j];
+    }
     p.nchunks_gf = lo.Wn / KCH;
     p.wprep_floats = (long long)p.nchunks_main * 32 * lo.Wn + (long long)p.nchunks_gf * 32 * lo.F;
     const long long ntiles = ((long long)P + TP - 1) / TP;
@@ -71,8 +76,8 @@ static inline Plan make_plan(const Layout& lo, int P, const bool has_grad[FDGS_N
 // ---- weight formatting ----------------------------------------------------------------------------------------
 // A section is one [N rows][K] operand stored as K/16 chunks; a chunk = hi tile then lo tile, each the canonical
 // K-major tile [4 column groups][N][4] (umma.cuh).  element(n, k) = T ? W[k*ld + n] : W[n*ld + k].
-struct PrepSec { const float* W; int ld, N, K, T; long long off; };
-struct PrepArgs { PrepSec s[2 + 2 * FDGS_NUM_HEADS]; int nsec; };
+struct PrepSec { const float* W; int ld, N, K, T; long long off; int Kvalid; };   // columns k >= Kvalid are zero padding
+struct PrepArgs { PrepSec s[2 + 3 * FDGS_NUM_HEADS]; int nsec; };
 
 __global__ void k_deform_wprep_bwd(PrepArgs a, float* __restrict__ out) {
     for (int si = 0; si < a.nsec; ++si) {
@@ -80,8 +85,8 @@ __global__ void k_deform_wprep_bwd(PrepArgs a, float* __restrict__ out) {
         const int total = s.N * s.K;
         for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
             int n, k; float w;
-            if (s.T) { k = i / s.N; n = i % s.N; w = s.W[(size_t)k * s.ld + n]; }     // coalesced read either way
-            else     { n = i / s.K; k = i % s.K; w = s.W[(size_t)n * s.ld + k]; }
+            if (s.T) { k = i / s.N; n = i % s.N; w = k < s.Kvalid ? s.W[(size_t)k * s.ld + n] : 0.f; }     // coalesced read either way
+            else     { n = i / s.K; k = i % s.K; w = k < s.Kvalid ? s.W[(size_t)n * s.ld + k] : 0.f; }
             float hi, lo;
             split_tf32_rn(w, hi, lo);
             float* c = out + s.off + (long long)(k / KCH) * 32 * s.N;
@@ -122,7 +127,7 @@ static inline Smem make_smem(const Layout& lo) {
     int o = 0;
     s.off_hs_hi = o; o += al(128 * Wn);        // relu(h) hi, K-major canonical tile; feat hi aliases its head
     s.off_hs_lo = o; o += al(128 * Wn);
-    s.off_w2 = o; o += al(60 * Wn);            // 59 rows + 1 pad row (small heads read up to 4 rows)
+    s.off_w2 = o;                              // (the output layers run on the tensor cores: no W2 copy)
     s.off_b0 = o; o += al(Wn);
     s.off_b1 = o; o += al(FDGS_NUM_HEADS * Wn);
     s.off_red = o; o += al(2 * 128 * 3);
@@ -152,7 +157,7 @@ __device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, 256;" ::: 
 // TMEM column map (512 columns): accumulator (trunk h, head z, g_feat), g_z / g_h hi, lo, g_relu_h accumulator
 constexpr uint32_t TM_ACC = 0, TM_GHI = 128, TM_GLO = 256, TM_GRH = 384;
 constexpr int B_WFULL = 0, B_WEMPTY = 8, B_FEATFULL = 16, B_ACCFULL = 17, B_HFULL = 18, B_GZFULL = 19, B_GRHFULL = 20,
-              B_GHFULL = 21, B_GFFULL = 22, B_COUNT = 23;
+              B_GHFULL = 21, B_GFFULL = 22, B_GOFULL = 23, B_COUNT = 24;
 
 __device__ __forceinline__ int w2_row0(int h) { return h == 0 ? 0 : h == 1 ? 3 : h == 2 ? 6 : h == 3 ? 10 : 11; }
 
@@ -249,59 +254,77 @@ __device__ __forceinline__ void sample_bwd4(const Layout& lo, int l, const float
     }
 }
 
-// ---- head epilogue: z = relu(acc + b1); g_z = (g_o W2)[z > 0]; scratch stores; g_z hi/lo -> TMEM ---------------------
-// NOP = compile-time bound on the head's output width (4 for dx/ds/dr/do, 48 for dshs); NH = columns per thread.
-template <int NOP, int NH, int WN>
-__device__ __forceinline__ void head_epilogue(uint32_t lane_base, int col0, int NO, bool valid, const float* __restrict__ gsrc,
-                                              const float* __restrict__ b1s, const float* __restrict__ w2s,
-                                              float* __restrict__ rz_row, float* __restrict__ gz_row) {
-    float go[NOP];
+// ---- head epilogue, pass 1: z = relu(acc + b1) -> scratch, ReLU gate bits; upstream gradient g_o hi/lo -> TMEM --------
+// The thread's g_o columns are [hf*24, hf*24+24) of 48 for dshs, and all 8 (zero padded) on the hf == 0 warps otherwise.
+template <int NH>
+__device__ __forceinline__ void head_pass1(uint32_t lane_base, int col0, int hf, int NO, bool valid, const float* __restrict__ gsrc,
+                                           const float* __restrict__ b1s, float* __restrict__ rz_row, uint32_t (&zgate)[NH / 32 + 1]) {
+    if (NO == 48) {
 #pragma unroll
-    for (int o = 0; o < NOP; ++o) go[o] = 0.f;
-    if (valid) {
-        if (NOP == 48) {
-#pragma unroll
-            for (int o = 0; o < 48; o += 4) {
-                const float4 v = *reinterpret_cast<const float4*>(gsrc + o);
-                go[o] = v.x; go[o + 1] = v.y; go[o + 2] = v.z; go[o + 3] = v.w;
+        for (int c = 0; c < 24; c += 8) {
+            float4 v0 = make_float4(0.f, 0.f, 0.f, 0.f), v1 = v0;
+            if (valid) {
+                v0 = *reinterpret_cast<const float4*>(gsrc + hf * 24 + c);
+                v1 = *reinterpret_cast<const float4*>(gsrc + hf * 24 + c + 4);
             }
-        } else {
+            const float x[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+            uint32_t hi[8], lw[8];
 #pragma unroll
-            for (int o = 0; o < NOP; ++o) if (o < NO) go[o] = gsrc[o];
+            for (int j = 0; j < 8; ++j) { float a, b; split_tf32_rn(x[j], a, b); hi[j] = __float_as_uint(a); lw[j] = __float_as_uint(b); }
+            tmem_st8(lane_base + TM_GHI + hf * 24 + c, hi);
+            tmem_st8(lane_base + TM_GLO + hf * 24 + c, lw);
         }
+    } else if (hf == 0) {
+        uint32_t hi[8], lw[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const float x = (valid && j < NO) ? gsrc[j] : 0.f;
+            float a, b; split_tf32_rn(x, a, b); hi[j] = __float_as_uint(a); lw[j] = __float_as_uint(b);
+        }
+        tmem_st8(lane_base + TM_GHI, hi);
+        tmem_st8(lane_base + TM_GLO, lw);
     }
-#pragma unroll 1
+#pragma unroll
+    for (int c0 = 0; c0 < NH; c0 += 32) {
+        uint32_t v[32];
+        tmem_ld32(lane_base + TM_ACC + col0 + c0, v);
+        tmem_wait_ld();
+        uint32_t m = 0;
+#pragma unroll
+        for (int j = 0; j < 32; j += 4) {
+            float z[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                z[u] = fmaxf(__uint_as_float(v[j + u]) + b1s[col0 + c0 + j + u], 0.f);
+                m |= (z[u] > 0.f ? 1u : 0u) << (j + u);
+            }
+            __stcs(reinterpret_cast<float4*>(rz_row + ((col0 + c0 + j) >> 2) * 128), make_float4(z[0], z[1], z[2], z[3]));
+        }
+        zgate[c0 / 32] = m;
+    }
+    tmem_wait_st();
+}
+
+// ---- pass 2: g_z = (g_o W2)[z > 0] (accumulator) -> scratch, hi/lo -> TMEM (A operand of g_relu_h += g_z W1) -----------
+template <int NH>
+__device__ __forceinline__ void head_pass2(uint32_t lane_base, int col0, float* __restrict__ gz_row, const uint32_t (&zgate)[NH / 32 + 1]) {
+#pragma unroll
     for (int c0 = 0; c0 < NH; c0 += 16) {
-        uint32_t v[16];
+        uint32_t v[16], hi[16], lw[16];
         tmem_ld16(lane_base + TM_ACC + col0 + c0, v);
         tmem_wait_ld();
-        float z[16], gr[16];
-#pragma unroll
-        for (int j = 0; j < 16; ++j) { z[j] = fmaxf(__uint_as_float(v[j]) + b1s[col0 + c0 + j], 0.f); gr[j] = 0.f; }
-#pragma unroll
-        for (int o = 0; o < NOP; ++o) {
-            const float g = go[o];
-            const float* w = w2s + o * WN + col0 + c0;
-#pragma unroll
-            for (int j = 0; j < 16; j += 4) {
-                const float4 w4 = *reinterpret_cast<const float4*>(w + j);
-                gr[j] = fmaf(g, w4.x, gr[j]); gr[j + 1] = fmaf(g, w4.y, gr[j + 1]);
-                gr[j + 2] = fmaf(g, w4.z, gr[j + 2]); gr[j + 3] = fmaf(g, w4.w, gr[j + 3]);
-            }
-        }
-        uint32_t hi[16], lw[16];
+        const uint32_t m = zgate[c0 / 32] >> (c0 & 31);
+        float g[16];
 #pragma unroll
         for (int j = 0; j < 16; ++j) {
-            gr[j] = z[j] > 0.f ? gr[j] : 0.f;
+            g[j] = ((m >> j) & 1u) ? __uint_as_float(v[j]) : 0.f;
             float a, b;
-            split_tf32_rn(gr[j], a, b);
+            split_tf32_rn(g[j], a, b);
             hi[j] = __float_as_uint(a); lw[j] = __float_as_uint(b);
         }
 #pragma unroll
-        for (int j = 0; j < 16; j += 4) {
-            __stcs(reinterpret_cast<float4*>(rz_row + ((col0 + c0 + j) >> 2) * 128), make_float4(z[j], z[j + 1], z[j + 2], z[j + 3]));
-            __stcs(reinterpret_cast<float4*>(gz_row + ((col0 + c0 + j) >> 2) * 128), make_float4(gr[j], gr[j + 1], gr[j + 2], gr[j + 3]));
-        }
+        for (int j = 0; j < 16; j += 4)
+            __stcs(reinterpret_cast<float4*>(gz_row + ((col0 + c0 + j) >> 2) * 128), make_float4(g[j], g[j + 1], g[j + 2], g[j + 3]));
         tmem_st16(lane_base + TM_GHI + col0 + c0, hi);
         tmem_st16(lane_base + TM_GLO + col0 + c0, lw);
     }
@@ -320,7 +343,6 @@ k_deform_bwd_data(Layout lo, Plan plan, Smem sp, Net net, IO io, const float* __
     float* HS_lo = sm + sp.off_hs_lo;
     float* F_hi = HS_hi;                       // the feat tile lives in the head of the relu(h) buffers
     float* F_lo = HS_lo;
-    float* W2s = sm + sp.off_w2;
     float* B0s = sm + sp.off_b0;
     float* B1s = sm + sp.off_b1;
     float* red = sm + sp.off_red;
@@ -339,7 +361,6 @@ k_deform_bwd_data(Layout lo, Plan plan, Smem sp, Net net, IO io, const float* __
     }
     if (warp == 9) tmem_alloc(tmem_slot, 512);
     if (tid < NEPI) {
-        for (int i = tid; i < 60 * WN; i += NEPI) W2s[i] = 0.f;
         for (int i = tid; i < WN; i += NEPI) B0s[i] = net.b0[i];
     }
     __syncthreads();
@@ -348,7 +369,6 @@ k_deform_bwd_data(Layout lo, Plan plan, Smem sp, Net net, IO io, const float* __
             const int h = plan.heads[j];
             const int NO = head_out(h);
             for (int i = tid; i < WN; i += NEPI) B1s[h * WN + i] = net.b1[h][i];
-            for (int i = tid; i < NO * WN; i += NEPI) W2s[w2_row0(h) * WN + i] = net.w2[h][i];
         }
     }
     tc_fence_before();
@@ -379,7 +399,7 @@ k_deform_bwd_data(Layout lo, Plan plan, Smem sp, Net net, IO io, const float* __
         if (lane == 0) {
             const uint32_t idesc = make_idesc_tf32(128, WN, 0, 0);
             const uint32_t idesc_gf = make_idesc_tf32(128, F, 0, 0);
-            uint32_t g = 0, ph_feat = 0, ph_h = 0, ph_gz = 0, ph_gh = 0;
+            uint32_t g = 0, ph_feat = 0, ph_h = 0, ph_gz = 0, ph_gh = 0, ph_go = 0;
             for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
                 // trunk: ACC = feat . W0^T
                 mbar_wait(&bars[B_FEATFULL], ph_feat); ph_feat ^= 1;
@@ -420,6 +440,31 @@ k_deform_bwd_data(Layout lo, Plan plan, Smem sp, Net net, IO io, const float* __
                             mma_tf32_ss(tmem + TM_ACC, desc_kmajor(HS_hi, 128, k), desc_kmajor(bh, WN, ks * 8), idesc, 1);
                         }
                         mma_commit(&bars[B_WEMPTY + slot]);
+                    }
+                    mma_commit(&bars[B_ACCFULL]);
+                    // g_relu_z: ACC = g_o . W2       (A = g_o from TMEM, B = W2^T chunks, K padded to 8 / 48)
+                    mbar_wait(&bars[B_GOFULL], ph_go); ph_go ^= 1;
+                    tc_fence_after();
+                    {
+                        const int ksteps = head_out(plan.heads[i]) > 8 ? 6 : 1;
+                        for (int c = 0; c < plan.k2chunks[i]; ++c, ++g) {
+                            const uint32_t slot = g % S;
+                            mbar_wait(&bars[B_WFULL + slot], (g / S) & 1);
+                            tc_fence_after();
+                            const float* bh = ring + (size_t)slot * SLOT;
+                            const float* bl = bh + 16 * WN;
+#pragma unroll
+                            for (int ks = 0; ks < 2; ++ks) {
+                                if (c * 2 + ks < ksteps) {
+                                    const uint32_t k = (uint32_t)(c * KCH + ks * 8);
+                                    const int first = (c == 0 && ks == 0) ? 0 : 1;
+                                    mma_tf32_ts(tmem + TM_ACC, tmem + TM_GLO + k, desc_kmajor(bh, WN, ks * 8), idesc, first);
+                                    mma_tf32_ts(tmem + TM_ACC, tmem + TM_GHI + k, desc_kmajor(bl, WN, ks * 8), idesc, 1);
+                                    mma_tf32_ts(tmem + TM_ACC, tmem + TM_GHI + k, desc_kmajor(bh, WN, ks * 8), idesc, 1);
+                                }
+                            }
+                            mma_commit(&bars[B_WEMPTY + slot]);
+                        }
                     }
                     mma_commit(&bars[B_ACCFULL]);
                     // g_relu_h += g_z . W1          (A from TMEM, B = W1^T chunks)
@@ -556,10 +601,14 @@ k_deform_bwd_data(Layout lo, Plan plan, Smem sp, Net net, IO io, const float* __
                 // blocked scratch: [tile][row / 32][col / 4][row % 32][4]  ->  + (col >> 2) * 128
                 float* rz_row = io.S_RZ[i] + (size_t)tile * TP * WN + (row >> 5) * 32 * WN + (row & 31) * 4;
                 float* gz_row = io.S_GZ[i] + (size_t)tile * TP * WN + (row >> 5) * 32 * WN + (row & 31) * 4;
-                if (h == FDGS_HEAD_SHS)
-                    head_epilogue<48, NH, WN>(lane_base, col0, NO, valid, gsrc, B1s + h * WN, W2s + w2_row0(h) * WN, rz_row, gz_row);
-                else
-                    head_epilogue<4, NH, WN>(lane_base, col0, NO, valid, gsrc, B1s + h * WN, W2s + w2_row0(h) * WN, rz_row, gz_row);
+                uint32_t zgate[NH / 32 + 1];
+                head_pass1<NH>(lane_base, col0, hf, NO, valid, gsrc, B1s + h * WN, rz_row, zgate);
+                tc_fence_before();
+                epi_bar();
+                if (tid == 0) mbar_arrive(&bars[B_GOFULL]);        // z drained from the accumulator, g_o staged in TMEM
+                mbar_wait(&bars[B_ACCFULL], ph_acc); ph_acc ^= 1;  // accumulator = g_o . W2
+                tc_fence_after();
+                head_pass2<NH>(lane_base, col0, gz_row, zgate);
                 tc_fence_before();
                 epi_bar();
                 if (tid == 0) mbar_arrive(&bars[B_GZFULL]);
@@ -926,13 +975,16 @@ int backward(const Layout& lo, const FdgsDeformBackward* a, const float* packed,
     PrepArgs pa;
     int ns = 0;
     long long off = 0;
-    pa.s[ns++] = PrepSec{a->net.trunk_w[0], F, Wn, F, 0, off}; off += (long long)(F / KCH) * 32 * Wn;
+    pa.s[ns++] = PrepSec{a->net.trunk_w[0], F, Wn, F, 0, off, F}; off += (long long)(F / KCH) * 32 * Wn;
     for (int j = 0; j < plan.nheads; ++j) {
         const float* w1 = a->net.head_w1[plan.heads[j]];
-        pa.s[ns++] = PrepSec{w1, Wn, Wn, Wn, 0, off}; off += (long long)(Wn / KCH) * 32 * Wn;
-        pa.s[ns++] = PrepSec{w1, Wn, Wn, Wn, 1, off}; off += (long long)(Wn / KCH) * 32 * Wn;      // (n = h, k = z) = W1[z][h]
+        pa.s[ns++] = PrepSec{w1, Wn, Wn, Wn, 0, off, Wn}; off += (long long)(Wn / KCH) * 32 * Wn;
+        const int NO = head_out(plan.heads[j]);                                                       // (n = z, k = o) = W2[o][z]
+        pa.s[ns++] = PrepSec{a->net.head_w2[plan.heads[j]], Wn, Wn, plan.k2chunks[j] * KCH, 1, off, NO};
+        off += (long long)plan.k2chunks[j] * 32 * Wn;
+        pa.s[ns++] = PrepSec{w1, Wn, Wn, Wn, 1, off, Wn}; off += (long long)(Wn / KCH) * 32 * Wn;  // (n = h, k = z) = W1[z][h]
     }
-    pa.s[ns++] = PrepSec{a->net.trunk_w[0], F, F, Wn, 1, off}; off += (long long)(Wn / KCH) * 32 * F;  // (n = f, k = h) = W0[h][f]
+    pa.s[ns++] = PrepSec{a->net.trunk_w[0], F, F, Wn, 1, off, Wn}; off += (long long)(Wn / KCH) * 32 * F;  // (n = f, k = h) = W0[h][f]
     pa.nsec = ns;
     if (off != plan.wprep_floats) return FDGS_E_BADARG;
     { FDGS_PROF("k_deform_wprep_bwd", stream);
