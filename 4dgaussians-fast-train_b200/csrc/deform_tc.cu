@@ -255,26 +255,34 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
         const uint32_t lane_base = tmem + ((uint32_t)((warp & 3) * 32) << 16);
         const int col0 = hf * NH;
         uint32_t pf0 = 0, pf1 = 0;
-        const int C = lo.C, CH = C >> 1;
+        const int C = lo.C;
+        const int items = lo.F >> 2;
+        const int LP = (items & 7) == 0 ? 8 : 4, IPT = items / LP, PPW = 32 / LP, SPASS = TP / (8 * PPW);
+        const int sg = lane / LP, sq = lane % LP;
         for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
             const int p0 = tile * TP;
             const int p = p0 + row;
             // ---- HexPlane sampling -> feat tile (hi / lo) ---------------------------------------------------
-            {
-                float q[4];
-                if (p < io.P) point_coords(lo, io.xyz, p, 0.f, q);
-                for (int l = 0; l < lo.L; ++l)
-                    for (int cc = 0; cc < CH; cc += 4) {
-                        const int c0 = hf * CH + cc;
-                        float prod[4] = {0.f, 0.f, 0.f, 0.f};
-                        if (p < io.P) sample_level<4>(lo, l, q, packed, trow, c0, prod);
-                        float4 hi, lw;
-                        split_tf32_rn(prod[0], hi.x, lw.x); split_tf32_rn(prod[1], hi.y, lw.y);
-                        split_tf32_rn(prod[2], hi.z, lw.z); split_tf32_rn(prod[3], hi.w, lw.w);
-                        const int o = tile_off(row, l * C + c0, 128);
-                        *reinterpret_cast<float4*>(F_hi + o) = hi;
-                        *reinterpret_cast<float4*>(F_lo + o) = lw;
-                    }
+            // LP adjacent lanes share one point and take consecutive channel quads: a warp-wide gather then touches
+            // 32/LP points x 64-byte taps instead of 32 unrelated lines (the L1 tag stage serves one line per cycle).
+            for (int pass = 0; pass < SPASS; ++pass) {
+                const int srow = pass * (8 * PPW) + warp * PPW + sg;
+                const int sp_ = p0 + srow;
+                const bool sval = sp_ < io.P;
+                float q[4] = {0.f, 0.f, 0.f, 0.f};
+                if (sval) point_coords(lo, io.xyz, sp_, 0.f, q);
+                for (int it = 0; it < IPT; ++it) {
+                    const int item = sq + it * LP;
+                    const int l = (item * 4) / C, c0 = (item * 4) % C;
+                    float prod[4] = {0.f, 0.f, 0.f, 0.f};
+                    if (sval) sample_level<4>(lo, l, q, packed, trow, c0, prod);
+                    float4 hi, lw;
+                    split_tf32_rn(prod[0], hi.x, lw.x); split_tf32_rn(prod[1], hi.y, lw.y);
+                    split_tf32_rn(prod[2], hi.z, lw.z); split_tf32_rn(prod[3], hi.w, lw.w);
+                    const int o = tile_off(srow, item * 4, 128);
+                    *reinterpret_cast<float4*>(F_hi + o) = hi;
+                    *reinterpret_cast<float4*>(F_lo + o) = lw;
+                }
             }
             fence_async_smem();
             epi_bar();

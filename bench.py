@@ -175,7 +175,12 @@ def algorithmic_per_launch(kernel, s):
         "k_blend_bwd": ("hbm", R * 48.0 + HW * 20.0 + T * 8.0 + P * 44.0),
         "k_preprocess_bwd": ("hbm", P * (301.0 - 192 + 12 * M) + P * (64.0 + 12 * M)),
         "k_deform_fwd": ("tensor", mlp_fwd_flop),
+        "k_deform_fwd_tc": ("tensor", mlp_fwd_flop),
         "k_deform_bwd": ("tensor", 2.0 * mlp_fwd_flop),
+        # the MLP backward is 2x the forward FLOPs: one forward's worth of data gradients, one of weight gradients
+        # (the activation recompute inside k_deform_bwd_data is NOT counted as algorithmic work)
+        "k_deform_bwd_data": ("tensor", mlp_fwd_flop),
+        "k_deform_bwd_weights": ("tensor", mlp_fwd_flop),
     }
     return table.get(kernel)
 
