@@ -357,11 +357,14 @@ def main():
             if use_dist:
                 dist.all_reduce(fps_ms, op=dist.ReduceOp.MAX)
             extras["render_fps"] = round(3 * B / (float(fps_ms) * 1e-3), 2)
-        if L is not None and eff_rank == 0:
-            # per-kernel CUDA-event timing inside the library, on the launching stream
-            L.profile_enable(True)
+        if L is not None:
+            # per-kernel CUDA-event timing inside the library, on the launching stream.  Every rank runs the two
+            # iterations (they contain the gradient all-reduce, a collective); rank 0 alone records and reports.
+            if eff_rank == 0:
+                L.profile_enable(True)
             for _ in range(2):
                 step_resident()
+        if L is not None and eff_rank == 0:
             prof = L.profile_collect()
             L.profile_enable(False)
             P = cfg["P"]
