@@ -185,6 +185,15 @@ def algorithmic_per_launch(kernel, s):
     return table.get(kernel)
 
 
+# dram__bytes_read.sum + dram__bytes_write.sum per launch from the `ncu --set full` capture of this workload
+# (profiles/r01_ncu_full_summary.csv; P = 300k DyNeRF view).  Reported only for that workload.
+NCU_TRAFFIC_BYTES = {
+    "k_deform_bwd_data": 0.085441e9 + 1.858870e9, "k_deform_bwd_weights": 2.093587e9 + 0.004668e9,
+    "k_deform_fwd_tc": 0.075685e9 + 0.037721e9, "k_blend_bwd": 0.118472e9 + 0.004498e9, "k_blend_fwd": 0.081388e9 + 0.011688e9,
+    "k_tile_sort": 0.024414e9 + 0.026626e9, "k_preprocess": 0.066738e9 + 0.003318e9, "k_preprocess_bwd": 0.092924e9 + 0.037773e9,
+}
+
+
 def roofline_for(prof, shape, peaks):
     """prof: {kernel: (launches, total_ms)} from the in-library CUDA-event profiler."""
     if not prof:
@@ -205,7 +214,9 @@ def roofline_for(prof, shape, peaks):
     else:
         achieved, unit, peak = amount / sec / 1e12, "TFLOP/s", peaks["tensor"]
     return {"kernel": top, "bound": bound, "achieved": round(achieved, 3), "peak": peak, "unit": unit,
-            "frac": round(achieved / peak, 5), "traffic": None, "peak_source": peaks["src"],
+            "frac": round(achieved / peak, 5),
+            "traffic": NCU_TRAFFIC_BYTES.get(top) if (shape["P"] == 300000 and shape["Wn"] == 128) else None,
+            "peak_source": peaks["src"],
             "avg_launch_us": round(sec * 1e6, 2), "algorithmic_per_launch": amount}, per_kernel
 
 
