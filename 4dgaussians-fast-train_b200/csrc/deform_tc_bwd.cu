@@ -721,7 +721,8 @@ struct WArgs { WJob j[MAXJOBS]; int njobs; long long rows; };   // rows = Pp (mu
 constexpr int WK = 32;             // points per stage
 constexpr int TSTAGES = 2;         // formatted (hi/lo tile32) operand stages feeding the tensor core
 constexpr int RSTAGES = 3;         // raw FP32 stages filled by bulk async copies
-constexpr int W_THREADS = 320;     // 8 staging/epilogue warps + MMA warp + bulk-copy producer warp
+constexpr int NSW = 16;            // staging / epilogue warps
+constexpr int W_THREADS = (NSW + 2) * 32;   // + MMA warp + bulk-copy producer warp
 constexpr int WB_TFULL = 0, WB_TEMPTY = 2, WB_RFULL = 4, WB_REMPTY = 7, WB_DONE = 10, WB_COUNT = 11;
 
 __device__ __forceinline__ float4 load4(const float* __restrict__ base, int ld, long long r, int c, int ncols, long long nrows) {
@@ -765,18 +766,18 @@ k_deform_bwd_weights(WArgs args)
     if (tid == 0) {
         for (int i = 0; i < WB_COUNT; ++i) {
             const bool eight = (i >= WB_TFULL && i < WB_TFULL + TSTAGES) || (i >= WB_REMPTY && i < WB_REMPTY + RSTAGES);
-            mbar_init(&bars[i], eight ? 8 : 1);
+            mbar_init(&bars[i], eight ? NSW : 1);
         }
         fence_mbar_init();
     }
     if (tid < 128) { csumA[tid] = 0.f; csumB[tid] = 0.f; }
-    if (warp == 8) tmem_alloc(&tmem_slot, 128);
+    if (warp == NSW) tmem_alloc(&tmem_slot, 128);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = tmem_slot;
 
-    if (warp == 9) {
+    if (warp == NSW + 1) {
         // ===== producer ====================================================================================
         if (lane == 0) {
             uint32_t g = 0;
@@ -791,7 +792,7 @@ k_deform_bwd_weights(WArgs args)
             }
         }
         __syncwarp();
-    } else if (warp == 8) {
+    } else if (warp == NSW) {
         // ===== MMA issuer ==================================================================================
         if (lane == 0) {
             const uint32_t idesc = make_idesc_tf32(128, N16, 1, 1);
@@ -818,36 +819,47 @@ k_deform_bwd_weights(WArgs args)
         __syncwarp();
     } else {
         // ===== staging =====================================================================================
-        // A warp instruction covers 4 column groups x 8 rows; a thread's column group is the same in every pass
-        // and stage, so its column sums (bias gradients) stay in registers.
+        // NSW warps; a warp instruction covers 4 column groups x 8 rows; a thread's column group is the same in
+        // every pass and stage, so its column sums (bias gradients) stay in registers.
+        constexpr int NI = 1024 / (NSW * 32);                        // float4s of A per thread per stage
         const int gprB = nblkB * 8;                                 // float4 groups per staged B row (8, 16 or 32)
-        const int nrb = gprB >> 3;                                  // B float4s per thread per stage (1, 2 or 4)
         const int sub = lane >> 3, row8 = lane & 7;
-        const int u0 = warp * 4 + sub;
-        const int cgA = u0;
-        int cgB, rowA[4], rowB[4];
+        const int u0 = warp * 4 + sub;                              // 0 .. 4*NSW-1
+        const int cgA = u0 & 31;
+        int cgB, rowA[NI], rowB[NI];
+        bool actB[NI];
 #pragma unroll
-        for (int i = 0; i < 4; ++i) rowA[i] = i * 8 + row8;
+        for (int i = 0; i < NI; ++i) rowA[i] = ((i * (4 * NSW) + u0) >> 5) * 8 + row8;
         if (J.blkB) {
             cgB = u0 % gprB;
 #pragma unroll
-            for (int i = 0; i < 4; ++i) rowB[i] = (((i * 32 + u0) / gprB) * 8 + row8) & (WK - 1);
+            for (int i = 0; i < NI; ++i) {
+                const int u = i * (4 * NSW) + u0;
+                actB[i] = u < gprB * 4;
+                rowB[i] = ((u / gprB) * 8 + row8) & (WK - 1);
+            }
         } else {
             cgB = tid % gprB;
 #pragma unroll
-            for (int i = 0; i < 4; ++i) rowB[i] = (tid / gprB + (256 / gprB) * i) & (WK - 1);
+            for (int i = 0; i < NI; ++i) {
+                const int idx = i * (NSW * 32) + tid;
+                actB[i] = idx < gprB * WK;
+                rowB[i] = (idx / gprB) & (WK - 1);
+            }
         }
         const bool onA = cgA * 4 < J.ma, onB = cgB * 4 < J.nb;
         const bool wantA = J.biasA != nullptr, wantB = J.biasB != nullptr;
-        int oA[4], oB[4];
+        int oA[NI], oB[NI];
 #pragma unroll
-        for (int i = 0; i < 4; ++i) { oA[i] = tile32_off(rowA[i], cgA * 4, WK); oB[i] = tile32_off(rowB[i], cgB * 4, WK); }
+        for (int i = 0; i < NI; ++i) { oA[i] = tile32_off(rowA[i], cgA * 4, WK); oB[i] = tile32_off(rowB[i], cgB * 4, WK); }
         float sa[4] = {0.f, 0.f, 0.f, 0.f}, sb[4] = {0.f, 0.f, 0.f, 0.f};
         const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
-        float4 vbn[4] = {z4, z4, z4, z4};                           // row-major B: one stage of register prefetch
+        float4 vbn[NI];                                             // row-major B: one stage of register prefetch
+#pragma unroll
+        for (int i = 0; i < NI; ++i) vbn[i] = z4;
         auto issueB = [&](long long s) {
 #pragma unroll
-            for (int i = 0; i < 4; ++i) vbn[i] = (i < nrb) ? load4(J.B, J.ldb, s * WK + rowB[i], cgB * 4, J.nb, J.rowsB) : z4;
+            for (int i = 0; i < NI; ++i) vbn[i] = actB[i] ? load4(J.B, J.ldb, s * WK + rowB[i], cgB * 4, J.nb, J.rowsB) : z4;
         };
         if (!J.blkB && s_begin < s_end) issueB(s_begin);
         uint32_t g = 0;
@@ -855,21 +867,21 @@ k_deform_bwd_weights(WArgs args)
             const uint32_t rslot = g % RSTAGES, tslot = g % TSTAGES;
             const float* rawA = raw0 + (size_t)rslot * raw_floats;
             const float* rawB = rawA + rawA_f;
-            float4 va[4], vb[4];
+            float4 va[NI], vb[NI];
             mbar_wait(&bars[WB_RFULL + rslot], (g / RSTAGES) & 1);
 #pragma unroll
-            for (int i = 0; i < 4; ++i) va[i] = onA ? *reinterpret_cast<const float4*>(rawA + (cgA * 32 + rowA[i]) * 4) : z4;
+            for (int i = 0; i < NI; ++i) va[i] = onA ? *reinterpret_cast<const float4*>(rawA + (cgA * 32 + rowA[i]) * 4) : z4;
             if (J.blkB) {
 #pragma unroll
-                for (int i = 0; i < 4; ++i) vb[i] = (i < nrb && onB) ? *reinterpret_cast<const float4*>(rawB + (cgB * 32 + rowB[i]) * 4) : z4;
+                for (int i = 0; i < NI; ++i) vb[i] = (actB[i] && onB) ? *reinterpret_cast<const float4*>(rawB + (cgB * 32 + rowB[i]) * 4) : z4;
             } else {
 #pragma unroll
-                for (int i = 0; i < 4; ++i) vb[i] = vbn[i];
+                for (int i = 0; i < NI; ++i) vb[i] = vbn[i];
                 if (s + 1 < s_end) issueB(s + 1);
             }
-            float4 ahi[4], alo[4], bhi[4], blo[4];
+            float4 ahi[NI], alo[NI], bhi[NI], blo[NI];
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
+            for (int i = 0; i < NI; ++i) {
                 split_tf32_rn(va[i].x, ahi[i].x, alo[i].x); split_tf32_rn(va[i].y, ahi[i].y, alo[i].y);
                 split_tf32_rn(va[i].z, ahi[i].z, alo[i].z); split_tf32_rn(va[i].w, ahi[i].w, alo[i].w);
                 if (wantA) { sa[0] += va[i].x; sa[1] += va[i].y; sa[2] += va[i].z; sa[3] += va[i].w; }
@@ -884,10 +896,10 @@ k_deform_bwd_weights(WArgs args)
             float* Bh = Ah + 8192;
             const int lofsB = nblkB * 1024;
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
+            for (int i = 0; i < NI; ++i) {
                 *reinterpret_cast<float4*>(Ah + oA[i]) = ahi[i];
                 *reinterpret_cast<float4*>(Ah + 4096 + oA[i]) = alo[i];
-                if (i < nrb) {
+                if (actB[i]) {
                     *reinterpret_cast<float4*>(Bh + oB[i]) = bhi[i];
                     *reinterpret_cast<float4*>(Bh + lofsB + oB[i]) = blo[i];
                 }
@@ -905,7 +917,7 @@ k_deform_bwd_weights(WArgs args)
 #pragma unroll
             for (int u = 0; u < 4; ++u) atomicAdd(&csumB[cgB * 4 + u], sb[u]);
         }
-        asm volatile("bar.sync 1, 256;" ::: "memory");
+        asm volatile("bar.sync 1, %0;" ::"n"(NSW * 32) : "memory");
         if (tid < 128) {
             if (wantA && tid < J.ma) atomicAdd(&J.biasA[tid], csumA[tid]);
             if (wantB && tid < J.nb) atomicAdd(&J.biasB[tid], csumB[tid]);
@@ -916,8 +928,9 @@ k_deform_bwd_weights(WArgs args)
         if (s_end > s_begin) {
             const int m = (warp & 3) * 32 + lane;
             const uint32_t lane_base = tmem + ((uint32_t)((warp & 3) * 32) << 16);
-            const int half = N16 / 2 >= 8 ? ((N16 / 2 + 7) & ~7) : 8;
-            const int nb0 = (warp >> 2) ? half : 0, nb1 = (warp >> 2) ? N16 : (half < N16 ? half : N16);
+            constexpr int NG = NSW / 4;                              // warps per TMEM lane quarter: split the columns
+            const int per = ((N16 + NG - 1) / NG + 7) & ~7;
+            const int nb0 = (warp >> 2) * per, nb1 = nb0 + per < N16 ? nb0 + per : N16;
             for (int c0 = nb0; c0 < nb1; c0 += 8) {
                 uint32_t v[8];
                 tmem_ld8(lane_base + c0, v);
@@ -935,7 +948,7 @@ k_deform_bwd_weights(WArgs args)
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
-    if (warp == 8) tmem_free(tmem, 128);
+    if (warp == NSW) tmem_free(tmem, 128);
 }
 
 // =====================================================================================================================
