@@ -749,6 +749,9 @@ k_deform_bwd_weights(WArgs args)
     __shared__ uint32_t tmem_slot;
     __shared__ float csumA[128], csumB[128];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+#ifdef FDGS_PHASE_TIMING
+    const long long t_start_ = clock64();
+#endif
     int jb = 0, first = 0;
     for (; jb < args.njobs; ++jb) { if ((int)blockIdx.x < first + args.j[jb].slices) break; first += args.j[jb].slices; }
     if (jb >= args.njobs) return;
@@ -782,8 +785,17 @@ k_deform_bwd_weights(WArgs args)
         if (lane == 0) {
             uint32_t g = 0;
             const uint32_t bytes = (uint32_t)(rawA_f + rawB_f) * 4;
+            constexpr int PFD = 8;                                  // stages prefetched into L2 ahead of the ring
+            for (long long s = s_begin; s < s_end && s < s_begin + PFD; ++s) {
+                bulk_prefetch_l2(J.A + (size_t)s * rawA_f, (uint32_t)rawA_f * 4);
+                if (rawB_f) bulk_prefetch_l2(J.B + (size_t)s * rawB_f, (uint32_t)rawB_f * 4);
+            }
             for (long long s = s_begin; s < s_end; ++s, ++g) {
                 const uint32_t slot = g % RSTAGES;
+                if (s + PFD < s_end) {
+                    bulk_prefetch_l2(J.A + (size_t)(s + PFD) * rawA_f, (uint32_t)rawA_f * 4);
+                    if (rawB_f) bulk_prefetch_l2(J.B + (size_t)(s + PFD) * rawB_f, (uint32_t)rawB_f * 4);
+                }
                 mbar_wait(&bars[WB_REMPTY + slot], ((g / RSTAGES) & 1) ^ 1);
                 mbar_expect_tx(&bars[WB_RFULL + slot], bytes);
                 float* dst = raw0 + (size_t)slot * raw_floats;
@@ -949,6 +961,9 @@ k_deform_bwd_weights(WArgs args)
     __syncthreads();
     tc_fence_after();
     if (warp == NSW) tmem_free(tmem, 128);
+#ifdef FDGS_PHASE_TIMING
+    if (tid == 0) printf("bwd_weights cta %d job %d slice %d/%d stages %lld cycles %lld\n", (int)blockIdx.x, jb, slice, J.slices, s_end - s_begin, clock64() - t_start_);
+#endif
 }
 
 // =====================================================================================================================
@@ -1038,12 +1053,12 @@ int backward(const Layout& lo, const FdgsDeformBackward* a, const float* packed,
         const int h = plan.heads[j];
         const int NO = head_out(h);
         wa.j[nj] = WJob{io.S_GZ[j], Wn, Wn, (int)plan.Pp, io.S_H, Wn, Wn, (int)plan.Pp, dw1[h], Wn, 0, a->d_head_b1[h], nullptr, 1, 1, 1};
-        cost[nj++] = 1.0;
+        cost[nj++] = 1.0;                                 // relative per-stage cost, measured (cycles/stage 1750 : 2050 : 1530)
         wa.j[nj] = WJob{io.S_RZ[j], Wn, Wn, (int)plan.Pp, gsrc[h], NO, NO, a->P, a->d_head_w2[h], Wn, 1, nullptr, a->d_head_b2[h], 1, 1, 0};
-        cost[nj++] = NO > 4 ? 0.85 : 0.8;       // per-stage cost is instruction-, not byte-bound (measured)
+        cost[nj++] = 1.17;
     }
     wa.j[nj] = WJob{io.S_GH, Wn, Wn, (int)plan.Pp, io.S_F, F, F, (int)plan.Pp, a->d_trunk_w[0], F, 0, a->d_trunk_b[0], nullptr, 1, 1, 1};
-    cost[nj++] = 0.65;
+    cost[nj++] = 0.87;
     wa.njobs = nj; wa.rows = plan.Pp;
     // distribute the SMs over the jobs in proportion to the bytes they stream
     double tot = 0; for (int i = 0; i < nj; ++i) tot += cost[i];
