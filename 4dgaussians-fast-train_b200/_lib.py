@@ -77,6 +77,7 @@ class FdgsDeformForward(C.Structure):
         ("packed_ws", C.c_void_p), ("packed_bytes", C.c_size_t),
         ("trow_ws", C.c_void_p), ("trow_bytes", C.c_size_t),
         ("wprep_ws", C.c_void_p), ("wprep_bytes", C.c_size_t),
+        ("save_ws", C.c_void_p), ("save_bytes", C.c_size_t),
         ("debug", C.c_int32),
     ]
 
@@ -96,6 +97,7 @@ class FdgsDeformBackward(C.Structure):
         ("packed_ws", C.c_void_p), ("trow_ws", C.c_void_p),
         ("ws", C.c_void_p), ("ws_bytes", C.c_size_t),
         ("scratch", C.c_void_p), ("scratch_bytes", C.c_size_t),
+        ("saved_ws", C.c_void_p), ("saved_bytes", C.c_size_t),
         ("debug", C.c_int32),
     ]
 
@@ -119,6 +121,7 @@ SYMBOLS = {
     "fdgs_deform_packed_bytes": (C.c_size_t, [C.POINTER(FdgsDeformNet)]),
     "fdgs_deform_trow_bytes": (C.c_size_t, [C.POINTER(FdgsDeformNet)]),
     "fdgs_deform_wprep_bytes": (C.c_size_t, [C.POINTER(FdgsDeformNet)]),
+    "fdgs_deform_forward_save_bytes": (C.c_size_t, [C.POINTER(FdgsDeformNet), C.c_int]),
     "fdgs_deform_forward": (C.c_int, [C.POINTER(FdgsDeformForward), C.c_void_p]),
     "fdgs_deform_backward_ws_bytes": (C.c_size_t, [C.POINTER(FdgsDeformNet)]),
     "fdgs_deform_backward_scratch_bytes": (C.c_size_t, [C.POINTER(FdgsDeformNet), C.c_int]),

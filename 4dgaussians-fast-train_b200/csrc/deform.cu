@@ -22,6 +22,7 @@
 
 namespace fdgs_deform_tc {
 size_t wprep_bytes(const fdgs_deform::Layout& lo);
+size_t save_bytes(const fdgs_deform::Layout& lo, int P);
 bool supported(const fdgs_deform::Layout& lo);
 int forward(const fdgs_deform::Layout& lo, const FdgsDeformForward* a, const float* packed, const float* trow, cudaStream_t stream);
 }
@@ -635,6 +636,11 @@ size_t fdgs_deform_wprep_bytes(const FdgsDeformNet* net) {
     Layout lo;
     if (!net || make_layout(*net, lo)) return 0;
     return fdgs_deform_tc::wprep_bytes(lo);
+}
+size_t fdgs_deform_forward_save_bytes(const FdgsDeformNet* net, int P) {
+    Layout lo;
+    if (!net || make_layout(*net, lo)) return 0;
+    return fdgs_deform_tc::save_bytes(lo, P);
 }
 size_t fdgs_deform_backward_ws_bytes(const FdgsDeformNet* net) {
     return fdgs_deform_packed_bytes(net) + fdgs_deform_trow_bytes(net);

@@ -63,6 +63,21 @@ struct GradPtrs {
     float* w2[FDGS_NUM_HEADS]; float* b2[FDGS_NUM_HEADS];
 };
 
+// Activations the training forward keeps for the backward (floats; rows padded to whole 128-point tiles, blocked layout
+// [tile][row/32][col/4][row%32][4] so that 32 consecutive rows are one contiguous run of 32*cols floats).
+struct SaveLayout { long long Pp, off_F, off_H, off_RZ[FDGS_NUM_HEADS], total; };
+static inline SaveLayout make_save_layout(const Layout& lo, int P) {
+    SaveLayout s;
+    s.Pp = (((long long)P + TP - 1) / TP) * TP;
+    auto al = [](long long x) { return (x + 63) & ~63LL; };
+    long long o = 0;
+    s.off_F = o; o += al(s.Pp * lo.F);
+    s.off_H = o; o += al(s.Pp * lo.Wn);
+    for (int h = 0; h < FDGS_NUM_HEADS; ++h) { s.off_RZ[h] = o; if ((lo.head_mask >> h) & 1) o += al(s.Pp * lo.Wn); }
+    s.total = o;
+    return s;
+}
+
 __host__ __device__ inline int head_out(int h) { return h == 0 ? 3 : h == 1 ? 3 : h == 2 ? 4 : h == 3 ? 1 : 48; }
 
 // ATen grid_sampler coordinate mapping, align_corners=True, padding_mode='border'

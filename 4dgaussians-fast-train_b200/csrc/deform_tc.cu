@@ -86,6 +86,9 @@ struct TcFwdIO {
     int P, sh_coeffs;
     const float *xyz, *scales, *rot, *opacity, *shs;
     float *o_xyz, *o_scales, *o_rot, *o_opacity, *o_shs;
+    // training: activations kept for the backward pass (blocked layout [tile][row/32][col/4][row%32][4]); null = none
+    float *S_F, *S_H;
+    float* S_RZ[FDGS_NUM_HEADS];     // by head id
 };
 
 // shared-memory plan (floats unless noted), all offsets multiples of 256 floats
@@ -282,6 +285,9 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
                     const int o = tile_off(srow, item * 4, 128);
                     *reinterpret_cast<float4*>(F_hi + o) = hi;
                     *reinterpret_cast<float4*>(F_lo + o) = lw;
+                    if (io.S_F)
+                        __stcs(reinterpret_cast<float4*>(io.S_F + (size_t)tile * TP * lo.F + (srow >> 5) * 32 * lo.F + (item * 32 + (srow & 31)) * 4),
+                               make_float4(prod[0], prod[1], prod[2], prod[3]));
                 }
             }
             fence_async_smem();
@@ -302,6 +308,14 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
                     float a, b;
                     split_tf32_rn(x, a, b);
                     hi[j] = __float_as_uint(a); lw[j] = __float_as_uint(b);
+                    v[j] = __float_as_uint(x);
+                }
+                if (io.S_H) {
+                    float* dst = io.S_H + (size_t)tile * TP * WN + (row >> 5) * 32 * WN + (row & 31) * 4;
+#pragma unroll
+                    for (int j = 0; j < 32; j += 4)
+                        __stcs(reinterpret_cast<float4*>(dst + ((col0 + c0 + j) >> 2) * 128),
+                               make_float4(__uint_as_float(v[j]), __uint_as_float(v[j + 1]), __uint_as_float(v[j + 2]), __uint_as_float(v[j + 3])));
                 }
                 tmem_st32(lane_base + TM_HHI + col0 + c0, hi);
                 tmem_st32(lane_base + TM_HLO + col0 + c0, lw);
@@ -327,6 +341,13 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
                     tmem_wait_ld();
 #pragma unroll
                     for (int j = 0; j < 32; ++j) z[c0 + j] = fmaxf(__uint_as_float(v[j]) + B1s[h * WN + col0 + c0 + j], 0.f);
+                    if (io.S_RZ[h]) {
+                        float* dst = io.S_RZ[h] + (size_t)tile * TP * WN + (row >> 5) * 32 * WN + (row & 31) * 4;
+#pragma unroll
+                        for (int j = 0; j < 32; j += 4)
+                            __stcs(reinterpret_cast<float4*>(dst + ((col0 + c0 + j) >> 2) * 128),
+                                   make_float4(z[c0 + j], z[c0 + j + 1], z[c0 + j + 2], z[c0 + j + 3]));
+                    }
                 }
                 tc_fence_before();
                 epi_bar();
@@ -392,6 +413,11 @@ static int sm_count() {
     return n;
 }
 
+size_t save_bytes(const Layout& lo, int P) {
+    if (!tc_supported(lo) || P <= 0) return 0;
+    return fdgs_align_up(sizeof(float) * (size_t)make_save_layout(lo, P).total);
+}
+
 size_t wprep_bytes(const Layout& lo) {
     if (!tc_supported(lo)) return 256;
     const TcPlan p = make_plan(lo);
@@ -420,6 +446,15 @@ int forward(const Layout& lo, const FdgsDeformForward* a, const float* packed, c
     io.P = a->P; io.sh_coeffs = a->sh_coeffs;
     io.xyz = a->xyz; io.scales = a->scales; io.rot = a->rotations; io.opacity = a->opacity; io.shs = a->shs;
     io.o_xyz = a->out_xyz; io.o_scales = a->out_scales; io.o_rot = a->out_rotations; io.o_opacity = a->out_opacity; io.o_shs = a->out_shs;
+    io.S_F = nullptr; io.S_H = nullptr;
+    for (int h = 0; h < FDGS_NUM_HEADS; ++h) io.S_RZ[h] = nullptr;
+    if (a->save_ws) {
+        if (a->save_bytes < save_bytes(lo, a->P)) return FDGS_E_WORKSPACE;
+        SaveLayout sl = make_save_layout(lo, a->P);
+        float* S = (float*)a->save_ws;
+        io.S_F = S + sl.off_F; io.S_H = S + sl.off_H;
+        for (int h = 0; h < FDGS_NUM_HEADS; ++h) if ((lo.head_mask >> h) & 1) io.S_RZ[h] = S + sl.off_RZ[h];
+    }
     const int ntiles = (a->P + TP - 1) / TP;
     const int grid = ntiles < sm_count() ? ntiles : sm_count();
     const int passes = a->precision == 1 ? 1 : 3;

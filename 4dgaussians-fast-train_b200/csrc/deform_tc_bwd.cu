@@ -34,6 +34,8 @@ struct Plan {
     int heads[FDGS_NUM_HEADS];     // active heads that received an upstream gradient
     int nchunks_main;              // chunks of 32*Wn floats per tile: W0, then per head W1_j, W2_j^T (K padded to 16), W1_j^T
     int k2chunks[FDGS_NUM_HEADS];  // W2_j^T chunks of plan slot j: 1 (out <= 4) or 3 (out = 48)
+    int seq_n;                     // main chunks streamed per tile, in MMA order (all of them, or - when the forward kept
+    short seq[112];                // the activations - only the W2_j^T and W1_j^T chunks)
     int nchunks_gf;                // chunks of 32*F floats (W0^T)
     long long wprep_floats;
     // scratch (floats), Pp = ntiles * 128 rows each
@@ -45,7 +47,7 @@ static inline bool tc_supported(const Layout& lo) {
     return lo.depth == 1 && (lo.Wn == 64 || lo.Wn == 128) && lo.F % KCH == 0 && lo.F >= KCH && lo.F <= 64 && lo.C >= 8;
 }
 
-static inline Plan make_plan(const Layout& lo, int P, const bool has_grad[FDGS_NUM_HEADS]) {
+static inline Plan make_plan(const Layout& lo, int P, const bool has_grad[FDGS_NUM_HEADS], bool saved = false) {
     Plan p;
     p.Wn = lo.Wn; p.F = lo.F; p.nheads = 0;
     for (int h = 0; h < FDGS_NUM_HEADS; ++h) if (((lo.head_mask >> h) & 1) && has_grad[h]) p.heads[p.nheads++] = h;
@@ -57,6 +59,16 @@ static inline Plan make_plan(const Layout& lo, int P, const bool has_grad[FDGS_N
     }
     p.nchunks_gf = lo.Wn / KCH;
     p.wprep_floats = (long long)p.nchunks_main * 32 * lo.Wn + (long long)p.nchunks_gf * 32 * lo.F;
+    {
+        int c = 0, n = 0;
+        for (int k = 0; k < lo.F / KCH; ++k, ++c) if (!saved) p.seq[n++] = (short)c;                 // W0
+        for (int j = 0; j < p.nheads; ++j) {
+            for (int k = 0; k < lo.Wn / KCH; ++k, ++c) if (!saved) p.seq[n++] = (short)c;            // W1_j
+            for (int k = 0; k < p.k2chunks[j]; ++k, ++c) p.seq[n++] = (short)c;                      // W2_j^T
+            for (int k = 0; k < lo.Wn / KCH; ++k, ++c) p.seq[n++] = (short)c;                        // W1_j^T
+        }
+        p.seq_n = n;
+    }
     const long long ntiles = ((long long)P + TP - 1) / TP;
     p.Pp = ntiles * TP;
     auto al = [](long long x) { return (x + 63) & ~63LL; };
@@ -112,6 +124,9 @@ struct IO {
     float *S_F, *S_H, *S_GH;
     float* S_RZ[FDGS_NUM_HEADS];           // indexed by plan slot j
     float* S_GZ[FDGS_NUM_HEADS];
+    // activations kept by the forward (SAVED kernels read these instead of recomputing), same blocked layout
+    const float *V_H;
+    const float* V_RZ[FDGS_NUM_HEADS];     // indexed by plan slot j
 };
 
 struct Smem {
@@ -120,13 +135,15 @@ struct Smem {
     size_t bytes;
 };
 
-static inline Smem make_smem(const Layout& lo) {
+static inline Smem make_smem(const Layout& lo, bool saved = false) {
     Smem s;
     auto al = [](int x) { return (x + 255) & ~255; };
     const int Wn = lo.Wn;
     int o = 0;
-    s.off_hs_hi = o; o += al(128 * Wn);        // relu(h) hi, K-major canonical tile; feat hi aliases its head
-    s.off_hs_lo = o; o += al(128 * Wn);
+    // relu(h) hi / lo as K-major canonical tiles (feat hi / lo and, later, g_feat alias their heads); when the forward
+    // kept the activations only the g_feat staging tile remains
+    s.off_hs_hi = o; o += al(128 * (saved ? lo.F : Wn));
+    s.off_hs_lo = o; o += saved ? 0 : al(128 * Wn);
     s.off_w2 = o;                              // (the output layers run on the tensor cores: no W2 copy)
     s.off_b0 = o; o += al(Wn);
     s.off_b1 = o; o += al(FDGS_NUM_HEADS * Wn);
@@ -254,11 +271,9 @@ __device__ __forceinline__ void sample_bwd4(const Layout& lo, int l, const float
     }
 }
 
-// ---- head epilogue, pass 1: z = relu(acc + b1) -> scratch, ReLU gate bits; upstream gradient g_o hi/lo -> TMEM --------
+// ---- upstream gradient g_o hi/lo -> TMEM (A operand of g_relu_z = g_o W2) ----------------------------------------------
 // The thread's g_o columns are [hf*24, hf*24+24) of 48 for dshs, and all 8 (zero padded) on the hf == 0 warps otherwise.
-template <int NH>
-__device__ __forceinline__ void head_pass1(uint32_t lane_base, int col0, int hf, int NO, bool valid, const float* __restrict__ gsrc,
-                                           const float* __restrict__ b1s, float* __restrict__ rz_row, uint32_t (&zgate)[NH / 32 + 1]) {
+__device__ __forceinline__ void stage_go(uint32_t lane_base, int hf, int NO, bool valid, const float* __restrict__ gsrc) {
     if (NO == 48) {
 #pragma unroll
         for (int c = 0; c < 24; c += 8) {
@@ -284,6 +299,13 @@ __device__ __forceinline__ void head_pass1(uint32_t lane_base, int col0, int hf,
         tmem_st8(lane_base + TM_GHI, hi);
         tmem_st8(lane_base + TM_GLO, lw);
     }
+    tmem_wait_st();
+}
+
+// ---- pass 1 (recompute mode): z = relu(acc + b1) -> scratch, ReLU gate bits ----------------------------------------------
+template <int NH>
+__device__ __forceinline__ void head_pass1(uint32_t lane_base, int col0, const float* __restrict__ b1s, float* __restrict__ rz_row,
+                                           uint32_t (&zgate)[NH / 32 + 1]) {
 #pragma unroll
     for (int c0 = 0; c0 < NH; c0 += 32) {
         uint32_t v[32];
@@ -302,7 +324,22 @@ __device__ __forceinline__ void head_pass1(uint32_t lane_base, int col0, int hf,
         }
         zgate[c0 / 32] = m;
     }
-    tmem_wait_st();
+}
+
+// ---- ReLU gate bits of this thread's NH columns from an activation the forward kept (blocked row pointer) ---------------
+template <int NH>
+__device__ __forceinline__ void gate_from_saved(const float* __restrict__ row, int col0, uint32_t (&gate)[NH / 32 + 1]) {
+#pragma unroll
+    for (int c0 = 0; c0 < NH; c0 += 32) {
+        float4 v[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] = __ldcs(reinterpret_cast<const float4*>(row + ((col0 + c0 + 4 * j) >> 2) * 128));
+        uint32_t m = 0;
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+            m |= ((v[j].x > 0.f ? 1u : 0u) | (v[j].y > 0.f ? 2u : 0u) | (v[j].z > 0.f ? 4u : 0u) | (v[j].w > 0.f ? 8u : 0u)) << (4 * j);
+        gate[c0 / 32] = m;
+    }
 }
 
 // ---- pass 2: g_z = (g_o W2)[z > 0] (accumulator) -> scratch, hi/lo -> TMEM (A operand of g_relu_h += g_z W1) -----------
@@ -332,7 +369,7 @@ __device__ __forceinline__ void head_pass2(uint32_t lane_base, int col0, float* 
 }
 
 // =====================================================================================================================
-template <int WN>
+template <int WN, bool SAVED>
 __global__ void __launch_bounds__(NTHREADS, 1)
 k_deform_bwd_data(Layout lo, Plan plan, Smem sp, Net net, IO io, const float* __restrict__ packed,
                   const float* __restrict__ trow, float* __restrict__ gpacked, float* __restrict__ gtrow, int ntiles)
@@ -380,14 +417,14 @@ k_deform_bwd_data(Layout lo, Plan plan, Smem sp, Net net, IO io, const float* __
         // ===== producer: the same chunk sequence for every tile ===========================================
         if (lane == 0) {
             uint32_t g = 0;
-            const int nch = plan.nchunks_main + plan.nchunks_gf;
+            const int nch = plan.seq_n + plan.nchunks_gf;
             for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x)
                 for (int c = 0; c < nch; ++c, ++g) {
                     const uint32_t slot = g % S;
-                    const bool gf = c >= plan.nchunks_main;
+                    const bool gf = c >= plan.seq_n;
                     const uint32_t bytes = (gf ? 32 * F : SLOT) * 4;
-                    const float* src = net.wprep + (gf ? (size_t)plan.nchunks_main * SLOT + (size_t)(c - plan.nchunks_main) * 32 * F
-                                                       : (size_t)c * SLOT);
+                    const float* src = net.wprep + (gf ? (size_t)plan.nchunks_main * SLOT + (size_t)(c - plan.seq_n) * 32 * F
+                                                       : (size_t)plan.seq[c] * SLOT);
                     mbar_wait(&bars[B_WEMPTY + slot], ((g / S) & 1) ^ 1);
                     mbar_expect_tx(&bars[B_WFULL + slot], bytes);
                     bulk_g2s(ring + (size_t)slot * SLOT, src, bytes, &bars[B_WFULL + slot]);
@@ -402,6 +439,7 @@ k_deform_bwd_data(Layout lo, Plan plan, Smem sp, Net net, IO io, const float* __
             uint32_t g = 0, ph_feat = 0, ph_h = 0, ph_gz = 0, ph_gh = 0, ph_go = 0;
             for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
                 // trunk: ACC = feat . W0^T
+                if constexpr (!SAVED) {
                 mbar_wait(&bars[B_FEATFULL], ph_feat); ph_feat ^= 1;
                 tc_fence_after();
                 for (int c = 0; c < F / KCH; ++c, ++g) {
@@ -423,8 +461,10 @@ k_deform_bwd_data(Layout lo, Plan plan, Smem sp, Net net, IO io, const float* __
                 mma_commit(&bars[B_ACCFULL]);
                 mbar_wait(&bars[B_HFULL], ph_h); ph_h ^= 1;
                 tc_fence_after();
+                }
                 for (int i = 0; i < plan.nheads; ++i) {
                     // z_i: ACC = relu(h) . W1^T      (A from shared memory)
+                    if constexpr (!SAVED) {
                     for (int c = 0; c < WN / KCH; ++c, ++g) {
                         const uint32_t slot = g % S;
                         mbar_wait(&bars[B_WFULL + slot], (g / S) & 1);
@@ -442,6 +482,7 @@ k_deform_bwd_data(Layout lo, Plan plan, Smem sp, Net net, IO io, const float* __
                         mma_commit(&bars[B_WEMPTY + slot]);
                     }
                     mma_commit(&bars[B_ACCFULL]);
+                    }
                     // g_relu_z: ACC = g_o . W2       (A = g_o from TMEM, B = W2^T chunks, K padded to 8 / 48)
                     mbar_wait(&bars[B_GOFULL], ph_go); ph_go ^= 1;
                     tc_fence_after();
@@ -486,8 +527,9 @@ k_deform_bwd_data(Layout lo, Plan plan, Smem sp, Net net, IO io, const float* __
                         }
                         mma_commit(&bars[B_WEMPTY + slot]);
                     }
+                    if constexpr (SAVED) mma_commit(&bars[B_GRHFULL]);    // per head: g_z in TMEM may be overwritten by the next g_o
                 }
-                mma_commit(&bars[B_GRHFULL]);
+                if constexpr (!SAVED) mma_commit(&bars[B_GRHFULL]);
                 // g_feat: ACC[0, F) = g_h . W0       (A from TMEM, B = W0^T chunks, N = F)
                 mbar_wait(&bars[B_GHFULL], ph_gh); ph_gh ^= 1;
                 tc_fence_after();
@@ -526,6 +568,10 @@ k_deform_bwd_data(Layout lo, Plan plan, Smem sp, Net net, IO io, const float* __
         for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
             const int p = tile * TP + row;
             const bool valid = p < io.P;
+            uint32_t gate[NH / 32 + 1];
+            if constexpr (SAVED) {
+                gate_from_saved<NH>(io.V_H + (size_t)tile * TP * WN + (row >> 5) * 32 * WN + (row & 31) * 4, col0, gate);
+            } else {
             // ---- HexPlane sampling -> feat tile (hi / lo) + scratch ----------------------------------------
             // Sampler mapping: LP adjacent lanes share one point and take consecutive channel quads, so a warp-wide
             // gather touches 32/LP points x (64-byte taps) instead of 32 unrelated lines (the L1 tag stage, one line
@@ -560,7 +606,6 @@ k_deform_bwd_data(Layout lo, Plan plan, Smem sp, Net net, IO io, const float* __
             mbar_wait(&bars[B_ACCFULL], ph_acc); ph_acc ^= 1;
             tc_fence_after();
             PT(1)
-            uint32_t gate[NH / 32];
 #pragma unroll
             for (int c0 = 0; c0 < NH; c0 += 32) {
                 uint32_t v[32];
@@ -590,19 +635,30 @@ k_deform_bwd_data(Layout lo, Plan plan, Smem sp, Net net, IO io, const float* __
             if (tid == 0) mbar_arrive(&bars[B_HFULL]);
             PT(2)
 
+            }
             // ---- heads ---------------------------------------------------------------------------------------------
             for (int i = 0; i < plan.nheads; ++i) {
                 const int h = plan.heads[i];
                 const int NO = head_out(h);
-                mbar_wait(&bars[B_ACCFULL], ph_acc); ph_acc ^= 1;
-                tc_fence_after();
-                PT(3)
                 const float* gsrc = io.g[h] + (size_t)(valid ? p : 0) * NO;
                 // blocked scratch: [tile][row / 32][col / 4][row % 32][4]  ->  + (col >> 2) * 128
-                float* rz_row = io.S_RZ[i] + (size_t)tile * TP * WN + (row >> 5) * 32 * WN + (row & 31) * 4;
-                float* gz_row = io.S_GZ[i] + (size_t)tile * TP * WN + (row >> 5) * 32 * WN + (row & 31) * 4;
+                const size_t rowoff = (size_t)tile * TP * WN + (row >> 5) * 32 * WN + (row & 31) * 4;
+                float* gz_row = io.S_GZ[i] + rowoff;
                 uint32_t zgate[NH / 32 + 1];
-                head_pass1<NH>(lane_base, col0, hf, NO, valid, gsrc, B1s + h * WN, rz_row, zgate);
+                if constexpr (SAVED) {
+                    gate_from_saved<NH>(io.V_RZ[i] + rowoff, col0, zgate);
+                    if (i > 0) {                                    // g_relu_h += g_z W1 of the previous head has read its g_z
+                        mbar_wait(&bars[B_GRHFULL], ph_grh); ph_grh ^= 1;
+                        tc_fence_after();
+                    }
+                    PT(3)
+                } else {
+                    mbar_wait(&bars[B_ACCFULL], ph_acc); ph_acc ^= 1;
+                    tc_fence_after();
+                    PT(3)
+                    head_pass1<NH>(lane_base, col0, B1s + h * WN, io.S_RZ[i] + rowoff, zgate);
+                }
+                stage_go(lane_base, hf, NO, valid, gsrc);
                 tc_fence_before();
                 epi_bar();
                 if (tid == 0) mbar_arrive(&bars[B_GOFULL]);        // z drained from the accumulator, g_o staged in TMEM
@@ -988,15 +1044,19 @@ int backward(const Layout& lo, const FdgsDeformBackward* a, const float* packed,
     const float* gsrc[FDGS_NUM_HEADS] = {a->g_xyz, a->g_scales, a->g_rotations, a->g_opacity, a->g_shs};
     bool has[FDGS_NUM_HEADS];
     for (int h = 0; h < FDGS_NUM_HEADS; ++h) has[h] = gsrc[h] != nullptr;
-    const Plan plan = make_plan(lo, a->P, has);
+    const bool saved = a->saved_ws != nullptr;
+    const Plan plan = make_plan(lo, a->P, has, saved);
     if (plan.nheads == 0) {
         FDGS_CUDA(cudaMemsetAsync(a->d_xyz_grid, 0, sizeof(float) * 3 * (size_t)a->P, stream));
         return FDGS_OK;
     }
     if (!a->scratch || a->scratch_bytes < sizeof(float) * (size_t)plan.total_floats) return FDGS_E_WORKSPACE;
-    const Smem sp = make_smem(lo);
+    const Smem sp = make_smem(lo, saved);
     if (sp.slots < 3) return FDGS_E_SMEM;
     float* S = (float*)a->scratch;
+    const SaveLayout sl = make_save_layout(lo, a->P);
+    if (saved && a->saved_bytes < sizeof(float) * (size_t)sl.total) return FDGS_E_WORKSPACE;
+    const float* V = (const float*)a->saved_ws;
     const int Wn = lo.Wn, F = lo.F;
 
     // 1. weights -> hi/lo K-major chunks in consumption order: W0 | per head (W1, W1^T) | W0^T
@@ -1029,19 +1089,24 @@ int backward(const Layout& lo, const FdgsDeformBackward* a, const float* packed,
     for (int h = 0; h < FDGS_NUM_HEADS; ++h) io.g[h] = gsrc[h];
     io.S_F = S + plan.off_F; io.S_H = S + plan.off_H; io.S_GH = S + plan.off_GH;
     for (int j = 0; j < FDGS_NUM_HEADS; ++j) { io.S_RZ[j] = S + plan.off_RZ[j]; io.S_GZ[j] = S + plan.off_GZ[j]; }
+    io.V_H = nullptr;
+    for (int j = 0; j < FDGS_NUM_HEADS; ++j) io.V_RZ[j] = nullptr;
+    if (saved) {        // the forward kept feat, relu(h), relu(z_j): nothing is recomputed and the weight kernel reads them in place
+        io.V_H = V + sl.off_H;
+        io.S_F = const_cast<float*>(V + sl.off_F); io.S_H = const_cast<float*>(V + sl.off_H);
+        for (int j = 0; j < plan.nheads; ++j) { io.V_RZ[j] = V + sl.off_RZ[plan.heads[j]]; io.S_RZ[j] = const_cast<float*>(io.V_RZ[j]); }
+    }
     const int ntiles = (a->P + TP - 1) / TP;
     const int grid = ntiles < sm_count() ? ntiles : sm_count();
-    if (Wn == 128) {
-        FDGS_CUDA(cudaFuncSetAttribute(k_deform_bwd_data<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sp.bytes));
-        { FDGS_PROF("k_deform_bwd_data", stream);
-        k_deform_bwd_data<128><<<grid, NTHREADS, sp.bytes, stream>>>(lo, plan, sp, net, io, packed, trow, gpacked, gtrow, ntiles);
-        }
-    } else {
-        FDGS_CUDA(cudaFuncSetAttribute(k_deform_bwd_data<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sp.bytes));
-        { FDGS_PROF("k_deform_bwd_data", stream);
-        k_deform_bwd_data<64><<<grid, NTHREADS, sp.bytes, stream>>>(lo, plan, sp, net, io, packed, trow, gpacked, gtrow, ntiles);
-        }
-    }
+#define FDGS_LAUNCH_BWD_DATA(WN_, SV_)                                                                                          \
+    do {                                                                                                                         \
+        FDGS_CUDA(cudaFuncSetAttribute(k_deform_bwd_data<WN_, SV_>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sp.bytes)); \
+        FDGS_PROF(SV_ ? "k_deform_bwd_data_saved" : "k_deform_bwd_data", stream);                                                \
+        k_deform_bwd_data<WN_, SV_><<<grid, NTHREADS, sp.bytes, stream>>>(lo, plan, sp, net, io, packed, trow, gpacked, gtrow, ntiles); \
+    } while (0)
+    if (Wn == 128) { if (saved) FDGS_LAUNCH_BWD_DATA(128, true); else FDGS_LAUNCH_BWD_DATA(128, false); }
+    else           { if (saved) FDGS_LAUNCH_BWD_DATA(64, true);  else FDGS_LAUNCH_BWD_DATA(64, false); }
+#undef FDGS_LAUNCH_BWD_DATA
     FDGS_LAUNCH_CHECK(a->debug, stream);
 
     // 3. weight gradients: jobs x point slices, one CTA each

@@ -129,6 +129,13 @@ class _DeformFunction(torch.autograd.Function):
             a.trow_ws, a.trow_bytes = trow.data_ptr(), trow.numel()
             wprep = net_mod._wprep(lib, a.net, dev)
             a.wprep_ws, a.wprep_bytes = wprep.data_ptr(), wprep.numel()
+            # training: the kernel keeps feat / relu(h) / relu(z_j) for the backward (no recompute there)
+            saved = None
+            if net_mod.save_activations and any(ctx.needs_input_grad) and int(net_mod.precision) != 2:
+                nsave = lib.fdgs_deform_forward_save_bytes(C.byref(a.net), int(P))
+                if nsave:
+                    saved = torch.empty((nsave,), dtype=torch.uint8, device=dev)
+                    a.save_ws, a.save_bytes = saved.data_ptr(), saved.numel()
             a.debug = 0
             L.check(lib.fdgs_deform_forward(C.byref(a), C.c_void_p(torch.cuda.current_stream().cuda_stream)),
                     "fdgs_deform_forward")
@@ -137,6 +144,7 @@ class _DeformFunction(torch.autograd.Function):
         ctx.mod = net_mod
         ctx.time_host = time_host
         ctx.save_for_backward(point_c, packed, trow, *([time_dev] if time_dev is not None else []))
+        ctx.saved_act = saved
         ctx.has_time_dev = time_dev is not None
         ctx.n_params = len(params)
         ctx.sh_coeffs = a.sh_coeffs
@@ -176,9 +184,12 @@ class _DeformFunction(torch.autograd.Function):
             scratch = mod._bwd_scratch(lib, a.net, P, dev) if int(mod.precision) != 2 else None
             if scratch is not None:
                 a.scratch, a.scratch_bytes = scratch.data_ptr(), scratch.numel()
+            if ctx.saved_act is not None and scratch is not None:
+                a.saved_ws, a.saved_bytes = ctx.saved_act.data_ptr(), ctx.saved_act.numel()
             a.debug = 0
             L.check(lib.fdgs_deform_backward(C.byref(a), C.c_void_p(torch.cuda.current_stream().cuda_stream)),
                     "fdgs_deform_backward")
+            ctx.saved_act = None      # stream-ordered: the caching allocator may hand the block out again
             del keep
         # identity paths (mask == 1, scene/deformation.py:104-146)
         d_point = d_xyz + g[0] if g[0] is not None else d_xyz
@@ -211,6 +222,7 @@ class Deformation(nn.Module):
         self.args = args
         self.ratio = 0
         self.precision = 0      # 0: FP32-equivalent (3xTF32 on tcgen05), 1: single-pass TF32, 2: FP32 CUDA-core kernels
+        self.save_activations = True   # training forward keeps the hidden activations (~3.2 KB/point) instead of recomputing
         self._packed = None
         self._packed_key = None
         self.create_net()

@@ -216,12 +216,16 @@ typedef struct FdgsDeformForward {
                                              must stay alive until the matching backward              */
     void* wprep_ws;  size_t wprep_bytes;  /* fdgs_deform_wprep_bytes(): MLP weights split hi/lo and tiled for the
                                              tensor cores; rewritten by every call (scratch)          */
+    void* save_ws; size_t save_bytes;     /* optional, training: fdgs_deform_forward_save_bytes(net, P) bytes that receive
+                                             the HexPlane features and the hidden activations relu(h), relu(z_j) for
+                                             fdgs_deform_backward (saved_ws); NULL = keep nothing (inference)        */
     int32_t debug;
 } FdgsDeformForward;
 
 size_t fdgs_deform_packed_bytes(const FdgsDeformNet* net);
 size_t fdgs_deform_trow_bytes(const FdgsDeformNet* net);
 size_t fdgs_deform_wprep_bytes(const FdgsDeformNet* net);
+size_t fdgs_deform_forward_save_bytes(const FdgsDeformNet* net, int P);   /* 0 = this net/precision keeps nothing */
 int fdgs_deform_forward(const FdgsDeformForward* a, void* stream);
 
 typedef struct FdgsDeformBackward {
@@ -254,6 +258,8 @@ typedef struct FdgsDeformBackward {
                                        the two tensor-core backward kernels + formatted weights; contents are dead
                                        after the call (reuse it across views).  Required unless precision == 2 or the
                                        function returns 0 for this net (then the CUDA-core kernel runs).            */
+    const void* saved_ws; size_t saved_bytes; /* the forward call's save_ws (same net, same P, same xyz); NULL = the
+                                       backward recomputes the activations itself                                  */
     int32_t debug;
 } FdgsDeformBackward;
 

@@ -213,3 +213,34 @@ def test_plane_update_invalidates_packed_cache():
     b1 = ref(xyz, z(P, 3), z(P, 4), z(P, 1), z(P, 16, 3), t)[0]
     assert util.rel_err(a1.detach(), b1.detach()) < OUT_TOL
     assert float((a1 - a0).abs().max()) > 0
+
+
+@pytest.mark.parametrize("cfg_name", ["dnerf", "dynerf"])
+def test_saved_activations_match_recompute(cfg_name):
+    """The training forward keeps feat / relu(h) / relu(z_j) for the backward (save_activations=True, default); with it
+    off the backward recomputes them on the tensor cores.  Same 3xTF32 arithmetic either way: outputs identical,
+    gradients equal up to the order of the float atomics."""
+    cfg = CONFIGS[cfg_name]
+    P = 20000
+    g = synth.make_gaussians(P, extent=cfg["extent"], logscale=cfg["logscale"], seed=2, device="cuda")
+    res = []
+    for save in (True, False):
+        net = synth.seeded_deformation(deform_network, cfg["args"](), device="cuda")
+        net.deformation_net.set_aabb(g["xyz"].max(0).values.tolist(), g["xyz"].min(0).values.tolist())
+        net.deformation_net.save_activations = save
+        leaves = {k: v.clone().requires_grad_(True) for k, v in g.items()}
+        shs = torch.cat([leaves["f_dc"], leaves["f_rest"]], dim=1)
+        t = torch.full((P, 1), 0.4, device="cuda")
+        outs = net(leaves["xyz"], leaves["scaling"], leaves["rotation"], leaves["opacity"], shs, t)
+        gen = torch.Generator(device="cuda").manual_seed(3)
+        sum((o * torch.randn(o.shape, generator=gen, device="cuda")).sum() for o in outs).backward()
+        res.append(([o.detach() for o in outs], {k: v.grad for k, v in leaves.items() if v.grad is not None},
+                    {k: p.grad for k, p in net.named_parameters() if p.grad is not None}))
+    (o1, gi1, gp1), (o2, gi2, gp2) = res
+    for a, b in zip(o1, o2):
+        assert torch.equal(a, b)
+    assert gi1.keys() == gi2.keys() and gp1.keys() == gp2.keys() and len(gp1) >= 12
+    for k in gi1:
+        assert util.rel_err(gi1[k], gi2[k]) < 2e-6, k
+    for k in gp1:
+        assert util.rel_err(gp1[k], gp2[k]) < 2e-6, k
