@@ -222,6 +222,7 @@ class Deformation(nn.Module):
         self.args = args
         self.ratio = 0
         self.precision = 0      # 0: FP32-equivalent (3xTF32 on tcgen05), 1: single-pass TF32, 2: FP32 CUDA-core kernels
+        self.grads_in_place = False    # see _alloc_param_grads
         self.save_activations = True   # training forward keeps the hidden activations (~3.2 KB/point) instead of recomputing
         self._packed = None
         self._packed_key = None
@@ -346,23 +347,31 @@ class Deformation(nn.Module):
         return ps
 
     def _alloc_param_grads(self, a, g):
+        """Gradient buffers of every parameter, in `_param_list` order.  The kernels ACCUMULATE (+=) into them.  With
+        `grads_in_place` (set by fdgs.dp.GradBucket users) a parameter whose .grad already exists - e.g. a view into
+        the flat all-reduce bucket - receives its gradient directly and autograd gets None for it: no zero-fill and
+        no `grad += new` pass per parameter and view."""
         grads = []
+
+        def buf(p):
+            if self.grads_in_place and p.grad is not None and p.grad.is_contiguous() and p.grad.dtype == torch.float32 \
+                    and p.grad.shape == p.shape:
+                grads.append(None)
+                return p.grad.data_ptr()
+            t = torch.zeros_like(p, memory_format=torch.contiguous_format)
+            grads.append(t)
+            return t.data_ptr()
+
         for l, planes in enumerate(self.grid.grids):
             for k, p in enumerate(planes):
-                t = torch.zeros_like(p, memory_format=torch.contiguous_format)
-                a.d_planes[l][k] = t.data_ptr()
-                grads.append(t)
+                a.d_planes[l][k] = buf(p)
         for d, lin in enumerate(self._trunk_linears()):
-            w, b = torch.zeros_like(lin.weight), torch.zeros_like(lin.bias)
-            a.d_trunk_w[d], a.d_trunk_b[d] = w.data_ptr(), b.data_ptr()
-            grads += [w, b]
+            a.d_trunk_w[d], a.d_trunk_b[d] = buf(lin.weight), buf(lin.bias)
         for h, name in enumerate(HEADS):
             if (self.head_mask >> h) & 1:
                 seq = getattr(self, name)
-                ts = [torch.zeros_like(seq[1].weight), torch.zeros_like(seq[1].bias),
-                      torch.zeros_like(seq[3].weight), torch.zeros_like(seq[3].bias)]
-                a.d_head_w1[h], a.d_head_b1[h], a.d_head_w2[h], a.d_head_b2[h] = [t.data_ptr() for t in ts]
-                grads += ts
+                a.d_head_w1[h], a.d_head_b1[h] = buf(seq[1].weight), buf(seq[1].bias)
+                a.d_head_w2[h], a.d_head_b2[h] = buf(seq[3].weight), buf(seq[3].bias)
         return grads
 
     # ---- reference API ------------------------------------------------------------------------

@@ -75,6 +75,16 @@ class GradBucket:
         return dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=group, async_op=async_op)
 
 
+def grads_in_place(module, on=True):
+    """Lets the fused deformation backward accumulate parameter gradients straight into the existing .grad tensors
+    (the bucket slots) instead of returning fresh tensors that autograd then adds - the kernels' epilogues write the
+    buffer NCCL reduces.  Only valid while every .grad is owned by a GradBucket (never replaced, zeroed by bucket.zero())."""
+    for m in module.modules():
+        if hasattr(m, "grads_in_place"):
+            m.grads_in_place = bool(on)
+    return module
+
+
 def l1_view_loss(image, gt, n_views_total):
     """This view's share of the reference's loss: l1_loss(cat(images), cat(gts)) over B equal-size views
     (utils/loss_utils.py l1_loss = mean|a-b|, train.py:231-244) == sum_i mean|img_i - gt_i| / B."""

@@ -148,7 +148,10 @@ def make_bucket(pc, net, dev):
     for name, on in zip(hm_names, active):
         if on:
             params += list(getattr(dn, name).parameters())
-    return GradBucket(params, extra={"viewspace": (pc._xyz.shape[0], 3)}, device=dev)
+    bucket = GradBucket(params, extra={"viewspace": (pc._xyz.shape[0], 3)}, device=dev)
+    from fdgs.dp import grads_in_place
+    grads_in_place(net)      # fdgs deformation backward writes the bucket slots directly (no-op for the reference arm)
+    return bucket
 
 
 # ------------------------------------------------------------------------------------------------ roofline

@@ -244,3 +244,38 @@ def test_saved_activations_match_recompute(cfg_name):
         assert util.rel_err(gi1[k], gi2[k]) < 2e-6, k
     for k in gp1:
         assert util.rel_err(gp1[k], gp2[k]) < 2e-6, k
+
+
+def test_grads_in_place_accumulate_into_bucket():
+    """fdgs.dp.grads_in_place: the backward kernels add parameter gradients straight into the bucket slots; two
+    backward passes give twice the gradient of one pass through the ordinary autograd route."""
+    from fdgs.dp import GradBucket, grads_in_place
+    cfg = CONFIGS["dnerf"]
+    P = 5000
+    g = synth.make_gaussians(P, extent=cfg["extent"], logscale=cfg["logscale"], seed=4, device="cuda")
+
+    def run(net, times):
+        for _ in range(times):
+            shs = torch.cat([g["f_dc"], g["f_rest"]], dim=1)
+            t = torch.full((P, 1), 0.7, device="cuda")
+            outs = net(g["xyz"], g["scaling"], g["rotation"], g["opacity"], shs, t)
+            gen = torch.Generator(device="cuda").manual_seed(3)
+            sum((o * torch.randn(o.shape, generator=gen, device="cuda")).sum() for o in outs).backward()
+
+    ref = synth.seeded_deformation(deform_network, cfg["args"](), device="cuda")
+    ref.deformation_net.set_aabb(g["xyz"].max(0).values.tolist(), g["xyz"].min(0).values.tolist())
+    run(ref, 1)
+    net = synth.seeded_deformation(deform_network, cfg["args"](), device="cuda")
+    net.deformation_net.set_aabb(g["xyz"].max(0).values.tolist(), g["xyz"].min(0).values.tolist())
+    params = [p for k, p in net.named_parameters() if dict(ref.named_parameters())[k].grad is not None]
+    bucket = GradBucket(params, device="cuda")
+    grads_in_place(net)
+    run(net, 2)
+    n = 0
+    for (k, p), (_, q) in zip(net.named_parameters(), ref.named_parameters()):
+        if q.grad is None:
+            continue
+        assert p.grad.data_ptr() == bucket.views[n].data_ptr(), k       # still the bucket slot
+        assert util.rel_err(p.grad, 2 * q.grad) < 2e-6, k
+        n += 1
+    assert n == len(params) >= 12
