@@ -18,6 +18,16 @@
 #include "deform_common.cuh"
 #include "umma.cuh"
 #include "prof.cuh"
+#include <cstdio>
+#ifdef FDGS_PHASE_TIMING
+#define PT_DECL long long pt_[8] = {0,0,0,0,0,0,0,0}; long long pt_t = clock64();
+#define PT(i) { const long long n_ = clock64(); pt_[i] += n_ - pt_t; pt_t = n_; }
+#define PT_PRINT if (blockIdx.x == 0 && tid == 0) printf("fwd phases (cycles, CTA0): sample %lld | wait_trunk %lld | trunk_epi %lld | wait_z %lld | relu_pass %lld | wait_out %lld | out_pass %lld\n", pt_[0], pt_[1], pt_[2], pt_[3], pt_[4], pt_[5], pt_[6]);
+#else
+#define PT_DECL
+#define PT(i)
+#define PT_PRINT
+#endif
 
 namespace fdgs_deform_tc {
 using namespace fdgs_deform;
@@ -269,6 +279,7 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
         const int items = F >> 2;
         const int LP = (items & 7) == 0 ? 8 : 4, IPT = items / LP, PPW = 32 / LP, SPASS = TP / (8 * PPW);
         const int sg = lane / LP, sq = lane % LP;
+        PT_DECL
         for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
             const int p0 = tile * TP;
             const size_t rowoff = (size_t)tile * TP * WN + (row >> 5) * 32 * WN + (row & 31) * 4;   // blocked save layout
@@ -298,10 +309,12 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
             fence_async_smem();
             epi_bar();
             if (tid == 0) mbar_arrive(&bars[B_FEATFULL]);
+            PT(0)
 
             // ---- trunk epilogue: relu(h + b0) -> shared memory hi / lo (A operand of the heads), kept copy ----------
             mbar_wait(&bars[B_ACCFULL], ph_acc); ph_acc ^= 1;
             tc_fence_after();
+            PT(1)
 #pragma unroll 1
             for (int c0 = 0; c0 < NH; c0 += 32) {
                 uint32_t v[32];
@@ -326,14 +339,32 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
             tc_fence_before();
             epi_bar();
             if (tid == 0) mbar_arrive(&bars[B_HFULL]);
+            PT(2)
 
             // ---- heads -----------------------------------------------------------------------------------------
             for (int i = 0; i < plan.nheads; ++i) {
                 const int h = plan.heads[i];
                 const int NO = head_out(h);
+                // base values (the head's input rows of this tile, contiguous) are fetched now: their DRAM latency hides
+                // behind the two GEMMs.  Thread t owns float4s t, t + 256, ... of the tile's rows * NO floats.
+                float* outp = h == 0 ? io.o_xyz : h == 1 ? io.o_scales : h == 2 ? io.o_rot : h == 3 ? io.o_opacity : io.o_shs;
+                const float* inp = h == 0 ? io.xyz : h == 1 ? io.scales : h == 2 ? io.rot : h == 3 ? io.opacity : io.shs;
+                const int rows = io.P - p0 < TP ? io.P - p0 : TP;
+                const int total = rows * NO;
+                const bool vec = (total & 3) == 0 && !(h == 2 && lo.apply_rotation) && !(h == 4 && io.sh_coeffs != 16);
+                float4 base[6];
+                if (vec) {
+                    const float4* src4 = reinterpret_cast<const float4*>(inp + (size_t)p0 * NO);
+#pragma unroll
+                    for (int k = 0; k < 6; ++k) {
+                        const int i4 = tid + k * NEPI;
+                        base[k] = (i4 * 4 < total) ? __ldcs(src4 + i4) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    }
+                }
                 // z = relu(acc + b1): kept copy, hi / lo -> TMEM (A operand of the output layer)
                 mbar_wait(&bars[B_ACCFULL], ph_acc); ph_acc ^= 1;
                 tc_fence_after();
+                PT(3)
                 float* rz = io.S_RZ[h] ? io.S_RZ[h] + rowoff : nullptr;
 #pragma unroll 1
                 for (int c0 = 0; c0 < NH; c0 += 16) {
@@ -361,10 +392,12 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
                 tc_fence_before();
                 epi_bar();
                 if (tid == 0) mbar_arrive(&bars[B_RZFULL]);
+                PT(4)
 
                 // o = relu(z) W2^T (+ b2): accumulator -> staging [row][NO] -> coalesced base + delta
                 mbar_wait(&bars[B_OUTFULL], ph_out); ph_out ^= 1;
                 tc_fence_after();
+                PT(5)
                 {
                     const int npt = plan.nop[i] >> 1;                 // output columns per thread: 8 or 24
                     for (int c0 = 0; c0 < npt; c0 += 8) {
@@ -381,13 +414,20 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
                 tc_fence_before();
                 epi_bar();
                 {
-                    float* outp = h == 0 ? io.o_xyz : h == 1 ? io.o_scales : h == 2 ? io.o_rot : h == 3 ? io.o_opacity : io.o_shs;
-                    const float* inp = h == 0 ? io.xyz : h == 1 ? io.scales : h == 2 ? io.rot : h == 3 ? io.opacity : io.shs;
                     const bool nobase = (h == 2 && lo.apply_rotation);
-                    const int rows = io.P - p0 < TP ? io.P - p0 : TP;
-                    const int total = rows * NO;
                     float* dst = outp + (size_t)p0 * NO;
-                    if (h == 4 && io.sh_coeffs != 16) {               // M = 1 broadcast: base index (p, n % 3)
+                    if (vec) {
+                        float4* dst4 = reinterpret_cast<float4*>(dst);
+                        const float4* o4 = reinterpret_cast<const float4*>(OUTs);
+#pragma unroll
+                        for (int k = 0; k < 6; ++k) {
+                            const int i4 = tid + k * NEPI;
+                            if (i4 * 4 < total) {
+                                const float4 d = o4[i4];
+                                dst4[i4] = make_float4(base[k].x + d.x, base[k].y + d.y, base[k].z + d.z, base[k].w + d.w);
+                            }
+                        }
+                    } else if (h == 4 && io.sh_coeffs != 16) {        // M = 1 broadcast: base index (p, n % 3)
                         for (int idx = tid; idx < total; idx += NEPI) {
                             const int r = idx / NO, n = idx % NO;
                             dst[idx] = inp[(size_t)(p0 + r) * io.sh_coeffs * 3 + (n % 3)] + OUTs[idx];
@@ -400,8 +440,10 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
                     }
                 }
                 epi_bar();                                            // staging buffer free for the next head
+                PT(6)
             }
         }
+        PT_PRINT
     }
     // ---- teardown ----------------------------------------------------------------------------------------
     tc_fence_before();
