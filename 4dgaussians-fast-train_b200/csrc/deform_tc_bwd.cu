@@ -273,29 +273,36 @@ __device__ __forceinline__ void sample_bwd4(const Layout& lo, int l, const float
 
 // ---- upstream gradient g_o hi/lo -> TMEM (A operand of g_relu_z = g_o W2) ----------------------------------------------
 // The thread's g_o columns are [hf*24, hf*24+24) of 48 for dshs, and all 8 (zero padded) on the hf == 0 warps otherwise.
-__device__ __forceinline__ void stage_go(uint32_t lane_base, int hf, int NO, bool valid, const float* __restrict__ gsrc) {
+// go_load is issued early (global latency hides behind the barrier waits), go_store writes the split values to TMEM.
+__device__ __forceinline__ void go_load(float (&x)[24], int hf, int NO, bool valid, const float* __restrict__ gsrc) {
+#pragma unroll
+    for (int j = 0; j < 24; ++j) x[j] = 0.f;
+    if (!valid) return;
+    if (NO == 48) {
+#pragma unroll
+        for (int c = 0; c < 24; c += 4) {
+            const float4 v = *reinterpret_cast<const float4*>(gsrc + hf * 24 + c);
+            x[c] = v.x; x[c + 1] = v.y; x[c + 2] = v.z; x[c + 3] = v.w;
+        }
+    } else if (hf == 0) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) if (j < NO) x[j] = gsrc[j];
+    }
+}
+__device__ __forceinline__ void go_store(uint32_t lane_base, int hf, int NO, const float (&x)[24]) {
     if (NO == 48) {
 #pragma unroll
         for (int c = 0; c < 24; c += 8) {
-            float4 v0 = make_float4(0.f, 0.f, 0.f, 0.f), v1 = v0;
-            if (valid) {
-                v0 = *reinterpret_cast<const float4*>(gsrc + hf * 24 + c);
-                v1 = *reinterpret_cast<const float4*>(gsrc + hf * 24 + c + 4);
-            }
-            const float x[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
             uint32_t hi[8], lw[8];
 #pragma unroll
-            for (int j = 0; j < 8; ++j) { float a, b; split_tf32_rn(x[j], a, b); hi[j] = __float_as_uint(a); lw[j] = __float_as_uint(b); }
+            for (int j = 0; j < 8; ++j) { float a, b; split_tf32_rn(x[c + j], a, b); hi[j] = __float_as_uint(a); lw[j] = __float_as_uint(b); }
             tmem_st8(lane_base + TM_GHI + hf * 24 + c, hi);
             tmem_st8(lane_base + TM_GLO + hf * 24 + c, lw);
         }
     } else if (hf == 0) {
         uint32_t hi[8], lw[8];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            const float x = (valid && j < NO) ? gsrc[j] : 0.f;
-            float a, b; split_tf32_rn(x, a, b); hi[j] = __float_as_uint(a); lw[j] = __float_as_uint(b);
-        }
+        for (int j = 0; j < 8; ++j) { float a, b; split_tf32_rn(x[j], a, b); hi[j] = __float_as_uint(a); lw[j] = __float_as_uint(b); }
         tmem_st8(lane_base + TM_GHI, hi);
         tmem_st8(lane_base + TM_GLO, lw);
     }
@@ -645,6 +652,8 @@ k_deform_bwd_data(Layout lo, Plan plan, Smem sp, Net net, IO io, const float* __
                 const size_t rowoff = (size_t)tile * TP * WN + (row >> 5) * 32 * WN + (row & 31) * 4;
                 float* gz_row = io.S_GZ[i] + rowoff;
                 uint32_t zgate[NH / 32 + 1];
+                float gox[24];
+                go_load(gox, hf, NO, valid, gsrc);
                 if constexpr (SAVED) {
                     gate_from_saved<NH>(io.V_RZ[i] + rowoff, col0, zgate);
                     if (i > 0) {                                    // g_relu_h += g_z W1 of the previous head has read its g_z
@@ -658,7 +667,7 @@ k_deform_bwd_data(Layout lo, Plan plan, Smem sp, Net net, IO io, const float* __
                     PT(3)
                     head_pass1<NH>(lane_base, col0, B1s + h * WN, io.S_RZ[i] + rowoff, zgate);
                 }
-                stage_go(lane_base, hf, NO, valid, gsrc);
+                go_store(lane_base, hf, NO, gox);
                 tc_fence_before();
                 epi_bar();
                 if (tid == 0) mbar_arrive(&bars[B_GOFULL]);        // z drained from the accumulator, g_o staged in TMEM
