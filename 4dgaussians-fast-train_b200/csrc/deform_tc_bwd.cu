@@ -827,7 +827,9 @@ k_deform_bwd_weights(WArgs args)
     const int N16 = (J.nb + 15) & ~15;
     const int nblkB = (J.nb + 31) >> 5;
     const int stage_floats = 2 * 4096 + 2 * nblkB * 1024;         // A_hi[4][32][32], A_lo, B_hi[nblkB][32][32], B_lo
-    const int rawA_f = 32 * J.lda, rawB_f = J.blkB ? 32 * J.ldb : 0;
+    // raw stage: the 32 rows of A (blocked) and of B (blocked, or row-major [32][ldb] for the upstream gradients g_o)
+    const int rawA_f = 32 * J.lda, rawB_f = 32 * J.ldb;
+    const long long fullB = J.blkB ? nst : (long long)J.rowsB / WK;   // stages whose 32 B rows all exist in memory
     const int raw_floats = (rawA_f + rawB_f + 255) & ~255;
     float* raw0 = sm + (size_t)TSTAGES * stage_floats;
 
@@ -849,23 +851,23 @@ k_deform_bwd_weights(WArgs args)
         // ===== producer ====================================================================================
         if (lane == 0) {
             uint32_t g = 0;
-            const uint32_t bytes = (uint32_t)(rawA_f + rawB_f) * 4;
             constexpr int PFD = 8;                                  // stages prefetched into L2 ahead of the ring
             for (long long s = s_begin; s < s_end && s < s_begin + PFD; ++s) {
                 bulk_prefetch_l2(J.A + (size_t)s * rawA_f, (uint32_t)rawA_f * 4);
-                if (rawB_f) bulk_prefetch_l2(J.B + (size_t)s * rawB_f, (uint32_t)rawB_f * 4);
+                if (s < fullB) bulk_prefetch_l2(J.B + (size_t)s * rawB_f, (uint32_t)rawB_f * 4);
             }
             for (long long s = s_begin; s < s_end; ++s, ++g) {
                 const uint32_t slot = g % RSTAGES;
                 if (s + PFD < s_end) {
                     bulk_prefetch_l2(J.A + (size_t)(s + PFD) * rawA_f, (uint32_t)rawA_f * 4);
-                    if (rawB_f) bulk_prefetch_l2(J.B + (size_t)(s + PFD) * rawB_f, (uint32_t)rawB_f * 4);
+                    if (s + PFD < fullB) bulk_prefetch_l2(J.B + (size_t)(s + PFD) * rawB_f, (uint32_t)rawB_f * 4);
                 }
+                const bool withB = s < fullB;                       // a partial last stage of g_o is read with checked loads
                 mbar_wait(&bars[WB_REMPTY + slot], ((g / RSTAGES) & 1) ^ 1);
-                mbar_expect_tx(&bars[WB_RFULL + slot], bytes);
+                mbar_expect_tx(&bars[WB_RFULL + slot], (uint32_t)(rawA_f + (withB ? rawB_f : 0)) * 4);
                 float* dst = raw0 + (size_t)slot * raw_floats;
                 bulk_g2s(dst, J.A + (size_t)s * rawA_f, (uint32_t)rawA_f * 4, &bars[WB_RFULL + slot]);
-                if (rawB_f) bulk_g2s(dst + rawA_f, J.B + (size_t)s * rawB_f, (uint32_t)rawB_f * 4, &bars[WB_RFULL + slot]);
+                if (withB) bulk_g2s(dst + rawA_f, J.B + (size_t)s * rawB_f, (uint32_t)rawB_f * 4, &bars[WB_RFULL + slot]);
             }
         }
         __syncwarp();
@@ -931,14 +933,6 @@ k_deform_bwd_weights(WArgs args)
         for (int i = 0; i < NI; ++i) { oA[i] = tile32_off(rowA[i], cgA * 4, WK); oB[i] = tile32_off(rowB[i], cgB * 4, WK); }
         float sa[4] = {0.f, 0.f, 0.f, 0.f}, sb[4] = {0.f, 0.f, 0.f, 0.f};
         const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
-        float4 vbn[NI];                                             // row-major B: one stage of register prefetch
-#pragma unroll
-        for (int i = 0; i < NI; ++i) vbn[i] = z4;
-        auto issueB = [&](long long s) {
-#pragma unroll
-            for (int i = 0; i < NI; ++i) vbn[i] = actB[i] ? load4(J.B, J.ldb, s * WK + rowB[i], cgB * 4, J.nb, J.rowsB) : z4;
-        };
-        if (!J.blkB && s_begin < s_end) issueB(s_begin);
         uint32_t g = 0;
         for (long long s = s_begin; s < s_end; ++s, ++g) {
             const uint32_t rslot = g % RSTAGES, tslot = g % TSTAGES;
@@ -951,10 +945,22 @@ k_deform_bwd_weights(WArgs args)
             if (J.blkB) {
 #pragma unroll
                 for (int i = 0; i < NI; ++i) vb[i] = (actB[i] && onB) ? *reinterpret_cast<const float4*>(rawB + (cgB * 32 + rowB[i]) * 4) : z4;
+            } else if (s < fullB) {                                  // row-major [32][ldb] rows of g_o in the raw stage
+#pragma unroll
+                for (int i = 0; i < NI; ++i) {
+                    vb[i] = z4;
+                    if (actB[i] && onB) {
+                        const float* r = rawB + rowB[i] * J.ldb + cgB * 4;
+                        const int c = cgB * 4;
+                        vb[i].x = r[0];
+                        if (c + 1 < J.nb) vb[i].y = r[1];
+                        if (c + 2 < J.nb) vb[i].z = r[2];
+                        if (c + 3 < J.nb) vb[i].w = r[3];
+                    }
+                }
             } else {
 #pragma unroll
-                for (int i = 0; i < NI; ++i) vb[i] = vbn[i];
-                if (s + 1 < s_end) issueB(s + 1);
+                for (int i = 0; i < NI; ++i) vb[i] = actB[i] ? load4(J.B, J.ldb, s * WK + rowB[i], cgB * 4, J.nb, J.rowsB) : z4;
             }
             float4 ahi[NI], alo[NI], bhi[NI], blo[NI];
 #pragma unroll
@@ -1129,7 +1135,7 @@ int backward(const Layout& lo, const FdgsDeformBackward* a, const float* packed,
         wa.j[nj] = WJob{io.S_GZ[j], Wn, Wn, (int)plan.Pp, io.S_H, Wn, Wn, (int)plan.Pp, dw1[h], Wn, 0, a->d_head_b1[h], nullptr, 1, 1, 1};
         cost[nj++] = 1.0;                                 // relative per-stage cost, measured (cycles/stage 1750 : 2050 : 1530)
         wa.j[nj] = WJob{io.S_RZ[j], Wn, Wn, (int)plan.Pp, gsrc[h], NO, NO, a->P, a->d_head_w2[h], Wn, 1, nullptr, a->d_head_b2[h], 1, 1, 0};
-        cost[nj++] = 1.17;
+        cost[nj++] = 0.87;
     }
     wa.j[nj] = WJob{io.S_GH, Wn, Wn, (int)plan.Pp, io.S_F, F, F, (int)plan.Pp, a->d_trunk_w[0], F, 0, a->d_trunk_b[0], nullptr, 1, 1, 1};
     cost[nj++] = 0.87;
