@@ -65,7 +65,8 @@ struct GradPtrs {
 
 // Activations the training forward keeps for the backward (floats; rows padded to whole 128-point tiles, blocked layout
 // [tile][row/32][col/4][row%32][4] so that 32 consecutive rows are one contiguous run of 32*cols floats).
-struct SaveLayout { long long Pp, off_F, off_H, off_RZ[FDGS_NUM_HEADS], total; };
+// off_M: ReLU gate bit masks, uint32 [6 slots: trunk, head 0..4][Pp][4 words: column half 0 (2 words), half 1 (2 words)].
+struct SaveLayout { long long Pp, off_F, off_H, off_RZ[FDGS_NUM_HEADS], off_M, total; };
 static inline SaveLayout make_save_layout(const Layout& lo, int P) {
     SaveLayout s;
     s.Pp = (((long long)P + TP - 1) / TP) * TP;
@@ -74,6 +75,7 @@ static inline SaveLayout make_save_layout(const Layout& lo, int P) {
     s.off_F = o; o += al(s.Pp * lo.F);
     s.off_H = o; o += al(s.Pp * lo.Wn);
     for (int h = 0; h < FDGS_NUM_HEADS; ++h) { s.off_RZ[h] = o; if ((lo.head_mask >> h) & 1) o += al(s.Pp * lo.Wn); }
+    s.off_M = o; o += al(6 * s.Pp * 4);
     s.total = o;
     return s;
 }

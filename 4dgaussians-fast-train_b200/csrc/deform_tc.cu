@@ -107,6 +107,8 @@ struct TcFwdIO {
     // training: activations kept for the backward pass (blocked layout [tile][row/32][col/4][row%32][4]); null = none
     float *S_F, *S_H;
     float* S_RZ[FDGS_NUM_HEADS];     // by head id
+    uint32_t* S_M;                   // ReLU gate masks [6][Pp][4]
+    long long Pp;
 };
 
 // shared-memory plan (floats unless noted), all offsets multiples of 256 floats
@@ -320,12 +322,14 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
                 uint32_t v[32];
                 tmem_ld32(lane_base + TM_ACC + col0 + c0, v);
                 tmem_wait_ld();
+                uint32_t m = 0;
 #pragma unroll
                 for (int j = 0; j < 32; j += 4) {
                     float x[4], a[4], b[4];
 #pragma unroll
                     for (int u = 0; u < 4; ++u) {
                         x[u] = fmaxf(__uint_as_float(v[j + u]) + B0s[col0 + c0 + j + u], 0.f);
+                        m |= (x[u] > 0.f ? 1u : 0u) << (j + u);
                         split_tf32_rn(x[u], a[u], b[u]);
                     }
                     const int o = tile_off(row, col0 + c0 + j, 128);
@@ -334,6 +338,7 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
                     if (io.S_H)
                         __stcs(reinterpret_cast<float4*>(io.S_H + rowoff + ((col0 + c0 + j) >> 2) * 128), make_float4(x[0], x[1], x[2], x[3]));
                 }
+                if (io.S_M) io.S_M[((size_t)(p0 + row)) * 4 + hf * 2 + (c0 >> 5)] = m;
             }
             fence_async_smem();
             tc_fence_before();
@@ -366,7 +371,8 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
                 tc_fence_after();
                 PT(3)
                 float* rz = io.S_RZ[h] ? io.S_RZ[h] + rowoff : nullptr;
-#pragma unroll 1
+                uint32_t zm[2] = {0u, 0u};
+#pragma unroll
                 for (int c0 = 0; c0 < NH; c0 += 16) {
                     uint32_t v[16], hi[16], lw[16];
                     tmem_ld16(lane_base + TM_ACC + col0 + c0, v);
@@ -378,6 +384,7 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
                         split_tf32_rn(z, a, b);
                         hi[j] = __float_as_uint(a); lw[j] = __float_as_uint(b);
                         v[j] = __float_as_uint(z);
+                        zm[c0 >> 5] |= (z > 0.f ? 1u : 0u) << ((c0 & 31) + j);
                     }
                     if (rz) {
 #pragma unroll
@@ -387,6 +394,11 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
                     }
                     tmem_st16(lane_base + TM_ZHI + col0 + c0, hi);
                     tmem_st16(lane_base + TM_ZLO + col0 + c0, lw);
+                }
+                if (io.S_M) {
+                    uint32_t* mp = io.S_M + ((size_t)(1 + h) * io.Pp + (p0 + row)) * 4 + hf * 2;
+                    mp[0] = zm[0];
+                    if (NH > 32) mp[1] = zm[1];
                 }
                 tmem_wait_st();
                 tc_fence_before();
@@ -500,13 +512,14 @@ int forward(const Layout& lo, const FdgsDeformForward* a, const float* packed, c
     io.P = a->P; io.sh_coeffs = a->sh_coeffs;
     io.xyz = a->xyz; io.scales = a->scales; io.rot = a->rotations; io.opacity = a->opacity; io.shs = a->shs;
     io.o_xyz = a->out_xyz; io.o_scales = a->out_scales; io.o_rot = a->out_rotations; io.o_opacity = a->out_opacity; io.o_shs = a->out_shs;
-    io.S_F = nullptr; io.S_H = nullptr;
+    io.S_F = nullptr; io.S_H = nullptr; io.S_M = nullptr; io.Pp = 0;
     for (int h = 0; h < FDGS_NUM_HEADS; ++h) io.S_RZ[h] = nullptr;
     if (a->save_ws) {
         if (a->save_bytes < save_bytes(lo, a->P)) return FDGS_E_WORKSPACE;
         SaveLayout sl = make_save_layout(lo, a->P);
         float* S = (float*)a->save_ws;
         io.S_F = S + sl.off_F; io.S_H = S + sl.off_H;
+        io.S_M = reinterpret_cast<uint32_t*>(S + sl.off_M); io.Pp = sl.Pp;
         for (int h = 0; h < FDGS_NUM_HEADS; ++h) if ((lo.head_mask >> h) & 1) io.S_RZ[h] = S + sl.off_RZ[h];
     }
     const int ntiles = (a->P + TP - 1) / TP;

@@ -127,6 +127,8 @@ struct IO {
     // activations kept by the forward (SAVED kernels read these instead of recomputing), same blocked layout
     const float *V_H;
     const float* V_RZ[FDGS_NUM_HEADS];     // indexed by plan slot j
+    const uint32_t* V_M;                   // ReLU gate masks [6: trunk, head id 0..4][Pp][4]
+    long long Pp;
 };
 
 struct Smem {
@@ -572,12 +574,47 @@ k_deform_bwd_data(Layout lo, Plan plan, Smem sp, Net net, IO io, const float* __
         const int LP = (items & 7) == 0 ? 8 : 4, IPT = items / LP, PPW = 32 / LP, SPASS = TP / (8 * PPW);
         const int sg = lane / LP, sq = lane % LP;
         PT_DECL
+        float* GF = HS_hi;                   // g_feat staging tile [F][128]: every MMA that read relu(h) has completed by then
+        int pend_tile = -1, pend_pass = 0;
+        // One quarter (8*PPW points) of a tile's sampler backward: plane-gradient scatter + d_xyz.  In SAVED mode these
+        // passes are issued between the head steps of the following tile, where the epilogue warps would otherwise
+        // wait for the tensor core.
+        auto samp_pass = [&](int t, int pass) {
+            const int srow = pass * (8 * PPW) + warp * PPW + sg;
+            const int sp_ = t * TP + srow;
+            const bool sval = sp_ < io.P;
+            float q[4] = {0.f, 0.f, 0.f, 0.f};
+            if (sval) point_coords(lo, io.xyz, sp_, 0.f, q);
+            float dq[3] = {0.f, 0.f, 0.f};
+            for (int it = 0; it < IPT; ++it) {
+                const int item = sq + it * LP;
+                const int l = (item * 4) / C, c0 = (item * 4) % C;
+                const float4 d4 = *reinterpret_cast<const float4*>(GF + tile_off(srow, item * 4, 128));
+                const float df[4] = {d4.x, d4.y, d4.z, d4.w};
+                if (sval) sample_bwd4(lo, l, q, packed, trow, gpacked, gtrow, c0, df, dq);
+            }
+#pragma unroll
+            for (int a = 0; a < 3; ++a) {
+                dq[a] += __shfl_xor_sync(0xffffffffu, dq[a], 1);
+                dq[a] += __shfl_xor_sync(0xffffffffu, dq[a], 2);
+                if (LP == 8) dq[a] += __shfl_xor_sync(0xffffffffu, dq[a], 4);
+            }
+            if (sq == 0 && sval) {
+#pragma unroll
+                for (int a = 0; a < 3; ++a) {
+                    const float mx = lo.aabb[a], mn = lo.aabb[3 + a];
+                    io.d_xyz[3 * (size_t)sp_ + a] = dq[a] * (2.0f / (mn - mx));
+                }
+            }
+        };
         for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
             const int p = tile * TP + row;
             const bool valid = p < io.P;
             uint32_t gate[NH / 32 + 1];
             if constexpr (SAVED) {
-                gate_from_saved<NH>(io.V_H + (size_t)tile * TP * WN + (row >> 5) * 32 * WN + (row & 31) * 4, col0, gate);
+                const uint32_t* mp = io.V_M + (size_t)p * 4 + hf * 2;
+                gate[0] = __ldcs(mp);
+                if (NH > 32) gate[1] = __ldcs(mp + 1);
             } else {
             // ---- HexPlane sampling -> feat tile (hi / lo) + scratch ----------------------------------------
             // Sampler mapping: LP adjacent lanes share one point and take consecutive channel quads, so a warp-wide
@@ -655,7 +692,9 @@ k_deform_bwd_data(Layout lo, Plan plan, Smem sp, Net net, IO io, const float* __
                 float gox[24];
                 go_load(gox, hf, NO, valid, gsrc);
                 if constexpr (SAVED) {
-                    gate_from_saved<NH>(io.V_RZ[i] + rowoff, col0, zgate);
+                    const uint32_t* mp = io.V_M + ((size_t)(1 + h) * io.Pp + p) * 4 + hf * 2;
+                    zgate[0] = __ldcs(mp);
+                    if (NH > 32) zgate[1] = __ldcs(mp + 1);
                     if (i > 0) {                                    // g_relu_h += g_z W1 of the previous head has read its g_z
                         mbar_wait(&bars[B_GRHFULL], ph_grh); ph_grh ^= 1;
                         tc_fence_after();
@@ -677,6 +716,7 @@ k_deform_bwd_data(Layout lo, Plan plan, Smem sp, Net net, IO io, const float* __
                 tc_fence_before();
                 epi_bar();
                 if (tid == 0) mbar_arrive(&bars[B_GZFULL]);
+                if (pend_tile >= 0 && pend_pass < SPASS) samp_pass(pend_tile, pend_pass++);     // overlaps g_relu_h += g_z W1
                 PT(4)
             }
 
@@ -715,8 +755,11 @@ k_deform_bwd_data(Layout lo, Plan plan, Smem sp, Net net, IO io, const float* __
             mbar_wait(&bars[B_GFFULL], ph_gf); ph_gf ^= 1;
             tc_fence_after();
             PT(7)
-            // accumulator rows (TMEM lane = point) -> shared memory, so that the sampler mapping can read any point
-            float* GF = HS_hi;                                       // every MMA that read relu(h) has completed
+            // accumulator rows (TMEM lane = point) -> shared memory, so that the sampler mapping can read any point.
+            // SAVED: the scatter passes of this tile run inside the NEXT tile's head loop (see samp_pass), so first
+            // finish whatever is still pending of the previous tile: the staging buffer is about to be overwritten.
+            while (pend_tile >= 0 && pend_pass < SPASS) samp_pass(pend_tile, pend_pass++);
+            epi_bar();
             for (int l = 0; l < lo.L; ++l)
                 for (int cc = 0; cc < CH; cc += 4) {
                     const int c0 = l * C + hf * CH + cc;
@@ -728,38 +771,15 @@ k_deform_bwd_data(Layout lo, Plan plan, Smem sp, Net net, IO io, const float* __
                 }
             tc_fence_before();
             epi_bar();
-            for (int pass = 0; pass < SPASS; ++pass) {
-                const int srow = pass * (8 * PPW) + warp * PPW + sg;
-                const int sp_ = tile * TP + srow;
-                const bool sval = sp_ < io.P;
-                float q[4] = {0.f, 0.f, 0.f, 0.f};
-                if (sval) point_coords(lo, io.xyz, sp_, 0.f, q);
-                float dq[3] = {0.f, 0.f, 0.f};
-                for (int it = 0; it < IPT; ++it) {
-                    const int item = sq + it * LP;
-                    const int l = (item * 4) / C, c0 = (item * 4) % C;
-                    const float4 d4 = *reinterpret_cast<const float4*>(GF + tile_off(srow, item * 4, 128));
-                    const float df[4] = {d4.x, d4.y, d4.z, d4.w};
-                    if (sval) sample_bwd4(lo, l, q, packed, trow, gpacked, gtrow, c0, df, dq);
-                }
-#pragma unroll
-                for (int a = 0; a < 3; ++a) {
-                    dq[a] += __shfl_xor_sync(0xffffffffu, dq[a], 1);
-                    dq[a] += __shfl_xor_sync(0xffffffffu, dq[a], 2);
-                    if (LP == 8) dq[a] += __shfl_xor_sync(0xffffffffu, dq[a], 4);
-                }
-                if (sq == 0 && sval) {
-#pragma unroll
-                    for (int a = 0; a < 3; ++a) {
-                        const float mx = lo.aabb[a], mn = lo.aabb[3 + a];
-                        io.d_xyz[3 * (size_t)sp_ + a] = dq[a] * (2.0f / (mn - mx));
-                    }
-                }
+            pend_tile = tile; pend_pass = 0;
+            if constexpr (!SAVED) {                                  // the staging buffer aliases relu(h): scatter now
+                while (pend_pass < SPASS) samp_pass(pend_tile, pend_pass++);
+                epi_bar();
             }
             PT(8)
-            epi_bar();          // the feat / relu(h) / g_feat buffer is free again
             PT(9)
         }
+        while (pend_tile >= 0 && pend_pass < SPASS) samp_pass(pend_tile, pend_pass++);
         PT_PRINT
     }
     tc_fence_before();
@@ -1104,10 +1124,11 @@ int backward(const Layout& lo, const FdgsDeformBackward* a, const float* packed,
     for (int h = 0; h < FDGS_NUM_HEADS; ++h) io.g[h] = gsrc[h];
     io.S_F = S + plan.off_F; io.S_H = S + plan.off_H; io.S_GH = S + plan.off_GH;
     for (int j = 0; j < FDGS_NUM_HEADS; ++j) { io.S_RZ[j] = S + plan.off_RZ[j]; io.S_GZ[j] = S + plan.off_GZ[j]; }
-    io.V_H = nullptr;
+    io.V_H = nullptr; io.V_M = nullptr; io.Pp = plan.Pp;
     for (int j = 0; j < FDGS_NUM_HEADS; ++j) io.V_RZ[j] = nullptr;
     if (saved) {        // the forward kept feat, relu(h), relu(z_j): nothing is recomputed and the weight kernel reads them in place
         io.V_H = V + sl.off_H;
+        io.V_M = reinterpret_cast<const uint32_t*>(V + sl.off_M);
         io.S_F = const_cast<float*>(V + sl.off_F); io.S_H = const_cast<float*>(V + sl.off_H);
         for (int j = 0; j < plan.nheads; ++j) { io.V_RZ[j] = V + sl.off_RZ[plan.heads[j]]; io.S_RZ[j] = const_cast<float*>(io.V_RZ[j]); }
     }
