@@ -371,12 +371,13 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
                 tc_fence_after();
                 PT(3)
                 float* rz = io.S_RZ[h] ? io.S_RZ[h] + rowoff : nullptr;
-                uint32_t zm[2] = {0u, 0u};
-#pragma unroll
+                uint32_t zm0 = 0u, zm1 = 0u;
+#pragma unroll 1
                 for (int c0 = 0; c0 < NH; c0 += 16) {
                     uint32_t v[16], hi[16], lw[16];
                     tmem_ld16(lane_base + TM_ACC + col0 + c0, v);
                     tmem_wait_ld();
+                    uint32_t mbits = 0u;
 #pragma unroll
                     for (int j = 0; j < 16; ++j) {
                         const float z = fmaxf(__uint_as_float(v[j]) + B1s[h * WN + col0 + c0 + j], 0.f);
@@ -384,8 +385,9 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
                         split_tf32_rn(z, a, b);
                         hi[j] = __float_as_uint(a); lw[j] = __float_as_uint(b);
                         v[j] = __float_as_uint(z);
-                        zm[c0 >> 5] |= (z > 0.f ? 1u : 0u) << ((c0 & 31) + j);
+                        mbits |= (z > 0.f ? 1u : 0u) << j;
                     }
+                    if (c0 < 32) zm0 |= mbits << (c0 & 31); else zm1 |= mbits << (c0 & 31);
                     if (rz) {
 #pragma unroll
                         for (int j = 0; j < 16; j += 4)
@@ -397,8 +399,8 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
                 }
                 if (io.S_M) {
                     uint32_t* mp = io.S_M + ((size_t)(1 + h) * io.Pp + (p0 + row)) * 4 + hf * 2;
-                    mp[0] = zm[0];
-                    if (NH > 32) mp[1] = zm[1];
+                    mp[0] = zm0;
+                    if (NH > 32) mp[1] = zm1;
                 }
                 tmem_wait_st();
                 tc_fence_before();
