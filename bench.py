@@ -183,6 +183,7 @@ def algorithmic_per_launch(kernel, s):
         # the MLP backward is 2x the forward FLOPs: one forward's worth of data gradients, one of weight gradients
         # (the activation recompute inside k_deform_bwd_data is NOT counted as algorithmic work)
         "k_deform_bwd_data": ("tensor", mlp_fwd_flop),
+        "k_deform_bwd_data_saved": ("tensor", mlp_fwd_flop),
         "k_deform_bwd_weights": ("tensor", mlp_fwd_flop),
     }
     return table.get(kernel)
