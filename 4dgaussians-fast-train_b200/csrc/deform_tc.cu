@@ -282,32 +282,46 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
         const int LP = (items & 7) == 0 ? 8 : 4, IPT = items / LP, PPW = 32 / LP, SPASS = TP / (8 * PPW);
         const int sg = lane / LP, sq = lane % LP;
         PT_DECL
+        // HexPlane sampling of one quarter (8*PPW points) of tile t into registers/local memory.  The passes of tile t+1
+        // are issued inside tile t's head loop, where the epilogue warps would otherwise wait for the output-layer GEMM.
+        float4 nf[8];                                                // SPASS * IPT <= 8 float4 per thread
+        auto sample_pass = [&](int t, int pass) {
+            const int srow = pass * (8 * PPW) + warp * PPW + sg;
+            const int sp_ = t * TP + srow;
+            const bool sval = sp_ < io.P;
+            float q[4] = {0.f, 0.f, 0.f, 0.f};
+            if (sval) point_coords(lo, io.xyz, sp_, 0.f, q);
+            for (int it = 0; it < IPT; ++it) {
+                const int item = sq + it * LP;
+                const int l = (item * 4) / C, c0 = (item * 4) % C;
+                float prod[4] = {0.f, 0.f, 0.f, 0.f};
+                if (sval) sample_level<4>(lo, l, q, packed, trow, c0, prod);
+                nf[pass * IPT + it] = make_float4(prod[0], prod[1], prod[2], prod[3]);
+            }
+        };
+        if ((int)blockIdx.x < ntiles)
+            for (int pass = 0; pass < SPASS; ++pass) sample_pass(blockIdx.x, pass);
         for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
             const int p0 = tile * TP;
             const size_t rowoff = (size_t)tile * TP * WN + (row >> 5) * 32 * WN + (row & 31) * 4;   // blocked save layout
-            // ---- HexPlane sampling -> feat tile (hi / lo) ---------------------------------------------------
+            // ---- feat tile (hi / lo) from the values sampled ahead of time (see sample_pass) -------------------
             for (int pass = 0; pass < SPASS; ++pass) {
                 const int srow = pass * (8 * PPW) + warp * PPW + sg;
-                const int sp_ = p0 + srow;
-                const bool sval = sp_ < io.P;
-                float q[4] = {0.f, 0.f, 0.f, 0.f};
-                if (sval) point_coords(lo, io.xyz, sp_, 0.f, q);
                 for (int it = 0; it < IPT; ++it) {
                     const int item = sq + it * LP;
-                    const int l = (item * 4) / C, c0 = (item * 4) % C;
-                    float prod[4] = {0.f, 0.f, 0.f, 0.f};
-                    if (sval) sample_level<4>(lo, l, q, packed, trow, c0, prod);
+                    const float4 pr = nf[pass * IPT + it];
                     float4 hi, lw;
-                    split_tf32_rn(prod[0], hi.x, lw.x); split_tf32_rn(prod[1], hi.y, lw.y);
-                    split_tf32_rn(prod[2], hi.z, lw.z); split_tf32_rn(prod[3], hi.w, lw.w);
+                    split_tf32_rn(pr.x, hi.x, lw.x); split_tf32_rn(pr.y, hi.y, lw.y);
+                    split_tf32_rn(pr.z, hi.z, lw.z); split_tf32_rn(pr.w, hi.w, lw.w);
                     const int o = tile_off(srow, item * 4, 128);
                     *reinterpret_cast<float4*>(F_hi + o) = hi;
                     *reinterpret_cast<float4*>(F_lo + o) = lw;
                     if (io.S_F)
-                        __stcs(reinterpret_cast<float4*>(io.S_F + (size_t)tile * TP * F + (srow >> 5) * 32 * F + (item * 32 + (srow & 31)) * 4),
-                               make_float4(prod[0], prod[1], prod[2], prod[3]));
+                        __stcs(reinterpret_cast<float4*>(io.S_F + (size_t)tile * TP * F + (srow >> 5) * 32 * F + (item * 32 + (srow & 31)) * 4), pr);
                 }
             }
+            const int next_tile = tile + gridDim.x;
+            int next_pass = 0;
             fence_async_smem();
             epi_bar();
             if (tid == 0) mbar_arrive(&bars[B_FEATFULL]);
@@ -406,6 +420,7 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
                 tc_fence_before();
                 epi_bar();
                 if (tid == 0) mbar_arrive(&bars[B_RZFULL]);
+                if (next_tile < ntiles && next_pass < SPASS) sample_pass(next_tile, next_pass++);     // overlaps o_i GEMM
                 PT(4)
 
                 // o = relu(z) W2^T (+ b2): accumulator -> staging [row][NO] -> coalesced base + delta
@@ -456,6 +471,7 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
                 epi_bar();                                            // staging buffer free for the next head
                 PT(6)
             }
+            while (next_tile < ntiles && next_pass < SPASS) sample_pass(next_tile, next_pass++);
         }
         PT_PRINT
     }
