@@ -192,9 +192,9 @@ def algorithmic_per_launch(kernel, s):
 # dram__bytes_read.sum + dram__bytes_write.sum per launch from the `ncu --set full` capture of this workload
 # (profiles/r01_ncu_full_summary.csv; P = 300k DyNeRF view).  Reported only for that workload.
 NCU_TRAFFIC_BYTES = {
-    "k_deform_bwd_data": 0.085441e9 + 1.858870e9, "k_deform_bwd_weights": 2.093587e9 + 0.004668e9,
-    "k_deform_fwd_tc": 0.075685e9 + 0.037721e9, "k_blend_bwd": 0.118472e9 + 0.004498e9, "k_blend_fwd": 0.081388e9 + 0.011688e9,
-    "k_tile_sort": 0.024414e9 + 0.026626e9, "k_preprocess": 0.066738e9 + 0.003318e9, "k_preprocess_bwd": 0.092924e9 + 0.037773e9,
+    "k_deform_fwd_tc": 0.075828e9 + 1.007398e9, "k_deform_bwd_data_saved": 0.114425e9 + 0.885651e9,
+    "k_deform_bwd_weights": 1.975819e9 + 0.004271e9, "k_blend_bwd": 0.118526e9 + 0.003856e9, "k_blend_fwd": 0.081387e9 + 0.010402e9,
+    "k_tile_sort": 0.024415e9 + 0.027028e9, "k_preprocess": 0.066749e9 + 0.004076e9, "k_preprocess_bwd": 0.092867e9 + 0.038299e9,
 }
 
 

@@ -13,7 +13,7 @@ def launches(path):
         v = float(r[vi].replace(",", ""))
         u = r[ui]
         us = v / 1e3 if u in ("ns", "nsecond") else v * 1e3 if u in ("ms", "msecond") else v
-        n = r[ki].split("(")[0][:90]
+        n = r[ki].split("(")[0][:90].replace(",", ";")
         a = agg.setdefault(n, [0, 0.0]); a[0] += 1; a[1] += us
     tot = sum(a[1] for a in agg.values())
     print(f"# total device time {tot/1e3:.3f} ms over {sum(a[0] for a in agg.values())} launches")
@@ -35,7 +35,7 @@ def full(path):
     ki = hdr.index("Kernel Name")
     print("kernel," + ",".join(f"{w} [{units[hdr.index(w)]}]" for w in WANT if w in hdr))
     for r in rows[2:]:
-        print(r[ki].split("(")[0][-60:] + "," + ",".join(r[hdr.index(w)] for w in WANT if w in hdr))
+        print(r[ki].split("(")[0][-60:].replace(",", ";") + "," + ",".join(r[hdr.index(w)] for w in WANT if w in hdr))
 
 if __name__ == "__main__":
     {"launches": launches, "full": full}[sys.argv[1]](sys.argv[2])
