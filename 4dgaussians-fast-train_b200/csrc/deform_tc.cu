@@ -206,69 +206,83 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
         }
         __syncwarp();
     } else if (warp == 9) {
-        // ===== MMA issuer ===================================================================================
-        if (lane == 0) {
+        // ===== MMA issuer: the whole warp runs the loop, one elected lane issues (see umma.cuh:elect_one) ============
+        {
+            const uint32_t tm = __shfl_sync(0xffffffffu, tmem, 0);
+            const uint32_t leader = elect_one();
             const uint32_t idesc = make_idesc_tf32(128, WN, 0, 0);
-            uint32_t g = 0, ph_feat = 0, ph_h = 0, ph_rz = 0;
-            // D[acc] (+)= A . B^T over `nck` streamed chunks of an [N][K] weight; A: shared-memory tile (hi, lo) or TMEM columns
-            auto gemm = [&](uint32_t acc, int nck, int N, uint32_t id, const float* a_hi, const float* a_lo, uint32_t ta_hi, uint32_t ta_lo) {
-                for (int c = 0; c < nck; ++c, ++g) {
-                    const uint32_t slot = g % S;
-                    mbar_wait(&bars[B_WFULL + slot], (g / S) & 1);
+            const uint64_t f_hi0 = desc_kmajor(F_hi, 128, 0), f_lo0 = desc_kmajor(F_lo, 128, 0);   // feat and relu(h) alias
+            const uint32_t ring_u = smem_addr(ring) >> 4;
+            uint32_t slot = 0, wph = 0, ph_feat = 0, ph_h = 0, ph_rz = 0;
+            // D[acc] (+)= A . B^T over `nck` streamed chunks of an [N][K] weight; A: shared-memory tile (SS) or TMEM columns
+            auto gemm = [&](uint32_t acc, int nck, int N, uint32_t id, bool ss, uint32_t ta_hi, uint32_t ta_lo) {
+                const uint64_t bd0 = make_sdesc(0u, (uint32_t)N * 16u, 128u);      // B descriptor without the start address
+                const uint32_t bstep = (uint32_t)N * 2u;                           // 8 K-columns of an N-row tile, 16-byte units
+#pragma unroll 1
+                for (int c = 0; c < nck; ++c) {
+                    mbar_wait(&bars[B_WFULL + slot], wph);
                     tc_fence_after();
-                    const float* bh = ring + (size_t)slot * SLOT;
-                    const float* bl = bh + 16 * N;
+                    if (leader) {
+                        const uint64_t dbh0 = bd0 + (ring_u + slot * (uint32_t)(SLOT / 4));
+                        const uint64_t dbl0 = dbh0 + (uint32_t)N * 4u;             // lo half follows the 16 hi columns
 #pragma unroll
-                    for (int ks = 0; ks < 2; ++ks) {
-                        const int k = c * KCH + ks * 8;
-                        const int first = (c == 0 && ks == 0) ? 0 : 1;
-                        const uint64_t dbh = desc_kmajor(bh, N, ks * 8), dbl = desc_kmajor(bl, N, ks * 8);
-                        if (a_hi) {
-                            if (passes == 3) {
-                                mma_tf32_ss(acc, desc_kmajor(a_lo, 128, k), dbh, id, first);
-                                mma_tf32_ss(acc, desc_kmajor(a_hi, 128, k), dbl, id, 1);
-                                mma_tf32_ss(acc, desc_kmajor(a_hi, 128, k), dbh, id, 1);
+                        for (int ks = 0; ks < 2; ++ks) {
+                            const uint32_t kk = (uint32_t)(c * 2 + ks);
+                            const int first = (c == 0 && ks == 0) ? 0 : 1;
+                            const uint64_t dbh = dbh0 + ks * bstep, dbl = dbl0 + ks * bstep;
+                            if (ss) {
+                                const uint64_t ah = f_hi0 + kk * 256u, al = f_lo0 + kk * 256u;
+                                if (passes == 3) {
+                                    mma_tf32_ss(acc, al, dbh, id, first);
+                                    mma_tf32_ss(acc, ah, dbl, id, 1);
+                                    mma_tf32_ss(acc, ah, dbh, id, 1);
+                                } else {
+                                    mma_tf32_ss(acc, ah, dbh, id, first);
+                                }
                             } else {
-                                mma_tf32_ss(acc, desc_kmajor(a_hi, 128, k), dbh, id, first);
-                            }
-                        } else {
-                            if (passes == 3) {
-                                mma_tf32_ts(acc, ta_lo + (uint32_t)k, dbh, id, first);
-                                mma_tf32_ts(acc, ta_hi + (uint32_t)k, dbl, id, 1);
-                                mma_tf32_ts(acc, ta_hi + (uint32_t)k, dbh, id, 1);
-                            } else {
-                                mma_tf32_ts(acc, ta_hi + (uint32_t)k, dbh, id, first);
+                                if (passes == 3) {
+                                    mma_tf32_ts(acc, ta_lo + kk * 8u, dbh, id, first);
+                                    mma_tf32_ts(acc, ta_hi + kk * 8u, dbl, id, 1);
+                                    mma_tf32_ts(acc, ta_hi + kk * 8u, dbh, id, 1);
+                                } else {
+                                    mma_tf32_ts(acc, ta_hi + kk * 8u, dbh, id, first);
+                                }
                             }
                         }
+                        mma_commit(&bars[B_WEMPTY + slot]);
                     }
-                    mma_commit(&bars[B_WEMPTY + slot]);
+                    __syncwarp();
+                    if (++slot == (uint32_t)S) { slot = 0; wph ^= 1; }
                 }
             };
             for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
                 mbar_wait(&bars[B_FEATFULL], ph_feat); ph_feat ^= 1;
                 tc_fence_after();
-                gemm(tmem + TM_ACC, F / KCH, WN, idesc, F_hi, F_lo, 0, 0);                    // h = feat W0^T
-                mma_commit(&bars[B_ACCFULL]);
+                gemm(tm + TM_ACC, F / KCH, WN, idesc, true, 0, 0);                            // h = feat W0^T
+                if (leader) mma_commit(&bars[B_ACCFULL]);
+                __syncwarp();
                 mbar_wait(&bars[B_HFULL], ph_h); ph_h ^= 1;
                 tc_fence_after();
                 if (plan.nheads > 0) {
-                    gemm(tmem + TM_ACC, WN / KCH, WN, idesc, HS_hi, HS_lo, 0, 0);             // z_0 = relu(h) W1_0^T
-                    mma_commit(&bars[B_ACCFULL]);
+                    gemm(tm + TM_ACC, WN / KCH, WN, idesc, true, 0, 0);                       // z_0 = relu(h) W1_0^T
+                    if (leader) mma_commit(&bars[B_ACCFULL]);
+                    __syncwarp();
                 }
                 for (int i = 0; i < plan.nheads; ++i) {
                     mbar_wait(&bars[B_RZFULL], ph_rz); ph_rz ^= 1;     // z_i drained, relu(z_i) hi/lo in TMEM
                     tc_fence_after();
-                    gemm(tmem + TM_OUT, WN / KCH, plan.nop[i], make_idesc_tf32(128, plan.nop[i], 0, 0), nullptr, nullptr,
-                         tmem + TM_ZHI, tmem + TM_ZLO);                                       // o_i = relu(z_i) W2_i^T
-                    mma_commit(&bars[B_OUTFULL]);
+                    gemm(tm + TM_OUT, WN / KCH, plan.nop[i], make_idesc_tf32(128, plan.nop[i], 0, 0), false,
+                         tm + TM_ZHI, tm + TM_ZLO);                                           // o_i = relu(z_i) W2_i^T
+                    if (leader) mma_commit(&bars[B_OUTFULL]);
+                    __syncwarp();
                     if (i + 1 < plan.nheads) {
-                        gemm(tmem + TM_ACC, WN / KCH, WN, idesc, HS_hi, HS_lo, 0, 0);         // z_{i+1}: overlaps epilogue i
-                        mma_commit(&bars[B_ACCFULL]);
+                        gemm(tm + TM_ACC, WN / KCH, WN, idesc, true, 0, 0);                   // z_{i+1}: overlaps epilogue i
+                        if (leader) mma_commit(&bars[B_ACCFULL]);
+                        __syncwarp();
                     }
                 }
             }
         }
-        __syncwarp();
     } else {
         // ===== sampler + epilogues ===============================================================================
         const int row = tid & 127, hf = tid >> 7;                    // epilogue mapping: TMEM lane = point row, column half

@@ -179,6 +179,15 @@ __device__ __forceinline__ void mma_tf32_ts(uint32_t d_tmem, uint32_t a_tmem, ui
                  "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, {%5, %5, %5, %5}, p;\n\t}"
                  ::"r"(d_tmem), "r"(a_tmem), "l"(bdesc), "r"(idesc), "r"(accumulate), "r"(0u) : "memory");
 }
+// One lane of a converged warp (elect.sync).  The MMA issuer runs its loop with the WHOLE warp and issues under this
+// predicate: the compiler then keeps descriptors / TMEM addresses in uniform registers and emits back-to-back UTCHMMA.
+// A loop entered by `if (lane == 0)` instead costs ~100 cycles per MMA in per-thread address arithmetic and
+// vector->uniform register "waterfalls" (measured, tools/umma_issue_probe.cu: N=128 SS 101 -> 69 cycles, N=16 TS 68 -> 36).
+__device__ __forceinline__ uint32_t elect_one() {
+    uint32_t p;
+    asm volatile("{\n\t.reg .pred P;\n\telect.sync _|P, 0xffffffff;\n\tselp.u32 %0, 1, 0, P;\n\t}" : "=r"(p));
+    return p;
+}
 // all previously issued MMAs of this thread arrive on `bar` when complete (implies fence::before_thread_sync)
 __device__ __forceinline__ void mma_commit(uint64_t* bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_addr(bar)) : "memory");
