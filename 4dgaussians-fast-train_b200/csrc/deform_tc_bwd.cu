@@ -441,127 +441,88 @@ k_deform_bwd_data(Layout lo, Plan plan, Smem sp, Net net, IO io, const float* __
         }
         __syncwarp();
     } else if (warp == 9) {
-        // ===== MMA issuer ===================================================================================
-        if (lane == 0) {
+        // ===== MMA issuer: the whole warp runs the loop, one elected lane issues (see umma.cuh:elect_one) ============
+        {
+            const uint32_t tm = __shfl_sync(0xffffffffu, tmem, 0);
+            const uint32_t leader = elect_one();
             const uint32_t idesc = make_idesc_tf32(128, WN, 0, 0);
             const uint32_t idesc_gf = make_idesc_tf32(128, F, 0, 0);
-            uint32_t g = 0, ph_feat = 0, ph_h = 0, ph_gz = 0, ph_gh = 0, ph_go = 0;
-            for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-                // trunk: ACC = feat . W0^T
-                if constexpr (!SAVED) {
-                mbar_wait(&bars[B_FEATFULL], ph_feat); ph_feat ^= 1;
-                tc_fence_after();
-                for (int c = 0; c < F / KCH; ++c, ++g) {
-                    const uint32_t slot = g % S;
-                    mbar_wait(&bars[B_WFULL + slot], (g / S) & 1);
+            const uint64_t s_hi0 = desc_kmajor(HS_hi, 128, 0), s_lo0 = desc_kmajor(HS_lo, 128, 0);   // feat aliases relu(h)
+            const uint32_t ring_u = smem_addr(ring) >> 4;
+            uint32_t slot = 0, wph = 0, ph_feat = 0, ph_h = 0, ph_gz = 0, ph_gh = 0, ph_go = 0;
+            // D[acc] (+)= A . B^T over `nck` streamed chunks (two 8-wide k-steps each, `ksteps` of them real) of an [N][K]
+            // weight.  A: the shared-memory tile (ss) or TMEM columns ta_hi / ta_lo.  fresh: the first MMA overwrites D.
+            auto gemm = [&](uint32_t acc, int nck, int N, uint32_t id, bool ss, uint32_t ta_hi, uint32_t ta_lo, int ksteps, bool fresh) {
+                const uint64_t bd0 = make_sdesc(0u, (uint32_t)N * 16u, 128u);
+                const uint32_t bstep = (uint32_t)N * 2u;
+#pragma unroll 1
+                for (int c = 0; c < nck; ++c) {
+                    mbar_wait(&bars[B_WFULL + slot], wph);
                     tc_fence_after();
-                    const float* bh = ring + (size_t)slot * SLOT;
-                    const float* bl = bh + 16 * WN;
-#pragma unroll
-                    for (int ks = 0; ks < 2; ++ks) {
-                        const int k = c * KCH + ks * 8;
-                        const int first = (c == 0 && ks == 0) ? 0 : 1;
-                        mma_tf32_ss(tmem + TM_ACC, desc_kmajor(F_lo, 128, k), desc_kmajor(bh, WN, ks * 8), idesc, first);
-                        mma_tf32_ss(tmem + TM_ACC, desc_kmajor(F_hi, 128, k), desc_kmajor(bl, WN, ks * 8), idesc, 1);
-                        mma_tf32_ss(tmem + TM_ACC, desc_kmajor(F_hi, 128, k), desc_kmajor(bh, WN, ks * 8), idesc, 1);
-                    }
-                    mma_commit(&bars[B_WEMPTY + slot]);
-                }
-                mma_commit(&bars[B_ACCFULL]);
-                mbar_wait(&bars[B_HFULL], ph_h); ph_h ^= 1;
-                tc_fence_after();
-                }
-                for (int i = 0; i < plan.nheads; ++i) {
-                    // z_i: ACC = relu(h) . W1^T      (A from shared memory)
-                    if constexpr (!SAVED) {
-                    for (int c = 0; c < WN / KCH; ++c, ++g) {
-                        const uint32_t slot = g % S;
-                        mbar_wait(&bars[B_WFULL + slot], (g / S) & 1);
-                        tc_fence_after();
-                        const float* bh = ring + (size_t)slot * SLOT;
-                        const float* bl = bh + 16 * WN;
+                    if (leader) {
+                        const uint64_t dbh0 = bd0 + (ring_u + slot * (uint32_t)(SLOT / 4));
+                        const uint64_t dbl0 = dbh0 + (uint32_t)N * 4u;
 #pragma unroll
                         for (int ks = 0; ks < 2; ++ks) {
-                            const int k = c * KCH + ks * 8;
-                            const int first = (c == 0 && ks == 0) ? 0 : 1;
-                            mma_tf32_ss(tmem + TM_ACC, desc_kmajor(HS_lo, 128, k), desc_kmajor(bh, WN, ks * 8), idesc, first);
-                            mma_tf32_ss(tmem + TM_ACC, desc_kmajor(HS_hi, 128, k), desc_kmajor(bl, WN, ks * 8), idesc, 1);
-                            mma_tf32_ss(tmem + TM_ACC, desc_kmajor(HS_hi, 128, k), desc_kmajor(bh, WN, ks * 8), idesc, 1);
+                            if (c * 2 + ks < ksteps) {
+                                const uint32_t kk = (uint32_t)(c * 2 + ks);
+                                const int first = (fresh && c == 0 && ks == 0) ? 0 : 1;
+                                const uint64_t dbh = dbh0 + ks * bstep, dbl = dbl0 + ks * bstep;
+                                if (ss) {
+                                    const uint64_t ah = s_hi0 + kk * 256u, al = s_lo0 + kk * 256u;
+                                    mma_tf32_ss(acc, al, dbh, id, first);
+                                    mma_tf32_ss(acc, ah, dbl, id, 1);
+                                    mma_tf32_ss(acc, ah, dbh, id, 1);
+                                } else {
+                                    mma_tf32_ts(acc, ta_lo + kk * 8u, dbh, id, first);
+                                    mma_tf32_ts(acc, ta_hi + kk * 8u, dbl, id, 1);
+                                    mma_tf32_ts(acc, ta_hi + kk * 8u, dbh, id, 1);
+                                }
+                            }
                         }
                         mma_commit(&bars[B_WEMPTY + slot]);
                     }
-                    mma_commit(&bars[B_ACCFULL]);
+                    __syncwarp();
+                    if (++slot == (uint32_t)S) { slot = 0; wph ^= 1; }
+                }
+            };
+            auto commit = [&](int b) { if (leader) mma_commit(&bars[b]); __syncwarp(); };
+            for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+                if constexpr (!SAVED) {
+                    // trunk: ACC = feat . W0^T
+                    mbar_wait(&bars[B_FEATFULL], ph_feat); ph_feat ^= 1;
+                    tc_fence_after();
+                    gemm(tm + TM_ACC, F / KCH, WN, idesc, true, 0, 0, 1 << 20, true);
+                    commit(B_ACCFULL);
+                    mbar_wait(&bars[B_HFULL], ph_h); ph_h ^= 1;
+                    tc_fence_after();
+                }
+                for (int i = 0; i < plan.nheads; ++i) {
+                    if constexpr (!SAVED) {
+                        // z_i: ACC = relu(h) . W1^T      (A from shared memory)
+                        gemm(tm + TM_ACC, WN / KCH, WN, idesc, true, 0, 0, 1 << 20, true);
+                        commit(B_ACCFULL);
                     }
                     // g_relu_z: ACC = g_o . W2       (A = g_o from TMEM, B = W2^T chunks, K padded to 8 / 48)
                     mbar_wait(&bars[B_GOFULL], ph_go); ph_go ^= 1;
                     tc_fence_after();
-                    {
-                        const int ksteps = head_out(plan.heads[i]) > 8 ? 6 : 1;
-                        for (int c = 0; c < plan.k2chunks[i]; ++c, ++g) {
-                            const uint32_t slot = g % S;
-                            mbar_wait(&bars[B_WFULL + slot], (g / S) & 1);
-                            tc_fence_after();
-                            const float* bh = ring + (size_t)slot * SLOT;
-                            const float* bl = bh + 16 * WN;
-#pragma unroll
-                            for (int ks = 0; ks < 2; ++ks) {
-                                if (c * 2 + ks < ksteps) {
-                                    const uint32_t k = (uint32_t)(c * KCH + ks * 8);
-                                    const int first = (c == 0 && ks == 0) ? 0 : 1;
-                                    mma_tf32_ts(tmem + TM_ACC, tmem + TM_GLO + k, desc_kmajor(bh, WN, ks * 8), idesc, first);
-                                    mma_tf32_ts(tmem + TM_ACC, tmem + TM_GHI + k, desc_kmajor(bl, WN, ks * 8), idesc, 1);
-                                    mma_tf32_ts(tmem + TM_ACC, tmem + TM_GHI + k, desc_kmajor(bh, WN, ks * 8), idesc, 1);
-                                }
-                            }
-                            mma_commit(&bars[B_WEMPTY + slot]);
-                        }
-                    }
-                    mma_commit(&bars[B_ACCFULL]);
+                    gemm(tm + TM_ACC, plan.k2chunks[i], WN, idesc, false, tm + TM_GHI, tm + TM_GLO,
+                         head_out(plan.heads[i]) > 8 ? 6 : 1, true);
+                    commit(B_ACCFULL);
                     // g_relu_h += g_z . W1          (A from TMEM, B = W1^T chunks)
                     mbar_wait(&bars[B_GZFULL], ph_gz); ph_gz ^= 1;
                     tc_fence_after();
-                    for (int c = 0; c < WN / KCH; ++c, ++g) {
-                        const uint32_t slot = g % S;
-                        mbar_wait(&bars[B_WFULL + slot], (g / S) & 1);
-                        tc_fence_after();
-                        const float* bh = ring + (size_t)slot * SLOT;
-                        const float* bl = bh + 16 * WN;
-#pragma unroll
-                        for (int ks = 0; ks < 2; ++ks) {
-                            const uint32_t k = (uint32_t)(c * KCH + ks * 8);
-                            const int first = (i == 0 && c == 0 && ks == 0) ? 0 : 1;
-                            mma_tf32_ts(tmem + TM_GRH, tmem + TM_GLO + k, desc_kmajor(bh, WN, ks * 8), idesc, first);
-                            mma_tf32_ts(tmem + TM_GRH, tmem + TM_GHI + k, desc_kmajor(bl, WN, ks * 8), idesc, 1);
-                            mma_tf32_ts(tmem + TM_GRH, tmem + TM_GHI + k, desc_kmajor(bh, WN, ks * 8), idesc, 1);
-                        }
-                        mma_commit(&bars[B_WEMPTY + slot]);
-                    }
-                    if constexpr (SAVED) mma_commit(&bars[B_GRHFULL]);    // per head: g_z in TMEM may be overwritten by the next g_o
+                    gemm(tm + TM_GRH, WN / KCH, WN, idesc, false, tm + TM_GHI, tm + TM_GLO, 1 << 20, i == 0);
+                    if constexpr (SAVED) commit(B_GRHFULL);    // per head: g_z in TMEM may be overwritten by the next g_o
                 }
-                if constexpr (!SAVED) mma_commit(&bars[B_GRHFULL]);
+                if constexpr (!SAVED) commit(B_GRHFULL);
                 // g_feat: ACC[0, F) = g_h . W0       (A from TMEM, B = W0^T chunks, N = F)
                 mbar_wait(&bars[B_GHFULL], ph_gh); ph_gh ^= 1;
                 tc_fence_after();
-                for (int c = 0; c < WN / KCH; ++c, ++g) {
-                    const uint32_t slot = g % S;
-                    mbar_wait(&bars[B_WFULL + slot], (g / S) & 1);
-                    tc_fence_after();
-                    const float* bh = ring + (size_t)slot * SLOT;
-                    const float* bl = bh + 16 * F;
-#pragma unroll
-                    for (int ks = 0; ks < 2; ++ks) {
-                        const uint32_t k = (uint32_t)(c * KCH + ks * 8);
-                        const int first = (c == 0 && ks == 0) ? 0 : 1;
-                        mma_tf32_ts(tmem + TM_ACC, tmem + TM_GLO + k, desc_kmajor(bh, F, ks * 8), idesc_gf, first);
-                        mma_tf32_ts(tmem + TM_ACC, tmem + TM_GHI + k, desc_kmajor(bl, F, ks * 8), idesc_gf, 1);
-                        mma_tf32_ts(tmem + TM_ACC, tmem + TM_GHI + k, desc_kmajor(bh, F, ks * 8), idesc_gf, 1);
-                    }
-                    mma_commit(&bars[B_WEMPTY + slot]);
-                }
-                mma_commit(&bars[B_GFFULL]);
+                gemm(tm + TM_ACC, WN / KCH, F, idesc_gf, false, tm + TM_GHI, tm + TM_GLO, 1 << 20, true);
+                commit(B_GFFULL);
             }
         }
-        __syncwarp();
     } else {
         // ===== sampler + epilogues: thread = point row `row`, column half `hf` ==========================
         const int row = tid & 127, hf = tid >> 7;
@@ -893,6 +854,8 @@ k_deform_bwd_weights(WArgs args)
         __syncwarp();
     } else if (warp == NSW) {
         // ===== MMA issuer ==================================================================================
+        // Single-thread loop on purpose: this kernel is shared-memory bound, and the elected-lane issuer of the data
+        // kernels (12 MMAs back to back) bunches the operand fetches against the staging warps: 690 -> 761 us, measured.
         if (lane == 0) {
             const uint32_t idesc = make_idesc_tf32(128, N16, 1, 1);
             uint32_t g = 0;
