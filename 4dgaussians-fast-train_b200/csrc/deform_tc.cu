@@ -40,7 +40,9 @@ constexpr int MAXCH = 96;          // chunks per tile: F/16 + heads * (Wn/16 + W
 
 // Pre-formatted weights ("wprep" workspace): a chunk holds KCH=16 reduction columns of an [N rows][K] weight as a hi
 // tile then a lo tile, each the canonical K-major tile [4 column groups][N][4] (umma.cuh) => 32*N floats, one bulk copy.
-// Order = MMA order: W0 (N = Wn), then per active head W1_j (N = Wn) and W2_j (N = 16 or 48, rows >= out are zero).
+// Memory order: W0 (N = Wn), then per active head W1_j (N = Wn) and W2_j (N = 16 or 48, rows >= out are zero).
+// Stream order (coff[]) = MMA order: W0, W1_0, then per head i: W1_{i+1} (its GEMM runs ahead, into the other
+// accumulator), W2_i.
 struct TcPlan {
     int Wn, F, nheads;
     int heads[FDGS_NUM_HEADS];
@@ -57,14 +59,26 @@ static inline TcPlan make_plan(const Layout& lo) {
     TcPlan p;
     p.Wn = lo.Wn; p.F = lo.F; p.nheads = 0;
     for (int h = 0; h < FDGS_NUM_HEADS; ++h) if ((lo.head_mask >> h) & 1) p.heads[p.nheads++] = h;
-    int c = 0; long long o = 0;
-    auto add = [&](int n, int N) { for (int i = 0; i < n; ++i) { p.coff[c] = (int)o; p.cfl[c] = 32 * N; o += 32 * N; ++c; } };
-    add(lo.F / KCH, lo.Wn);
+    long long o = (long long)(lo.F / KCH) * 32 * lo.Wn;
+    long long off1[FDGS_NUM_HEADS], off2[FDGS_NUM_HEADS];
     for (int j = 0; j < FDGS_NUM_HEADS; ++j) {
         p.nop[j] = j < p.nheads ? out_pad(p.heads[j]) : 16;
-        if (j < p.nheads) { add(lo.Wn / KCH, lo.Wn); add(lo.Wn / KCH, p.nop[j]); }
+        off1[j] = off2[j] = 0;
+        if (j < p.nheads) {
+            off1[j] = o; o += (long long)(lo.Wn / KCH) * 32 * lo.Wn;
+            off2[j] = o; o += (long long)(lo.Wn / KCH) * 32 * p.nop[j];
+        }
     }
-    p.nchunks = c; p.floats = o;
+    p.floats = o;
+    int c = 0;
+    auto add = [&](long long at, int n, int N) { for (int i = 0; i < n; ++i) { p.coff[c] = (int)(at + (long long)i * 32 * N); p.cfl[c] = 32 * N; ++c; } };
+    add(0, lo.F / KCH, lo.Wn);
+    if (p.nheads > 0) add(off1[0], lo.Wn / KCH, lo.Wn);
+    for (int j = 0; j < p.nheads; ++j) {
+        if (j + 1 < p.nheads) add(off1[j + 1], lo.Wn / KCH, lo.Wn);
+        add(off2[j], lo.Wn / KCH, p.nop[j]);
+    }
+    p.nchunks = c;
     return p;
 }
 
@@ -141,9 +155,12 @@ static inline SmemPlan make_smem_plan(const Layout& lo) {
 
 __device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
 
-// TMEM column map (512 columns allocated): accumulator (trunk h / head z), relu(z) hi, lo, output accumulator
-constexpr uint32_t TM_ACC = 0, TM_ZHI = 128, TM_ZLO = 256, TM_OUT = 384;
-constexpr int B_WFULL = 0, B_WEMPTY = 8, B_FEATFULL = 16, B_ACCFULL = 17, B_HFULL = 18, B_RZFULL = 19, B_OUTFULL = 20, B_COUNT = 21;
+// TMEM column map (512 columns allocated): two accumulators, relu(z) hi, lo.  Head i uses accumulator i & 1: z_i, then
+// (once relu(z_i) has been read out of it) its first 16 / 48 columns take the output layer o_i.  z_{i+1} is computed into
+// the other accumulator WHILE the epilogue warps turn z_i into relu(z_i) hi / lo.
+constexpr uint32_t TM_A0 = 0, TM_A1 = 128, TM_ZHI = 256, TM_ZLO = 384;
+constexpr int B_WFULL = 0, B_WEMPTY = 8, B_FEATFULL = 16, B_ACCFULL = 17 /* +1 */, B_HFULL = 19, B_RZFULL = 20, B_OUTFULL = 21,
+              B_OUTFREE = 22, B_COUNT = 23;
 
 __device__ __forceinline__ int b2_row0(int h) { return h == 0 ? 0 : h == 1 ? 3 : h == 2 ? 6 : h == 3 ? 10 : 11; }
 
@@ -153,7 +170,9 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
                 const float* __restrict__ trow, int ntiles, int passes)
 {
     extern __shared__ uint8_t smem_raw[];
-    float* sm = reinterpret_cast<float*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    // 1024-byte alignment by OFFSET from the shared array (not by integer casts of the pointer): the compiler keeps the
+    // shared address space and emits LDS / STS with 32-bit addresses instead of generic LD / ST
+    float* sm = reinterpret_cast<float*>(smem_raw + ((1024u - (smem_addr(smem_raw) & 1023u)) & 1023u));
     float* HS_hi = sm + sp.off_hs_hi;
     float* HS_lo = sm + sp.off_hs_lo;
     float* F_hi = HS_hi;
@@ -255,31 +274,33 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
                     if (++slot == (uint32_t)S) { slot = 0; wph ^= 1; }
                 }
             };
+            uint32_t ph_free = 0;
+            auto commit = [&](int b) { if (leader) mma_commit(&bars[b]); __syncwarp(); };
             for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
                 mbar_wait(&bars[B_FEATFULL], ph_feat); ph_feat ^= 1;
                 tc_fence_after();
-                gemm(tm + TM_ACC, F / KCH, WN, idesc, true, 0, 0);                            // h = feat W0^T
-                if (leader) mma_commit(&bars[B_ACCFULL]);
-                __syncwarp();
+                gemm(tm + TM_A0, F / KCH, WN, idesc, true, 0, 0);                             // h = feat W0^T
+                commit(B_ACCFULL);
                 mbar_wait(&bars[B_HFULL], ph_h); ph_h ^= 1;
                 tc_fence_after();
                 if (plan.nheads > 0) {
-                    gemm(tm + TM_ACC, WN / KCH, WN, idesc, true, 0, 0);                       // z_0 = relu(h) W1_0^T
-                    if (leader) mma_commit(&bars[B_ACCFULL]);
-                    __syncwarp();
+                    gemm(tm + TM_A0, WN / KCH, WN, idesc, true, 0, 0);                        // z_0 = relu(h) W1_0^T
+                    commit(B_ACCFULL);
                 }
                 for (int i = 0; i < plan.nheads; ++i) {
+                    if (i + 1 < plan.nheads) {
+                        if (i >= 1) {                                  // o_{i-1} has been read out of this accumulator
+                            mbar_wait(&bars[B_OUTFREE], ph_free); ph_free ^= 1;
+                            tc_fence_after();
+                        }
+                        gemm(tm + (((i + 1) & 1) ? TM_A1 : TM_A0), WN / KCH, WN, idesc, true, 0, 0);   // z_{i+1}: runs ahead
+                        commit(B_ACCFULL + ((i + 1) & 1));
+                    }
                     mbar_wait(&bars[B_RZFULL], ph_rz); ph_rz ^= 1;     // z_i drained, relu(z_i) hi/lo in TMEM
                     tc_fence_after();
-                    gemm(tm + TM_OUT, WN / KCH, plan.nop[i], make_idesc_tf32(128, plan.nop[i], 0, 0), false,
+                    gemm(tm + ((i & 1) ? TM_A1 : TM_A0), WN / KCH, plan.nop[i], make_idesc_tf32(128, plan.nop[i], 0, 0), false,
                          tm + TM_ZHI, tm + TM_ZLO);                                           // o_i = relu(z_i) W2_i^T
-                    if (leader) mma_commit(&bars[B_OUTFULL]);
-                    __syncwarp();
-                    if (i + 1 < plan.nheads) {
-                        gemm(tm + TM_ACC, WN / KCH, WN, idesc, true, 0, 0);                   // z_{i+1}: overlaps epilogue i
-                        if (leader) mma_commit(&bars[B_ACCFULL]);
-                        __syncwarp();
-                    }
+                    commit(B_OUTFULL);
                 }
             }
         }
@@ -288,7 +309,7 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
         const int row = tid & 127, hf = tid >> 7;                    // epilogue mapping: TMEM lane = point row, column half
         const uint32_t lane_base = tmem + ((uint32_t)((warp & 3) * 32) << 16);
         const int col0 = hf * NH;
-        uint32_t ph_acc = 0, ph_out = 0;
+        uint32_t ph_a0 = 0, ph_a1 = 0, ph_out = 0;
         const int C = lo.C;
         // sampler mapping: LP adjacent lanes share one point and take consecutive channel quads, so a warp-wide gather
         // touches 32/LP points x 64-byte taps instead of 32 unrelated lines (the L1 tag stage serves one line per cycle)
@@ -342,13 +363,13 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
             PT(0)
 
             // ---- trunk epilogue: relu(h + b0) -> shared memory hi / lo (A operand of the heads), kept copy ----------
-            mbar_wait(&bars[B_ACCFULL], ph_acc); ph_acc ^= 1;
+            mbar_wait(&bars[B_ACCFULL], ph_a0); ph_a0 ^= 1;
             tc_fence_after();
             PT(1)
 #pragma unroll 1
             for (int c0 = 0; c0 < NH; c0 += 32) {
                 uint32_t v[32];
-                tmem_ld32(lane_base + TM_ACC + col0 + c0, v);
+                tmem_ld32(lane_base + TM_A0 + col0 + c0, v);
                 tmem_wait_ld();
                 uint32_t m = 0;
 #pragma unroll
@@ -395,7 +416,9 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
                     }
                 }
                 // z = relu(acc + b1): kept copy, hi / lo -> TMEM (A operand of the output layer)
-                mbar_wait(&bars[B_ACCFULL], ph_acc); ph_acc ^= 1;
+                const uint32_t acc = lane_base + ((i & 1) ? TM_A1 : TM_A0);
+                if (i & 1) { mbar_wait(&bars[B_ACCFULL + 1], ph_a1); ph_a1 ^= 1; }
+                else { mbar_wait(&bars[B_ACCFULL], ph_a0); ph_a0 ^= 1; }
                 tc_fence_after();
                 PT(3)
                 float* rz = io.S_RZ[h] ? io.S_RZ[h] + rowoff : nullptr;
@@ -403,7 +426,7 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
 #pragma unroll 1
                 for (int c0 = 0; c0 < NH; c0 += 16) {
                     uint32_t v[16], hi[16], lw[16];
-                    tmem_ld16(lane_base + TM_ACC + col0 + c0, v);
+                    tmem_ld16(acc + col0 + c0, v);
                     tmem_wait_ld();
                     uint32_t mbits = 0u;
 #pragma unroll
@@ -445,7 +468,7 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
                     const int npt = plan.nop[i] >> 1;                 // output columns per thread: 8 or 24
                     for (int c0 = 0; c0 < npt; c0 += 8) {
                         uint32_t v[8];
-                        tmem_ld8(lane_base + TM_OUT + hf * npt + c0, v);
+                        tmem_ld8(acc + hf * npt + c0, v);
                         tmem_wait_ld();
 #pragma unroll
                         for (int j = 0; j < 8; ++j) {
@@ -456,6 +479,7 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
                 }
                 tc_fence_before();
                 epi_bar();
+                if (tid == 0 && i + 2 < plan.nheads) mbar_arrive(&bars[B_OUTFREE]);      // accumulator free for z_{i+2}
                 {
                     const bool nobase = (h == 2 && lo.apply_rotation);
                     float* dst = outp + (size_t)p0 * NO;

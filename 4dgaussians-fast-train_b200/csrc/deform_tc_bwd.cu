@@ -384,7 +384,9 @@ k_deform_bwd_data(Layout lo, Plan plan, Smem sp, Net net, IO io, const float* __
                   const float* __restrict__ trow, float* __restrict__ gpacked, float* __restrict__ gtrow, int ntiles)
 {
     extern __shared__ uint8_t smem_raw[];
-    float* sm = reinterpret_cast<float*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    // 1024-byte alignment by OFFSET from the shared array (not by integer casts of the pointer): the compiler keeps the
+    // shared address space and emits LDS / STS with 32-bit addresses instead of generic LD / ST
+    float* sm = reinterpret_cast<float*>(smem_raw + ((1024u - (smem_addr(smem_raw) & 1023u)) & 1023u));
     float* HS_hi = sm + sp.off_hs_hi;
     float* HS_lo = sm + sp.off_hs_lo;
     float* F_hi = HS_hi;                       // the feat tile lives in the head of the relu(h) buffers
@@ -790,7 +792,9 @@ __global__ void __launch_bounds__(W_THREADS, 1)
 k_deform_bwd_weights(WArgs args)
 {
     extern __shared__ uint8_t smem_raw[];
-    float* sm = reinterpret_cast<float*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    // 1024-byte alignment by OFFSET from the shared array (not by integer casts of the pointer): the compiler keeps the
+    // shared address space and emits LDS / STS with 32-bit addresses instead of generic LD / ST
+    float* sm = reinterpret_cast<float*>(smem_raw + ((1024u - (smem_addr(smem_raw) & 1023u)) & 1023u));
     __shared__ __align__(8) uint64_t bars[WB_COUNT + 1];
     __shared__ uint32_t tmem_slot;
     __shared__ float csumA[128], csumB[128];
