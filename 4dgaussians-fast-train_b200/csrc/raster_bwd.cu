@@ -1,6 +1,6 @@
 // Backward rasterizer for sm_100a.
 //   k_blend_bwd      : reverse-order blend backward; per-pixel partials are reduced across the
-//                      warp with a 16-shuffle transposed butterfly and accumulated per
+//                      warp with a 12-shuffle transposed butterfly and accumulated per
 //                      (tile, Gaussian) in shared memory; one global reduction per instance.
 //   k_preprocess_bwd : fused cov2D / mean2D->mean3D / SH / cov3D->(scale, rot) chain.
 // Replaces CudaRasterizer::Rasterizer::backward
@@ -66,24 +66,26 @@ __device__ __forceinline__ bool rect_culled(float mx, float my, float A, float B
     return (-0.5f * qmin) < (cull - margin);
 }
 
-// Reduce 16 per-lane slots across the warp with 16 shuffles (8+4+2+1+1).  On return lane L
-// holds the warp total of slot ((L>>4)&1)*8 + ((L>>3)&1)*4 + ((L>>2)&1)*2 + ((L>>1)&1) in v[0].
-__device__ __forceinline__ void warp_reduce16(float (&v)[16], int lane) {
+// Reduce 10 per-lane slots (9 accumulators + a zero pad) across the warp with 12 shuffles (5+3+2+1+1): a transposed
+// butterfly whose halves are 5 | 3 (of 5, padded to 6) | 2 (of 3, padded to 4) | 1.  On return lane L holds in v[0] the warp
+// total of slot ((L>>4)&1)*5 + ((L>>3)&1)*3 + ((L>>2)&1)*2 + ((L>>1)&1); lanes whose path ran through a pad hold 0.
+__device__ __forceinline__ void warp_reduce10(float (&v)[10], int lane) {
     {
         const bool up = lane & 16;
 #pragma unroll
-        for (int k = 0; k < 8; ++k) {
-            const float send = up ? v[k] : v[k + 8];
-            const float keep = up ? v[k + 8] : v[k];
+        for (int k = 0; k < 5; ++k) {
+            const float send = up ? v[k] : v[k + 5];
+            const float keep = up ? v[k + 5] : v[k];
             v[k] = keep + __shfl_xor_sync(FULL, send, 16);
         }
     }
     {
         const bool up = lane & 8;
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            const float send = up ? v[k] : v[k + 4];
-            const float keep = up ? v[k + 4] : v[k];
+        for (int k = 0; k < 3; ++k) {
+            const float hv = (k + 3 < 5) ? v[k + 3] : 0.f;
+            const float send = up ? v[k] : hv;
+            const float keep = up ? hv : v[k];
             v[k] = keep + __shfl_xor_sync(FULL, send, 8);
         }
     }
@@ -91,8 +93,9 @@ __device__ __forceinline__ void warp_reduce16(float (&v)[16], int lane) {
         const bool up = lane & 4;
 #pragma unroll
         for (int k = 0; k < 2; ++k) {
-            const float send = up ? v[k] : v[k + 2];
-            const float keep = up ? v[k + 2] : v[k];
+            const float hv = (k + 2 < 3) ? v[k + 2] : 0.f;
+            const float send = up ? v[k] : hv;
+            const float keep = up ? hv : v[k];
             v[k] = keep + __shfl_xor_sync(FULL, send, 4);
         }
     }
@@ -190,9 +193,9 @@ k_blend_bwd(const uint2* __restrict__ ranges, const FdgsRecord* __restrict__ rec
                     m &= m - 1;
                     const int jj = c1 - 1 - l;
                     const uint32_t pos = (uint32_t)(lo + jj);
-                    float v[16];
+                    float v[10];
 #pragma unroll
-                    for (int k = 0; k < 16; ++k) v[k] = 0.f;
+                    for (int k = 0; k < 10; ++k) v[k] = 0.f;
                     if (pos < last_contributor) {
                         const float4 q0 = reinterpret_cast<const float4*>(&rec[jj])[0];
                         const float4 q1 = reinterpret_cast<const float4*>(&rec[jj])[1];
@@ -231,8 +234,8 @@ k_blend_bwd(const uint2* __restrict__ ranges, const FdgsRecord* __restrict__ rec
                             }
                         }
                     }
-                    warp_reduce16(v, lane);
-                    const int slot = ((lane >> 4) & 1) * 8 + ((lane >> 3) & 1) * 4 + ((lane >> 2) & 1) * 2 + ((lane >> 1) & 1);
+                    warp_reduce10(v, lane);
+                    const int slot = ((lane >> 4) & 1) * 5 + ((lane >> 3) & 1) * 3 + ((lane >> 2) & 1) * 2 + ((lane >> 1) & 1);
                     if (!(lane & 1) && slot < NACC && v[0] != 0.f) atomicAdd(&acc[jj][slot], v[0]);
                 }
             }
