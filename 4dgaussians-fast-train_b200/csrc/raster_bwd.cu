@@ -206,7 +206,8 @@ k_blend_bwd(const uint2* __restrict__ ranges, const FdgsRecord* __restrict__ rec
                             const float alpha = fminf(0.99f, q1.y * G);
                             if (!(alpha < 1.0f / 255.0f)) {
                                 const float4 q2 = reinterpret_cast<const float4*>(&rec[jj])[2];
-                                T = T / (1.f - alpha);
+                                const float inv1ma = 1.f / (1.f - alpha);           // one division for both uses
+                                T = T * inv1ma;
                                 const float dchannel_dcolor = alpha * T;
                                 float dL_dalpha = 0.0f;
                                 ar0 = last_alpha * lc0 + (1.f - last_alpha) * ar0; lc0 = q2.x;
@@ -220,7 +221,7 @@ k_blend_bwd(const uint2* __restrict__ ranges, const FdgsRecord* __restrict__ rec
                                 v[2] = dchannel_dcolor * dLp2;
                                 dL_dalpha *= T;
                                 last_alpha = alpha;
-                                dL_dalpha += (-T_final / (1.f - alpha)) * bg_dot;
+                                dL_dalpha += (-T_final * inv1ma) * bg_dot;
                                 const float dL_dG = q1.y * dL_dalpha;
                                 const float gdx = G * dx, gdy = G * dy;
                                 const float dG_ddelx = -gdx * q0.z - gdy * q0.w;
