@@ -192,9 +192,9 @@ def algorithmic_per_launch(kernel, s):
 # dram__bytes_read.sum + dram__bytes_write.sum per launch from the `ncu --set full` capture of this workload
 # (profiles/r01_ncu_full_summary.csv; P = 300k DyNeRF view).  Reported only for that workload.
 NCU_TRAFFIC_BYTES = {
-    "k_deform_fwd_tc": 0.075828e9 + 1.007398e9, "k_deform_bwd_data_saved": 0.114425e9 + 0.885651e9,
-    "k_deform_bwd_weights": 1.975819e9 + 0.004271e9, "k_blend_bwd": 0.118526e9 + 0.003856e9, "k_blend_fwd": 0.081387e9 + 0.010402e9,
-    "k_tile_sort": 0.024415e9 + 0.027028e9, "k_preprocess": 0.066749e9 + 0.004076e9, "k_preprocess_bwd": 0.092867e9 + 0.038299e9,
+    "k_deform_fwd_tc": 0.075682e9 + 1.007728e9, "k_deform_bwd_data_saved": 0.112828e9 + 0.883818e9,
+    "k_deform_bwd_weights": 1.969523e9 + 0.004559e9, "k_blend_bwd": 0.120245e9 + 0.004495e9, "k_blend_fwd": 0.089820e9 + 0.011918e9,
+    "k_tile_sort": 0.025839e9 + 0.035511e9, "k_preprocess": 0.065620e9 + 0.002980e9, "k_preprocess_bwd": 0.093627e9 + 0.039184e9,
 }
 
 
