@@ -40,7 +40,7 @@ struct Plan {
     long long wprep_floats;
     // scratch (floats), Pp = ntiles * 128 rows each
     long long Pp;
-    long long off_wprep, off_F, off_H, off_GH, off_RZ[FDGS_NUM_HEADS], off_GZ[FDGS_NUM_HEADS], total_floats;
+    long long off_wprep, off_F, off_H, off_GH, off_GF, off_RZ[FDGS_NUM_HEADS], off_GZ[FDGS_NUM_HEADS], total_floats;
 };
 
 static inline bool tc_supported(const Layout& lo) {
@@ -77,6 +77,7 @@ static inline Plan make_plan(const Layout& lo, int P, const bool has_grad[FDGS_N
     p.off_F = o;  o += al(p.Pp * lo.F);
     p.off_H = o;  o += al(p.Pp * lo.Wn);
     p.off_GH = o; o += al(p.Pp * lo.Wn);
+    p.off_GF = o; o += al(p.Pp * lo.F);          // g_feat rows [Pp][F] for the sampler-backward kernel (SAVED path)
     for (int j = 0; j < FDGS_NUM_HEADS; ++j) {
         p.off_RZ[j] = o; if (j < p.nheads) o += al(p.Pp * lo.Wn);
         p.off_GZ[j] = o; if (j < p.nheads) o += al(p.Pp * lo.Wn);
@@ -122,6 +123,7 @@ struct IO {
     const float* g[FDGS_NUM_HEADS];        // upstream grads [P][out]
     float* d_xyz;
     float *S_F, *S_H, *S_GH;
+    float* G_F;                            // dL/dfeat rows [Pp][F] (SAVED path: the sampler backward is its own kernel)
     float* S_RZ[FDGS_NUM_HEADS];           // indexed by plan slot j
     float* S_GZ[FDGS_NUM_HEADS];
     // activations kept by the forward (SAVED kernels read these instead of recomputing), same blocked layout
@@ -375,6 +377,47 @@ __device__ __forceinline__ void head_pass2(uint32_t lane_base, int col0, float* 
         tmem_st16(lane_base + TM_GLO + col0 + c0, lw);
     }
     tmem_wait_st();
+}
+
+// Sampler backward as its own kernel (SAVED path): LP adjacent lanes per point take consecutive channel quads of its
+// dL/dfeat row (one coalesced 128-byte read per point), recompute the six bilinear samples, scatter dL/dplane with float4
+// reductions and reduce dL/dxyz over the point's lanes.
+__global__ void __launch_bounds__(256)
+k_deform_sample_bwd(Layout lo, int P, const float* __restrict__ xyz, const float* __restrict__ GFrows, const float* __restrict__ packed,
+                    const float* __restrict__ trow, float* __restrict__ gpacked, float* __restrict__ gtrow, float* __restrict__ d_xyz)
+{
+    const int F = lo.F, C = lo.C;
+    const int items = F >> 2;
+    const int LP = (items & 7) == 0 ? 8 : 4, IPT = items / LP, PPW = 32 / LP;
+    const int lane = threadIdx.x & 31, sg = lane / LP, sq = lane % LP;
+    const long long gw = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const long long sp_ = gw * PPW + sg;
+    const bool sval = sp_ < P;
+    float q[4] = {0.f, 0.f, 0.f, 0.f};
+    if (sval) point_coords(lo, xyz, (int)sp_, 0.f, q);
+    float dq[3] = {0.f, 0.f, 0.f};
+    for (int it = 0; it < IPT; ++it) {
+        const int item = sq + it * LP;
+        const int l = (item * 4) / C, c0 = (item * 4) % C;
+        if (sval) {
+            const float4 d4 = __ldcs(reinterpret_cast<const float4*>(GFrows + (size_t)sp_ * F + item * 4));
+            const float df[4] = {d4.x, d4.y, d4.z, d4.w};
+            sample_bwd4(lo, l, q, packed, trow, gpacked, gtrow, c0, df, dq);
+        }
+    }
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        dq[a] += __shfl_xor_sync(0xffffffffu, dq[a], 1);
+        dq[a] += __shfl_xor_sync(0xffffffffu, dq[a], 2);
+        if (LP == 8) dq[a] += __shfl_xor_sync(0xffffffffu, dq[a], 4);
+    }
+    if (sq == 0 && sval) {
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {
+            const float mx = lo.aabb[a], mn = lo.aabb[3 + a];
+            d_xyz[3 * (size_t)sp_ + a] = dq[a] * (2.0f / (mn - mx));
+        }
+    }
 }
 
 // =====================================================================================================================
@@ -718,9 +761,25 @@ k_deform_bwd_data(Layout lo, Plan plan, Smem sp, Net net, IO io, const float* __
             mbar_wait(&bars[B_GFFULL], ph_gf); ph_gf ^= 1;
             tc_fence_after();
             PT(7)
+            if constexpr (SAVED) {
+                // g_feat rows go to memory (128 B per point): the sampler backward - float4 reductions into the plane
+                // gradients - runs as its own full-occupancy kernel (k_deform_sample_bwd).  Inside this kernel its
+                // reductions ran at half the rate a dedicated kernel reaches (8 warps per SM, the LSU shared with the
+                // tensor core's operand reads; tools/red_probe.cu) and were 44 % of the kernel.
+                for (int l = 0; l < lo.L; ++l)
+                    for (int cc = 0; cc < CH; cc += 4) {
+                        const int c0 = l * C + hf * CH + cc;
+                        uint32_t v[4];
+                        tmem_ld4(lane_base + TM_ACC + (uint32_t)c0, v);            // warp-uniform address: all lanes execute
+                        tmem_wait_ld();
+                        if (valid)
+                            __stcs(reinterpret_cast<float4*>(io.G_F + (size_t)p * F + c0),
+                                   make_float4(__uint_as_float(v[0]), __uint_as_float(v[1]), __uint_as_float(v[2]), __uint_as_float(v[3])));
+                    }
+                tc_fence_before();
+                epi_bar();
+            } else {
             // accumulator rows (TMEM lane = point) -> shared memory, so that the sampler mapping can read any point.
-            // SAVED: the scatter passes of this tile run inside the NEXT tile's head loop (see samp_pass), so first
-            // finish whatever is still pending of the previous tile: the staging buffer is about to be overwritten.
             while (pend_tile >= 0 && pend_pass < SPASS) samp_pass(pend_tile, pend_pass++);
             epi_bar();
             for (int l = 0; l < lo.L; ++l)
@@ -735,9 +794,8 @@ k_deform_bwd_data(Layout lo, Plan plan, Smem sp, Net net, IO io, const float* __
             tc_fence_before();
             epi_bar();
             pend_tile = tile; pend_pass = 0;
-            if constexpr (!SAVED) {                                  // the staging buffer aliases relu(h): scatter now
-                while (pend_pass < SPASS) samp_pass(pend_tile, pend_pass++);
-                epi_bar();
+            while (pend_pass < SPASS) samp_pass(pend_tile, pend_pass++);          // the staging buffer aliases relu(h): scatter now
+            epi_bar();
             }
             PT(8)
             PT(9)
@@ -1089,7 +1147,7 @@ int backward(const Layout& lo, const FdgsDeformBackward* a, const float* packed,
     IO io;
     io.P = a->P; io.xyz = a->xyz; io.d_xyz = a->d_xyz_grid;
     for (int h = 0; h < FDGS_NUM_HEADS; ++h) io.g[h] = gsrc[h];
-    io.S_F = S + plan.off_F; io.S_H = S + plan.off_H; io.S_GH = S + plan.off_GH;
+    io.S_F = S + plan.off_F; io.S_H = S + plan.off_H; io.S_GH = S + plan.off_GH; io.G_F = S + plan.off_GF;
     for (int j = 0; j < FDGS_NUM_HEADS; ++j) { io.S_RZ[j] = S + plan.off_RZ[j]; io.S_GZ[j] = S + plan.off_GZ[j]; }
     io.V_H = nullptr; io.V_M = nullptr; io.Pp = plan.Pp;
     for (int j = 0; j < FDGS_NUM_HEADS; ++j) io.V_RZ[j] = nullptr;
@@ -1110,6 +1168,13 @@ int backward(const Layout& lo, const FdgsDeformBackward* a, const float* packed,
     if (Wn == 128) { if (saved) FDGS_LAUNCH_BWD_DATA(128, true); else FDGS_LAUNCH_BWD_DATA(128, false); }
     else           { if (saved) FDGS_LAUNCH_BWD_DATA(64, true);  else FDGS_LAUNCH_BWD_DATA(64, false); }
 #undef FDGS_LAUNCH_BWD_DATA
+    FDGS_LAUNCH_CHECK(a->debug, stream);
+    if (saved) {
+        const int lp = ((F >> 2) & 7) == 0 ? 8 : 4;
+        const long long warps = ((long long)a->P + (32 / lp) - 1) / (32 / lp);
+        FDGS_PROF("k_deform_sample_bwd", stream);
+        k_deform_sample_bwd<<<(unsigned)((warps + 7) / 8), 256, 0, stream>>>(lo, a->P, a->xyz, io.G_F, packed, trow, gpacked, gtrow, a->d_xyz_grid);
+    }
     FDGS_LAUNCH_CHECK(a->debug, stream);
 
     // 3. weight gradients: jobs x point slices, one CTA each
