@@ -379,10 +379,119 @@ __device__ __forceinline__ void head_pass2(uint32_t lane_base, int col0, float* 
     tmem_wait_st();
 }
 
+// Register-lean sampler backward for 4 channels of one level of one point (the standalone kernel; sample_bwd4 above needs
+// ~170 registers, one 256-thread CTA per SM).  Two sweeps over the six planes: the first keeps only the suffix products
+// of the samples, the second re-reads the taps (L1 / L2 hits), forms dL/dsample = df * prefix * suffix, scatters and
+// accumulates dL/dq.  Same arithmetic as sample_bwd4 up to the association of the 5-factor products.
+struct PlaneTaps {
+    float s[4], gx[4], gy[4];
+    float wx0, wx1, wy0, wy1, gmx, gmy;
+    int x0, y0;
+    bool xin, yin;
+};
+template <bool GRAD>
+__device__ __forceinline__ void plane_taps(const Layout& lo, int l, int k, const float q[4], const float* __restrict__ packed,
+                                           const float* __restrict__ trow, int c0, PlaneTaps& t) {
+    const int C = lo.C;
+    const int W = lo.pw[l][k];
+    const float ix = unnorm_clip(q[pa_of(k)], W, &t.gmx);
+    const float x0f = floorf(ix);
+    t.x0 = (int)x0f;
+    t.wx0 = (x0f + 1.f) - ix; t.wx1 = ix - x0f;
+    t.xin = t.x0 + 1 < W;
+    const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (k == 2 || k == 4 || k == 5) {
+        const float* T = trow + lo.toff[l][k == 2 ? 0 : (k == 4 ? 1 : 2)] + c0;
+        const float4 v0 = *reinterpret_cast<const float4*>(T + (size_t)t.x0 * C);
+        const float4 v1 = t.xin ? *reinterpret_cast<const float4*>(T + (size_t)(t.x0 + 1) * C) : z4;
+        const float a0[4] = {v0.x, v0.y, v0.z, v0.w}, a1[4] = {v1.x, v1.y, v1.z, v1.w};
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            t.s[c] = a0[c] * t.wx0 + a1[c] * t.wx1;
+            if (GRAD) { t.gx[c] = a1[c] - a0[c]; t.gy[c] = 0.f; }
+        }
+        t.gmy = 0.f; t.y0 = 0; t.wy0 = 0.f; t.wy1 = 0.f; t.yin = false;
+    } else {
+        const int H = lo.ph[l][k];
+        const float iy = unnorm_clip(q[pb_of(k)], H, &t.gmy);
+        const float y0f = floorf(iy);
+        t.y0 = (int)y0f;
+        t.wy0 = (y0f + 1.f) - iy; t.wy1 = iy - y0f;
+        t.yin = t.y0 + 1 < H;
+        const float* Pp = packed + lo.poff[l][k] + c0;
+        const size_t o00 = ((size_t)t.y0 * W + t.x0) * C;
+        const float4 v00 = *reinterpret_cast<const float4*>(Pp + o00);
+        const float4 v01 = t.xin ? *reinterpret_cast<const float4*>(Pp + o00 + C) : z4;
+        const float4 v10 = t.yin ? *reinterpret_cast<const float4*>(Pp + o00 + (size_t)W * C) : z4;
+        const float4 v11 = (t.xin && t.yin) ? *reinterpret_cast<const float4*>(Pp + o00 + (size_t)W * C + C) : z4;
+        const float a00[4] = {v00.x, v00.y, v00.z, v00.w}, a01[4] = {v01.x, v01.y, v01.z, v01.w};
+        const float a10[4] = {v10.x, v10.y, v10.z, v10.w}, a11[4] = {v11.x, v11.y, v11.z, v11.w};
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            t.s[c] = a00[c] * (t.wx0 * t.wy0) + a01[c] * (t.wx1 * t.wy0) + a10[c] * (t.wx0 * t.wy1) + a11[c] * (t.wx1 * t.wy1);
+            if (GRAD) {
+                t.gx[c] = (a01[c] - a00[c]) * t.wy0 + (a11[c] - a10[c]) * t.wy1;
+                t.gy[c] = (a10[c] - a00[c]) * t.wx0 + (a11[c] - a01[c]) * t.wx1;
+            }
+        }
+    }
+}
+
+__device__ __forceinline__ void sample_bwd4_lean(const Layout& lo, int l, const float q[4], const float* __restrict__ packed,
+                                                 const float* __restrict__ trow, float* __restrict__ gpacked,
+                                                 float* __restrict__ gtrow, int c0, const float (&df)[4], float (&dq)[3]) {
+    const int C = lo.C;
+    float suf[6][4];
+    {
+        float run[4] = {1.f, 1.f, 1.f, 1.f};
+#pragma unroll
+        for (int k = 5; k >= 0; --k) {
+            PlaneTaps t;
+            plane_taps<false>(lo, l, k, q, packed, trow, c0, t);
+#pragma unroll
+            for (int c = 0; c < 4; ++c) { suf[k][c] = run[c]; run[c] *= t.s[c]; }
+        }
+    }
+    float pre[4] = {df[0], df[1], df[2], df[3]};
+#pragma unroll
+    for (int k = 0; k < 6; ++k) {
+        PlaneTaps t;
+        plane_taps<true>(lo, l, k, q, packed, trow, c0, t);
+        float ds[4];
+        float gx = 0.f, gy = 0.f;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            ds[c] = pre[c] * suf[k][c];
+            pre[c] *= t.s[c];
+            gx += ds[c] * t.gx[c]; gy += ds[c] * t.gy[c];
+        }
+        dq[pa_of(k)] += gx * t.gmx;
+        const int W = lo.pw[l][k];
+        if (k == 2 || k == 4 || k == 5) {
+            float* T = gtrow + lo.toff[l][k == 2 ? 0 : (k == 4 ? 1 : 2)] + c0;
+            atomicAdd(reinterpret_cast<float4*>(T + (size_t)t.x0 * C), make_float4(ds[0] * t.wx0, ds[1] * t.wx0, ds[2] * t.wx0, ds[3] * t.wx0));
+            if (t.xin)
+                atomicAdd(reinterpret_cast<float4*>(T + (size_t)(t.x0 + 1) * C), make_float4(ds[0] * t.wx1, ds[1] * t.wx1, ds[2] * t.wx1, ds[3] * t.wx1));
+        } else {
+            dq[pb_of(k)] += gy * t.gmy;
+            float* Gp = gpacked + lo.poff[l][k] + c0;
+            const size_t o00 = ((size_t)t.y0 * W + t.x0) * C;
+            const float nw = t.wx0 * t.wy0, ne = t.wx1 * t.wy0, sw = t.wx0 * t.wy1, se = t.wx1 * t.wy1;
+            atomicAdd(reinterpret_cast<float4*>(Gp + o00), make_float4(ds[0] * nw, ds[1] * nw, ds[2] * nw, ds[3] * nw));
+            if (t.xin)
+                atomicAdd(reinterpret_cast<float4*>(Gp + o00 + C), make_float4(ds[0] * ne, ds[1] * ne, ds[2] * ne, ds[3] * ne));
+            if (t.yin)
+                atomicAdd(reinterpret_cast<float4*>(Gp + o00 + (size_t)W * C), make_float4(ds[0] * sw, ds[1] * sw, ds[2] * sw, ds[3] * sw));
+            if (t.xin && t.yin)
+                atomicAdd(reinterpret_cast<float4*>(Gp + o00 + (size_t)W * C + C), make_float4(ds[0] * se, ds[1] * se, ds[2] * se, ds[3] * se));
+        }
+    }
+}
+
 // Sampler backward as its own kernel (SAVED path): LP adjacent lanes per point take consecutive channel quads of its
 // dL/dfeat row (one coalesced 128-byte read per point), recompute the six bilinear samples, scatter dL/dplane with float4
 // reductions and reduce dL/dxyz over the point's lanes.
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 3)
 k_deform_sample_bwd(Layout lo, int P, const float* __restrict__ xyz, const float* __restrict__ GFrows, const float* __restrict__ packed,
                     const float* __restrict__ trow, float* __restrict__ gpacked, float* __restrict__ gtrow, float* __restrict__ d_xyz)
 {
@@ -402,7 +511,7 @@ k_deform_sample_bwd(Layout lo, int P, const float* __restrict__ xyz, const float
         if (sval) {
             const float4 d4 = __ldcs(reinterpret_cast<const float4*>(GFrows + (size_t)sp_ * F + item * 4));
             const float df[4] = {d4.x, d4.y, d4.z, d4.w};
-            sample_bwd4(lo, l, q, packed, trow, gpacked, gtrow, c0, df, dq);
+            sample_bwd4_lean(lo, l, q, packed, trow, gpacked, gtrow, c0, df, dq);
         }
     }
 #pragma unroll
