@@ -380,7 +380,7 @@ __device__ __forceinline__ void head_pass2(uint32_t lane_base, int col0, float* 
 }
 
 // Register-lean sampler backward for 4 channels of one level of one point (the standalone kernel; sample_bwd4 above needs
-// ~170 registers, one 256-thread CTA per SM).  Two sweeps over the six planes: the first keeps only the suffix products
+// ~170 registers, one 256-thread CTA per SM; measured 280 us; this one 222 us at two CTAs per SM, 244 at three, 309 at four).  Two sweeps over the six planes: the first keeps only the suffix products
 // of the samples, the second re-reads the taps (L1 / L2 hits), forms dL/dsample = df * prefix * suffix, scatters and
 // accumulates dL/dq.  Same arithmetic as sample_bwd4 up to the association of the 5-factor products.
 struct PlaneTaps {
@@ -491,7 +491,7 @@ __device__ __forceinline__ void sample_bwd4_lean(const Layout& lo, int l, const 
 // Sampler backward as its own kernel (SAVED path): LP adjacent lanes per point take consecutive channel quads of its
 // dL/dfeat row (one coalesced 128-byte read per point), recompute the six bilinear samples, scatter dL/dplane with float4
 // reductions and reduce dL/dxyz over the point's lanes.
-__global__ void __launch_bounds__(256, 3)
+__global__ void __launch_bounds__(256, 2)
 k_deform_sample_bwd(Layout lo, int P, const float* __restrict__ xyz, const float* __restrict__ GFrows, const float* __restrict__ packed,
                     const float* __restrict__ trow, float* __restrict__ gpacked, float* __restrict__ gtrow, float* __restrict__ d_xyz)
 {
