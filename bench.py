@@ -185,6 +185,9 @@ def algorithmic_per_launch(kernel, s):
         "k_deform_bwd_data": ("tensor", mlp_fwd_flop),
         "k_deform_bwd_data_saved": ("tensor", mlp_fwd_flop),
         "k_deform_bwd_weights": ("tensor", mlp_fwd_flop),
+        # sampler backward: dL/dfeat row + xyz in, d_xyz out, and the float4 reductions it sends to the L2-resident plane
+        # gradients (6 planes: 3 x 4 + 3 x 2 taps of 16 B per 4-channel quad) counted as bytes moved
+        "k_deform_sample_bwd": ("hbm", P * (4.0 * s["F"] + 24.0) + P * (s["F"] / 4.0) * 18 * 16.0),
     }
     return table.get(kernel)
 
@@ -192,9 +195,10 @@ def algorithmic_per_launch(kernel, s):
 # dram__bytes_read.sum + dram__bytes_write.sum per launch from the `ncu --set full` capture of this workload
 # (profiles/r01_ncu_full_summary.csv; P = 300k DyNeRF view).  Reported only for that workload.
 NCU_TRAFFIC_BYTES = {
-    "k_deform_fwd_tc": 0.075682e9 + 1.007728e9, "k_deform_bwd_data_saved": 0.112828e9 + 0.883818e9,
-    "k_deform_bwd_weights": 1.969523e9 + 0.004559e9, "k_blend_bwd": 0.120245e9 + 0.004495e9, "k_blend_fwd": 0.089820e9 + 0.011918e9,
-    "k_tile_sort": 0.025839e9 + 0.035511e9, "k_preprocess": 0.065620e9 + 0.002980e9, "k_preprocess_bwd": 0.093627e9 + 0.039184e9,
+    "k_deform_fwd_tc": 0.075682e9 + 1.007662e9, "k_deform_bwd_data_saved": 0.100450e9 + 0.905332e9,
+    "k_deform_bwd_weights": 1.987011e9 + 0.004113e9, "k_deform_sample_bwd": 0.049985e9 + 0.000285e9,
+    "k_blend_bwd": 0.120027e9 + 0.004179e9, "k_blend_fwd": 0.089780e9 + 0.011699e9,
+    "k_tile_sort": 0.025838e9 + 0.035497e9, "k_preprocess": 0.066367e9 + 0.003340e9, "k_preprocess_bwd": 0.093701e9 + 0.042599e9,
 }
 
 
