@@ -14,6 +14,9 @@ namespace {
 constexpr unsigned FULL = 0xffffffffu;
 constexpr int BATCH = 256;
 constexpr int NACC = 9;          // colour(3), mean2D(2), conic(3), opacity(1)
+#ifndef BLEND_BWD_NPX
+#define BLEND_BWD_NPX 2
+#endif
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
@@ -108,13 +111,17 @@ __device__ __forceinline__ void warp_reduce10(float (&v)[10], int lane) {
     v[0] += __shfl_xor_sync(FULL, v[0], 1);
 }
 
-__global__ void __launch_bounds__(256)
+// NPX pixels per thread (rows py and py + 4): a warp covers an 8 x (4 NPX) sub-rectangle of the tile, so one cull test,
+// one 12-shuffle reduction and one set of shared-memory atomics serve 32 NPX pixels of a hit.
+template <int NPX>
+__global__ void __launch_bounds__(256 / NPX)
 k_blend_bwd(const uint2* __restrict__ ranges, const FdgsRecord* __restrict__ records, int W, int H,
             const float* __restrict__ bg_color, const float* __restrict__ final_Ts,
             const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpixels,
             float* __restrict__ dL_dmean2D /*[P,3]*/, float* __restrict__ dL_dconic /*[P,4]*/,
             float* __restrict__ dL_dopacity, float* __restrict__ dL_dcolors /*[P,3]*/)
 {
+    constexpr int NT = 256 / NPX;
     __shared__ __align__(128) FdgsRecord srec[2][BATCH];
     __shared__ float acc[BATCH][NACC];
     __shared__ __align__(8) uint64_t bars[2];
@@ -124,22 +131,36 @@ k_blend_bwd(const uint2* __restrict__ ranges, const FdgsRecord* __restrict__ rec
     const int tile = blockIdx.y * tiles_x + blockIdx.x;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int wx = wid & 1, wy = wid >> 1;
-    const int bx0 = blockIdx.x * FDGS_TILE + wx * 8, by0 = blockIdx.y * FDGS_TILE + wy * 4;
-    const int px = bx0 + (lane & 7), py = by0 + (lane >> 3);
-    const bool inside = px < W && py < H;
-    const float pxf = (float)px, pyf = (float)py;
+    const int bx0 = blockIdx.x * FDGS_TILE + wx * 8, by0 = blockIdx.y * FDGS_TILE + wy * 4 * NPX;
+    const int px = bx0 + (lane & 7);
+    const float pxf = (float)px;
     const float cx0 = (float)bx0, cy0 = (float)by0;
-    const float cx1 = (float)min(bx0 + 7, W - 1), cy1 = (float)min(by0 + 3, H - 1);
+    const float cx1 = (float)min(bx0 + 7, W - 1), cy1 = (float)min(by0 + 4 * NPX - 1, H - 1);
     const size_t HW = (size_t)H * W;
-    const size_t pix_id = (size_t)py * W + px;
-
     const uint2 range = ranges[tile];
-    const float T_final = inside ? final_Ts[pix_id] : 0.f;
-    const uint32_t last_contributor = inside ? n_contrib[pix_id] : 0u;
-    float dLp0 = 0.f, dLp1 = 0.f, dLp2 = 0.f;
-    if (inside) { dLp0 = dL_dpixels[pix_id]; dLp1 = dL_dpixels[HW + pix_id]; dLp2 = dL_dpixels[2 * HW + pix_id]; }
-    float bg_dot = 0.f;
-    bg_dot += bg_color[0] * dLp0; bg_dot += bg_color[1] * dLp1; bg_dot += bg_color[2] * dLp2;
+
+    float pyf[NPX], T_final[NPX], T[NPX], dLp0[NPX], dLp1[NPX], dLp2[NPX], bg_dot[NPX];
+    float ar0[NPX], ar1[NPX], ar2[NPX], last_alpha[NPX], lc0[NPX], lc1[NPX], lc2[NPX];
+    uint32_t last_contributor[NPX];
+    uint32_t lmax = 0;
+#pragma unroll
+    for (int j = 0; j < NPX; ++j) {
+        const int py = by0 + (lane >> 3) + 4 * j;
+        const bool inside = px < W && py < H;
+        const size_t pix_id = (size_t)py * W + px;
+        pyf[j] = (float)py;
+        T_final[j] = inside ? final_Ts[pix_id] : 0.f;
+        last_contributor[j] = inside ? n_contrib[pix_id] : 0u;
+        lmax = max(lmax, last_contributor[j]);
+        dLp0[j] = dLp1[j] = dLp2[j] = 0.f;
+        if (inside) { dLp0[j] = dL_dpixels[pix_id]; dLp1[j] = dL_dpixels[HW + pix_id]; dLp2[j] = dL_dpixels[2 * HW + pix_id]; }
+        float bd = 0.f;
+        bd += bg_color[0] * dLp0[j]; bd += bg_color[1] * dLp1[j]; bd += bg_color[2] * dLp2[j];
+        bg_dot[j] = bd;
+        T[j] = T_final[j];
+        ar0[j] = ar1[j] = ar2[j] = 0.f;
+        last_alpha[j] = lc0[j] = lc1[j] = lc2[j] = 0.f;
+    }
     const float ddelx_dx = 0.5 * W, ddely_dy = 0.5 * H;
 
     if (threadIdx.x == 0) {
@@ -148,9 +169,9 @@ k_blend_bwd(const uint2* __restrict__ ranges, const FdgsRecord* __restrict__ rec
         mbar_init(&bars[1], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    for (int i = threadIdx.x; i < BATCH * NACC; i += 256) (&acc[0][0])[i] = 0.f;
+    for (int i = threadIdx.x; i < BATCH * NACC; i += NT) (&acc[0][0])[i] = 0.f;
     __syncthreads();
-    const uint32_t wmax = __reduce_max_sync(FULL, last_contributor);
+    const uint32_t wmax = __reduce_max_sync(FULL, lmax);
     if (lane == 0 && wmax) atomicMax(&s_maxc, wmax);
     __syncthreads();
     const int total = (int)min(s_maxc, range.y - range.x);     // records beyond the last contributor are dead
@@ -166,10 +187,6 @@ k_blend_bwd(const uint2* __restrict__ ranges, const FdgsRecord* __restrict__ rec
         bulk_g2s(&srec[b & 1][0], records + range.x + lo, bytes, &bars[b & 1]);
     };
     if (threadIdx.x == 0) issue(0);
-
-    float T = T_final;
-    float ar0 = 0.f, ar1 = 0.f, ar2 = 0.f;           // accum_rec
-    float last_alpha = 0.f, lc0 = 0.f, lc1 = 0.f, lc2 = 0.f;
 
     for (int b = 0; b < nb; ++b) {
         if (threadIdx.x == 0 && b + 1 < nb) issue(b + 1);
@@ -196,42 +213,45 @@ k_blend_bwd(const uint2* __restrict__ ranges, const FdgsRecord* __restrict__ rec
                     float v[10];
 #pragma unroll
                     for (int k = 0; k < 10; ++k) v[k] = 0.f;
-                    if (pos < last_contributor) {
-                        const float4 q0 = reinterpret_cast<const float4*>(&rec[jj])[0];
-                        const float4 q1 = reinterpret_cast<const float4*>(&rec[jj])[1];
-                        const float dx = q0.x - pxf, dy = q0.y - pyf;
-                        const float power = -0.5f * (q0.z * dx * dx + q1.x * dy * dy) - q0.w * dx * dy;
-                        if (!(power > 0.0f)) {
-                            const float G = expf(power);
-                            const float alpha = fminf(0.99f, q1.y * G);
-                            if (!(alpha < 1.0f / 255.0f)) {
-                                const float4 q2 = reinterpret_cast<const float4*>(&rec[jj])[2];
-                                const float inv1ma = 1.f / (1.f - alpha);           // one division for both uses
-                                T = T * inv1ma;
-                                const float dchannel_dcolor = alpha * T;
-                                float dL_dalpha = 0.0f;
-                                ar0 = last_alpha * lc0 + (1.f - last_alpha) * ar0; lc0 = q2.x;
-                                dL_dalpha += (q2.x - ar0) * dLp0;
-                                ar1 = last_alpha * lc1 + (1.f - last_alpha) * ar1; lc1 = q2.y;
-                                dL_dalpha += (q2.y - ar1) * dLp1;
-                                ar2 = last_alpha * lc2 + (1.f - last_alpha) * ar2; lc2 = q2.z;
-                                dL_dalpha += (q2.z - ar2) * dLp2;
-                                v[0] = dchannel_dcolor * dLp0;
-                                v[1] = dchannel_dcolor * dLp1;
-                                v[2] = dchannel_dcolor * dLp2;
-                                dL_dalpha *= T;
-                                last_alpha = alpha;
-                                dL_dalpha += (-T_final * inv1ma) * bg_dot;
-                                const float dL_dG = q1.y * dL_dalpha;
-                                const float gdx = G * dx, gdy = G * dy;
-                                const float dG_ddelx = -gdx * q0.z - gdy * q0.w;
-                                const float dG_ddely = -gdy * q1.x - gdx * q0.w;
-                                v[3] = dL_dG * dG_ddelx * ddelx_dx;
-                                v[4] = dL_dG * dG_ddely * ddely_dy;
-                                v[5] = -0.5f * gdx * dx * dL_dG;
-                                v[6] = -0.5f * gdx * dy * dL_dG;
-                                v[7] = -0.5f * gdy * dy * dL_dG;
-                                v[8] = G * dL_dalpha;
+#pragma unroll
+                    for (int pj = 0; pj < NPX; ++pj) {
+                        if (pos < last_contributor[pj]) {
+                            const float4 q0 = reinterpret_cast<const float4*>(&rec[jj])[0];
+                            const float4 q1 = reinterpret_cast<const float4*>(&rec[jj])[1];
+                            const float dx = q0.x - pxf, dy = q0.y - pyf[pj];
+                            const float power = -0.5f * (q0.z * dx * dx + q1.x * dy * dy) - q0.w * dx * dy;
+                            if (!(power > 0.0f)) {
+                                const float G = expf(power);
+                                const float alpha = fminf(0.99f, q1.y * G);
+                                if (!(alpha < 1.0f / 255.0f)) {
+                                    const float4 q2 = reinterpret_cast<const float4*>(&rec[jj])[2];
+                                    const float inv1ma = 1.f / (1.f - alpha);           // one division for both uses
+                                    T[pj] = T[pj] * inv1ma;
+                                    const float dchannel_dcolor = alpha * T[pj];
+                                    float dL_dalpha = 0.0f;
+                                    ar0[pj] = last_alpha[pj] * lc0[pj] + (1.f - last_alpha[pj]) * ar0[pj]; lc0[pj] = q2.x;
+                                    dL_dalpha += (q2.x - ar0[pj]) * dLp0[pj];
+                                    ar1[pj] = last_alpha[pj] * lc1[pj] + (1.f - last_alpha[pj]) * ar1[pj]; lc1[pj] = q2.y;
+                                    dL_dalpha += (q2.y - ar1[pj]) * dLp1[pj];
+                                    ar2[pj] = last_alpha[pj] * lc2[pj] + (1.f - last_alpha[pj]) * ar2[pj]; lc2[pj] = q2.z;
+                                    dL_dalpha += (q2.z - ar2[pj]) * dLp2[pj];
+                                    v[0] += dchannel_dcolor * dLp0[pj];
+                                    v[1] += dchannel_dcolor * dLp1[pj];
+                                    v[2] += dchannel_dcolor * dLp2[pj];
+                                    dL_dalpha *= T[pj];
+                                    last_alpha[pj] = alpha;
+                                    dL_dalpha += (-T_final[pj] * inv1ma) * bg_dot[pj];
+                                    const float dL_dG = q1.y * dL_dalpha;
+                                    const float gdx = G * dx, gdy = G * dy;
+                                    const float dG_ddelx = -gdx * q0.z - gdy * q0.w;
+                                    const float dG_ddely = -gdy * q1.x - gdx * q0.w;
+                                    v[3] += dL_dG * dG_ddelx * ddelx_dx;
+                                    v[4] += dL_dG * dG_ddely * ddely_dy;
+                                    v[5] += -0.5f * gdx * dx * dL_dG;
+                                    v[6] += -0.5f * gdx * dy * dL_dG;
+                                    v[7] += -0.5f * gdy * dy * dL_dG;
+                                    v[8] += G * dL_dalpha;
+                                }
                             }
                         }
                     }
@@ -242,26 +262,25 @@ k_blend_bwd(const uint2* __restrict__ ranges, const FdgsRecord* __restrict__ rec
             }
         }
         __syncthreads();                                   // batch fully accumulated
-        float a[NACC];
-        uint32_t gid = 0;
-        const bool mine = (int)threadIdx.x < cnt;
-        if (mine) {
-            gid = rec[threadIdx.x].id;
+        for (int r0 = 0; r0 < BATCH; r0 += NT) {
+            const int r = r0 + (int)threadIdx.x;
+            if (r < cnt) {
+                const uint32_t gid = rec[r].id;
+                float a[NACC];
 #pragma unroll
-            for (int k = 0; k < NACC; ++k) { a[k] = acc[threadIdx.x][k]; acc[threadIdx.x][k] = 0.f; }
+                for (int k = 0; k < NACC; ++k) { a[k] = acc[r][k]; acc[r][k] = 0.f; }
+                if (a[0] != 0.f) atomicAdd(&dL_dcolors[3 * (size_t)gid + 0], a[0]);
+                if (a[1] != 0.f) atomicAdd(&dL_dcolors[3 * (size_t)gid + 1], a[1]);
+                if (a[2] != 0.f) atomicAdd(&dL_dcolors[3 * (size_t)gid + 2], a[2]);
+                if (a[3] != 0.f) atomicAdd(&dL_dmean2D[3 * (size_t)gid + 0], a[3]);
+                if (a[4] != 0.f) atomicAdd(&dL_dmean2D[3 * (size_t)gid + 1], a[4]);
+                if (a[5] != 0.f) atomicAdd(&dL_dconic[4 * (size_t)gid + 0], a[5]);
+                if (a[6] != 0.f) atomicAdd(&dL_dconic[4 * (size_t)gid + 1], a[6]);
+                if (a[7] != 0.f) atomicAdd(&dL_dconic[4 * (size_t)gid + 3], a[7]);
+                if (a[8] != 0.f) atomicAdd(&dL_dopacity[gid], a[8]);
+            }
         }
         __syncthreads();                                   // srec[b&1] and acc are free again
-        if (mine) {
-            if (a[0] != 0.f) atomicAdd(&dL_dcolors[3 * (size_t)gid + 0], a[0]);
-            if (a[1] != 0.f) atomicAdd(&dL_dcolors[3 * (size_t)gid + 1], a[1]);
-            if (a[2] != 0.f) atomicAdd(&dL_dcolors[3 * (size_t)gid + 2], a[2]);
-            if (a[3] != 0.f) atomicAdd(&dL_dmean2D[3 * (size_t)gid + 0], a[3]);
-            if (a[4] != 0.f) atomicAdd(&dL_dmean2D[3 * (size_t)gid + 1], a[4]);
-            if (a[5] != 0.f) atomicAdd(&dL_dconic[4 * (size_t)gid + 0], a[5]);
-            if (a[6] != 0.f) atomicAdd(&dL_dconic[4 * (size_t)gid + 1], a[6]);
-            if (a[7] != 0.f) atomicAdd(&dL_dconic[4 * (size_t)gid + 3], a[7]);
-            if (a[8] != 0.f) atomicAdd(&dL_dopacity[gid], a[8]);
-        }
     }
 }
 
@@ -520,7 +539,7 @@ extern "C" int fdgs_raster_backward(const FdgsRasterBackward* a, void* stream_) 
     if (a->R > 0) {
         dim3 grid(gx, gy);
         { FDGS_PROF("k_blend_bwd", stream);
-        k_blend_bwd<<<grid, 256, 0, stream>>>(im.ranges, bn.records, a->W, a->H, a->background, im.final_T, im.n_contrib,
+        k_blend_bwd<BLEND_BWD_NPX><<<grid, 256 / BLEND_BWD_NPX, 0, stream>>>(im.ranges, bn.records, a->W, a->H, a->background, im.final_T, im.n_contrib,
                                               a->dL_dpix, a->dL_dmeans2D, a->dL_dconic, a->dL_dopacity, a->dL_dcolors);
         }
         FDGS_LAUNCH_CHECK(a->debug, stream);
