@@ -218,7 +218,9 @@ k_blend_bwd(const uint2* __restrict__ ranges, const FdgsRecord* __restrict__ rec
                         if (pos < last_contributor[pj]) {
                             const float4 q0 = reinterpret_cast<const float4*>(&rec[jj])[0];
                             const float4 q1 = reinterpret_cast<const float4*>(&rec[jj])[1];
-                            const float dx = q0.x - pxf, dy = q0.y - pyf[pj];
+                            float dx = q0.x - pxf;                 // opaque per pixel: same FMA contraction of `power`
+                            asm volatile("" : "+f"(dx));           // (and hence the same alpha tests) as the forward
+                            const float dy = q0.y - pyf[pj];
                             const float power = -0.5f * (q0.z * dx * dx + q1.x * dy * dy) - q0.w * dx * dy;
                             if (!(power > 0.0f)) {
                                 const float G = expf(power);
