@@ -197,7 +197,7 @@ def algorithmic_per_launch(kernel, s):
 NCU_TRAFFIC_BYTES = {
     "k_deform_fwd_tc": 0.075682e9 + 1.007662e9, "k_deform_bwd_data_saved": 0.100450e9 + 0.905332e9,
     "k_deform_bwd_weights": 1.987011e9 + 0.004113e9, "k_deform_sample_bwd": 0.049985e9 + 0.000285e9,
-    "k_blend_bwd": 0.120027e9 + 0.004179e9, "k_blend_fwd": 0.089780e9 + 0.011699e9,
+    "k_blend_bwd": 0.119234e9 + 0.003775e9, "k_blend_fwd": 0.089780e9 + 0.011699e9,
     "k_tile_sort": 0.025838e9 + 0.035497e9, "k_preprocess": 0.066367e9 + 0.003340e9, "k_preprocess_bwd": 0.093701e9 + 0.042599e9,
 }
 
