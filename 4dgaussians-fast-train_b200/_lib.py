@@ -102,6 +102,17 @@ class FdgsDeformBackward(C.Structure):
     ]
 
 
+class FdgsActivateForward(C.Structure):
+    _fields_ = [("P", C.c_int32), ("scales_raw", C.c_void_p), ("rotations_raw", C.c_void_p), ("opacity_raw", C.c_void_p),
+                ("scales", C.c_void_p), ("rotations", C.c_void_p), ("opacity", C.c_void_p)]
+
+
+class FdgsActivateBackward(C.Structure):
+    _fields_ = [("P", C.c_int32), ("rotations_raw", C.c_void_p), ("scales", C.c_void_p), ("rotations", C.c_void_p),
+                ("opacity", C.c_void_p), ("g_scales", C.c_void_p), ("g_rotations", C.c_void_p), ("g_opacity", C.c_void_p),
+                ("d_scales_raw", C.c_void_p), ("d_rotations_raw", C.c_void_p), ("d_opacity_raw", C.c_void_p)]
+
+
 # every symbol include/fdgs.h declares: name -> (restype, argtypes)
 SYMBOLS = {
     "fdgs_abi_version": (C.c_int, []),
@@ -126,6 +137,8 @@ SYMBOLS = {
     "fdgs_deform_backward_ws_bytes": (C.c_size_t, [C.POINTER(FdgsDeformNet)]),
     "fdgs_deform_backward_scratch_bytes": (C.c_size_t, [C.POINTER(FdgsDeformNet), C.c_int]),
     "fdgs_deform_backward": (C.c_int, [C.POINTER(FdgsDeformBackward), C.c_void_p]),
+    "fdgs_activate_forward": (C.c_int, [C.POINTER(FdgsActivateForward), C.c_void_p]),
+    "fdgs_activate_backward": (C.c_int, [C.POINTER(FdgsActivateBackward), C.c_void_p]),
 }
 
 _lib = None

@@ -1,0 +1,89 @@
+// Caller-side glue between the deformation field and the rasterizer (include/fdgs.h: fdgs_activate_*): the scale /
+// rotation / opacity activations of gaussian_renderer/__init__.py:97-99 (torch.exp, F.normalize(dim=1, eps=1e-12),
+// torch.sigmoid; scene/gaussian_model.py:47-58) and their backward, one launch each way instead of ~15 ATen kernels.
+#include "fdgs_common.cuh"
+#include "prof.cuh"
+
+namespace {
+
+constexpr float NORM_EPS = 1e-12f;
+
+__global__ void __launch_bounds__(256)
+k_activate_fwd(int P, const float* __restrict__ s_raw, const float* __restrict__ r_raw, const float* __restrict__ o_raw,
+               float* __restrict__ s, float* __restrict__ r, float* __restrict__ o)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P) return;
+    if (s) {
+#pragma unroll
+        for (int k = 0; k < 3; ++k) s[3 * (size_t)i + k] = expf(s_raw[3 * (size_t)i + k]);
+    }
+    if (r) {
+        const float4 q = reinterpret_cast<const float4*>(r_raw)[i];
+        const float n = sqrtf(q.x * q.x + q.y * q.y + q.z * q.z + q.w * q.w);
+        const float d = fmaxf(n, NORM_EPS);
+        reinterpret_cast<float4*>(r)[i] = make_float4(q.x / d, q.y / d, q.z / d, q.w / d);
+    }
+    if (o) o[i] = 1.0f / (1.0f + expf(-o_raw[i]));
+}
+
+__global__ void __launch_bounds__(256)
+k_activate_bwd(int P, const float* __restrict__ r_raw, const float* __restrict__ s, const float* __restrict__ r,
+               const float* __restrict__ o, const float* __restrict__ gs, const float* __restrict__ gr,
+               const float* __restrict__ go, float* __restrict__ ds, float* __restrict__ dr, float* __restrict__ dopa)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P) return;
+    if (ds) {
+#pragma unroll
+        for (int k = 0; k < 3; ++k) ds[3 * (size_t)i + k] = gs[3 * (size_t)i + k] * s[3 * (size_t)i + k];
+    }
+    if (dr) {
+        const float4 q = reinterpret_cast<const float4*>(r_raw)[i];
+        const float4 g = reinterpret_cast<const float4*>(gr)[i];
+        const float n = sqrtf(q.x * q.x + q.y * q.y + q.z * q.z + q.w * q.w);
+        float4 d;
+        if (n >= NORM_EPS) {              // d(q / n): (g - u (u . g)) / n with u = q / n
+            const float4 u = reinterpret_cast<const float4*>(r)[i];
+            const float dot = u.x * g.x + u.y * g.y + u.z * g.z + u.w * g.w;
+            const float inv = 1.0f / n;
+            d = make_float4((g.x - u.x * dot) * inv, (g.y - u.y * dot) * inv, (g.z - u.z * dot) * inv, (g.w - u.w * dot) * inv);
+        } else {                          // clamp_min(eps) is active: the denominator is the constant eps
+            d = make_float4(g.x / NORM_EPS, g.y / NORM_EPS, g.z / NORM_EPS, g.w / NORM_EPS);
+        }
+        reinterpret_cast<float4*>(dr)[i] = d;
+    }
+    if (dopa) { const float v = o[i]; dopa[i] = go[i] * v * (1.0f - v); }
+}
+
+}  // namespace
+
+extern "C" {
+
+int fdgs_activate_forward(const FdgsActivateForward* a, void* stream_) {
+    if (!a || a->P < 0) return FDGS_E_BADARG;
+    if ((a->scales && !a->scales_raw) || (a->rotations && !a->rotations_raw) || (a->opacity && !a->opacity_raw)) return FDGS_E_BADARG;
+    if (a->P == 0) return FDGS_OK;
+    cudaStream_t stream = (cudaStream_t)stream_;
+    { FDGS_PROF("k_activate_fwd", stream);
+    k_activate_fwd<<<(a->P + 255) / 256, 256, 0, stream>>>(a->P, a->scales_raw, a->rotations_raw, a->opacity_raw, a->scales, a->rotations, a->opacity);
+    }
+    FDGS_LAUNCH_CHECK(0, stream);
+    return FDGS_OK;
+}
+
+int fdgs_activate_backward(const FdgsActivateBackward* a, void* stream_) {
+    if (!a || a->P < 0) return FDGS_E_BADARG;
+    if ((a->d_scales_raw && (!a->g_scales || !a->scales)) || (a->d_rotations_raw && (!a->g_rotations || !a->rotations || !a->rotations_raw)) ||
+        (a->d_opacity_raw && (!a->g_opacity || !a->opacity))) return FDGS_E_BADARG;
+    if (a->P == 0) return FDGS_OK;
+    cudaStream_t stream = (cudaStream_t)stream_;
+    { FDGS_PROF("k_activate_bwd", stream);
+    k_activate_bwd<<<(a->P + 255) / 256, 256, 0, stream>>>(a->P, a->rotations_raw, a->scales, a->rotations, a->opacity, a->g_scales, a->g_rotations,
+                                                           a->g_opacity, a->d_scales_raw, a->d_rotations_raw, a->d_opacity_raw);
+    }
+    FDGS_LAUNCH_CHECK(0, stream);
+    return FDGS_OK;
+}
+
+}  // extern "C"

@@ -5,12 +5,15 @@ Differences, none observable in the results:
   * the per-call `.cuda()` copies of the camera matrices (:45-48) are skipped when the tensors are
     already on the device;
   * `time` is passed as one device scalar instead of a [P,1] repeat (:52) — the fused deformation
-    kernel takes one timestamp per view.
+    kernel takes one timestamp per view;
+  * when the model binds the reference's three activations (exp / normalize / sigmoid, :97-99) they run as
+    one fused kernel each way (fdgs.activations); any other callables are used as they are.
 """
 import math
 
 import torch
 
+from .activations import fused_activations, is_reference_activations
 from .diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer
 
 
@@ -54,9 +57,12 @@ def render(viewpoint_camera, pc, pipe=None, bg_color=None, scaling_modifier=1.0,
     else:
         raise NotImplementedError
 
-    scales_final = pc.scaling_activation(scales_final)
-    rotations_final = pc.rotation_activation(rotations_final)
-    opacity = pc.opacity_activation(opacity_final)
+    if scales_final.is_cuda and is_reference_activations(pc):
+        scales_final, rotations_final, opacity = fused_activations(scales_final, rotations_final, opacity_final)
+    else:
+        scales_final = pc.scaling_activation(scales_final)
+        rotations_final = pc.rotation_activation(rotations_final)
+        opacity = pc.opacity_activation(opacity_final)
 
     colors_precomp = override_color
     rendered_image, radii, depth = rasterizer(

@@ -267,6 +267,37 @@ size_t fdgs_deform_backward_ws_bytes(const FdgsDeformNet* net);
 size_t fdgs_deform_backward_scratch_bytes(const FdgsDeformNet* net, int P);
 int fdgs_deform_backward(const FdgsDeformBackward* a, void* stream);
 
+/* ---- activations between the two operators (caller-side glue) -----------------------------------
+ * Replaces the three activation calls of gaussian_renderer/__init__.py:97-99 on the deformation outputs
+ *   scales = exp(scales_raw), rotations = F.normalize(rotations_raw, dim=1, eps=1e-12), opacity = sigmoid(opacity_raw)
+ * (scene/gaussian_model.py:47-58 binds them as scaling_activation / rotation_activation / opacity_activation) and their
+ * ~10 autograd kernels with one kernel each way.  All pointers: device, contiguous FP32, P rows.                        */
+typedef struct {
+    int32_t P;
+    const float* scales_raw;        /* [P,3] */
+    const float* rotations_raw;     /* [P,4] */
+    const float* opacity_raw;       /* [P,1] */
+    float* scales;                  /* [P,3] out */
+    float* rotations;               /* [P,4] out */
+    float* opacity;                 /* [P,1] out */
+} FdgsActivateForward;
+int fdgs_activate_forward(const FdgsActivateForward* a, void* stream);
+
+typedef struct {
+    int32_t P;
+    const float* rotations_raw;     /* [P,4] forward input */
+    const float* scales;            /* [P,3] forward outputs */
+    const float* rotations;         /* [P,4] */
+    const float* opacity;           /* [P,1] */
+    const float* g_scales;          /* upstream grads w.r.t. the activated values; NULL = none */
+    const float* g_rotations;
+    const float* g_opacity;
+    float* d_scales_raw;            /* [P,3] out (written, not accumulated); NULL with a NULL upstream grad */
+    float* d_rotations_raw;         /* [P,4] */
+    float* d_opacity_raw;           /* [P,1] */
+} FdgsActivateBackward;
+int fdgs_activate_backward(const FdgsActivateBackward* a, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

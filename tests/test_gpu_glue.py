@@ -1,0 +1,78 @@
+"""Fused activation glue (include/fdgs.h: fdgs_activate_*) against the ATen ops the reference calls
+(gaussian_renderer/__init__.py:97-99): torch.exp, F.normalize(dim=1, eps=1e-12), torch.sigmoid."""
+import pytest
+import torch
+
+import util
+
+pytestmark = pytest.mark.gpu
+
+
+def _ref(s, r, o):
+    return torch.exp(s), torch.nn.functional.normalize(r), torch.sigmoid(o)
+
+
+@pytest.mark.parametrize("P", [1, 257, 100_003])
+def test_fused_activations_match_aten(P):
+    from fdgs.activations import fused_activations
+    gen = torch.Generator(device="cuda").manual_seed(P)
+    s = (torch.randn(P, 3, generator=gen, device="cuda") - 4).requires_grad_(True)
+    r = torch.randn(P, 4, generator=gen, device="cuda").requires_grad_(True)
+    o = (2 * torch.randn(P, 1, generator=gen, device="cuda")).requires_grad_(True)
+    outs = fused_activations(s, r, o)
+    s2, r2, o2 = (t.detach().clone().requires_grad_(True) for t in (s, r, o))
+    refs = _ref(s2, r2, o2)
+    for a, b in zip(outs, refs):
+        assert a.shape == b.shape
+        torch.testing.assert_close(a, b, rtol=2e-6, atol=1e-7)       # 1-2 ulp: expf / division order
+    gs = [torch.randn(t.shape, generator=gen, device="cuda") for t in outs]
+    torch.autograd.backward(outs, gs)
+    torch.autograd.backward(refs, gs)
+    for a, b in ((s, s2), (r, r2), (o, o2)):
+        torch.testing.assert_close(a.grad, b.grad, rtol=1e-5, atol=1e-6)
+
+
+def test_fused_activations_degenerate_rows_and_partial_grads():
+    from fdgs.activations import fused_activations
+    s = torch.zeros(4, 3, device="cuda", requires_grad=True)
+    r = torch.tensor([[0., 0, 0, 0], [1e-20, 0, 0, 0], [0, 3, 0, 4], [1, 1, 1, 1]], device="cuda", requires_grad=True)
+    o = torch.tensor([[-100.], [0.], [100.], [1.]], device="cuda")         # no grad wanted for opacity
+    so, ro, oo = fused_activations(s, r, o)
+    rs, rr, ro_ref = _ref(s.detach(), r.detach(), o)
+    torch.testing.assert_close(ro, rr, rtol=2e-6, atol=0)
+    torch.testing.assert_close(oo, ro_ref, rtol=2e-6, atol=1e-38)
+    assert not oo.requires_grad
+    (ro.sum() + so.sum()).backward()
+    r2 = r.detach().clone().requires_grad_(True)
+    torch.nn.functional.normalize(r2).sum().backward()
+    torch.testing.assert_close(r.grad, r2.grad, rtol=1e-5, atol=1e-6)      # includes the clamp_min(eps) rows
+    assert torch.equal(s.grad, torch.ones_like(s))
+
+
+def test_render_uses_fused_activations_and_matches_aten_path():
+    """render() with the reference's activations (fused) vs. the same model with wrapped callables (ATen path)."""
+    import fdgs  # noqa: F401
+    from fdgs import synth
+    from fdgs.configs import CONFIGS
+    from fdgs.deformation import deform_network
+    from fdgs.render import render
+    cfg = CONFIGS["tiny"]
+    net = synth.seeded_deformation(deform_network, cfg["args"](), seed=5, device="cuda")
+    g = synth.make_gaussians(cfg["P"], extent=cfg["extent"], logscale=cfg["logscale"], seed=1, device="cuda")
+    pc = synth.SynthGaussians(g, net).to("cuda")
+    net.deformation_net.set_aabb(pc._xyz.detach().max(0).values.tolist(), pc._xyz.detach().min(0).values.tolist())
+    cam = synth.make_cameras(cfg["W"], cfg["H"], cfg["fovx"], 1, device="cuda")[0]
+    bg = torch.ones(3, device="cuda")
+    out_fused = render(cam, pc, bg_color=bg)["render"]
+    out_fused.sum().backward()
+    g_fused = pc._scaling.grad.clone(), pc._rotation.grad.clone(), pc._opacity.grad.clone()
+    for p in (pc._scaling, pc._rotation, pc._opacity, pc._xyz, pc._features_dc, pc._features_rest):
+        p.grad = None
+    net.zero_grad(set_to_none=True)
+    pc.scaling_activation = lambda t: torch.exp(t)           # not the reference's function objects -> ATen path
+    out_aten = render(cam, pc, bg_color=bg)["render"]
+    out_aten.sum().backward()
+    torch.testing.assert_close(out_fused, out_aten, rtol=1e-5, atol=1e-6)
+    # the rasterizer backward sums with float atomics: two runs of the SAME path differ by ~1e-5 of the largest gradient
+    for a, b in zip(g_fused, (pc._scaling.grad, pc._rotation.grad, pc._opacity.grad)):
+        assert util.rel_err(a, b) < 1e-4
