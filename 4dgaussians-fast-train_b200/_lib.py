@@ -139,6 +139,8 @@ SYMBOLS = {
     "fdgs_deform_backward": (C.c_int, [C.POINTER(FdgsDeformBackward), C.c_void_p]),
     "fdgs_activate_forward": (C.c_int, [C.POINTER(FdgsActivateForward), C.c_void_p]),
     "fdgs_activate_backward": (C.c_int, [C.POINTER(FdgsActivateBackward), C.c_void_p]),
+    "fdgs_l1_loss_forward": (C.c_int, [C.c_void_p, C.c_void_p, C.c_longlong, C.c_float, C.c_void_p, C.c_void_p]),
+    "fdgs_l1_loss_backward": (C.c_int, [C.c_void_p, C.c_void_p, C.c_longlong, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]),
 }
 
 _lib = None

@@ -91,8 +91,9 @@ def l1_view_loss(image, gt, n_views_total):
     return (image - gt).abs().mean() / float(n_views_total)
 
 
-def train_iteration(render_fn, pc, cams, gts, bg, bucket, rank=0, world=1, read_loss=False):
+def train_iteration(render_fn, pc, cams, gts, bg, bucket, rank=0, world=1, read_loss=False, loss_fn=None):
     """One fwd+bwd iteration over the batch `cams` (all B views; this rank renders its shard).
+    loss_fn(image, gt, B): per-view loss; default = the ATen l1_view_loss above (fdgs.losses.l1_view_loss is the fused one).
     Returns (local loss sum as a tensor, max radii, visibility) like train.py:229-232 needs."""
     B = len(cams)
     bucket.zero()
@@ -100,7 +101,7 @@ def train_iteration(render_fn, pc, cams, gts, bg, bucket, rank=0, world=1, read_
     radii_max = None
     for i in shard_views(B, rank, world):
         out = render_fn(cams[i], pc, bg_color=bg, stage="fine")
-        loss = l1_view_loss(out["render"], gts[i], B)
+        loss = (loss_fn or l1_view_loss)(out["render"], gts[i], B)
         loss.backward()
         vs = out["viewspace_points"].grad
         if vs is not None and "viewspace" in bucket.extra:

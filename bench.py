@@ -299,12 +299,14 @@ def main():
             return ref_port.ref_render(refC, SettingsTuple, cam, pc, bg_color, stage=stage)
         launch_count = lambda: 0
         L = None
+        fused_loss = None
     else:
         import fdgs  # noqa: F401
         from fdgs import _lib as L
         from fdgs.render import render as render_fn
         L.load()
         launch_count = L.launch_count
+        from fdgs.losses import l1_view_loss as fused_loss     # the reference arm keeps the ATen loss
 
     cfg, args, pc, net, cams, gts_host = build_scene(a.config, a.impl, dev, a.views, a.points)
     from fdgs.dp import train_iteration, shard_views
@@ -321,7 +323,7 @@ def main():
         torch.cuda.synchronize()
 
     def step_resident():
-        train_iteration(render_fn, pc, cams, gts_dev, bg, bucket, eff_rank, eff_world)
+        train_iteration(render_fn, pc, cams, gts_dev, bg, bucket, eff_rank, eff_world, loss_fn=fused_loss)
 
     stage_gt = [None] * B
 
@@ -331,7 +333,7 @@ def main():
         for i in mine:
             stage_gt[i] = gts_host[i].to(dev, non_blocking=True)
             cs[i] = upload_camera(cams[i], cams_host[i], dev)
-        loss, _ = train_iteration(render_fn, pc, cs, stage_gt, bg, bucket, eff_rank, eff_world, read_loss=True)
+        loss, _ = train_iteration(render_fn, pc, cs, stage_gt, bg, bucket, eff_rank, eff_world, read_loss=True, loss_fn=fused_loss)
         return loss
 
     def timed(fn, steps):

@@ -298,6 +298,14 @@ typedef struct {
 } FdgsActivateBackward;
 int fdgs_activate_backward(const FdgsActivateBackward* a, void* stream);
 
+/* ---- L1 photometric loss of the training step (caller-side glue) ---------------------------------------------------------
+ * utils/loss_utils.py l1_loss(network_output, gt) = mean |a - b| (train.py's Ll1), with its autograd:
+ *   forward : *loss += scale * sum_i |a_i - b_i|          (*loss is a DEVICE scalar the caller zeroed; scale = 1 / n, or
+ *                                                           1 / (n * views) for one view's share of a batch loss)
+ *   backward: d_a_i = *g * scale * sign(a_i - b_i)        (*g = DEVICE scalar upstream gradient; sign(0) = 0 as in ATen)   */
+int fdgs_l1_loss_forward(const float* a, const float* b, long long n, float scale, float* loss, void* stream);
+int fdgs_l1_loss_backward(const float* a, const float* b, long long n, float scale, const float* g, float* d_a, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

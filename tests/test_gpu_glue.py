@@ -76,3 +76,24 @@ def test_render_uses_fused_activations_and_matches_aten_path():
     # the rasterizer backward sums with float atomics: two runs of the SAME path differ by ~1e-5 of the largest gradient
     for a, b in zip(g_fused, (pc._scaling.grad, pc._rotation.grad, pc._opacity.grad)):
         assert util.rel_err(a, b) < 1e-4
+
+
+@pytest.mark.parametrize("shape", [(3, 64, 200), (3, 1014, 1352), (7,), (1, 5, 3)])
+def test_fused_l1_loss_matches_aten(shape):
+    """fdgs.losses.l1_loss vs utils/loss_utils.py:20-21 (torch.abs(a - b).mean()), value and both gradients."""
+    from fdgs.losses import l1_loss, l1_view_loss
+    gen = torch.Generator(device="cuda").manual_seed(len(shape))
+    a = torch.rand(shape, generator=gen, device="cuda").requires_grad_(True)
+    b = torch.rand(shape, generator=gen, device="cuda").requires_grad_(True)
+    with torch.no_grad():
+        b[..., :1] = a[..., :1]                                   # exact ties: sign(0) = 0
+    a2, b2 = a.detach().clone().requires_grad_(True), b.detach().clone().requires_grad_(True)
+    l = l1_loss(a, b)
+    l_ref = torch.abs(a2 - b2).mean()
+    torch.testing.assert_close(l, l_ref, rtol=1e-5, atol=0)
+    (3.0 * l).backward()
+    (3.0 * l_ref).backward()
+    torch.testing.assert_close(a.grad, a2.grad, rtol=1e-6, atol=0)
+    torch.testing.assert_close(b.grad, b2.grad, rtol=1e-6, atol=0)
+    lv = l1_view_loss(a.detach(), b.detach(), 8)
+    torch.testing.assert_close(lv, l_ref.detach() / 8, rtol=1e-5, atol=0)
