@@ -12,16 +12,17 @@ import fdgs
 from fdgs import _lib as L
 from fdgs.render import render as render_fn
 from fdgs.dp import train_iteration
+from fdgs.losses import l1_view_loss as fused_loss
 L.load()
 cfg, args, pc, net, cams, gts_host = bench.build_scene("dynerf", "fdgs", dev, a.views, 0)
 bucket = bench.make_bucket(pc, net, dev)
 bg = torch.ones(3, device=dev)
 gts = [g.to(dev) for g in gts_host]
 for _ in range(3):
-    train_iteration(render_fn, pc, cams, gts, bg, bucket, 0, 1)
+    train_iteration(render_fn, pc, cams, gts, bg, bucket, 0, 1, loss_fn=fused_loss)
 torch.cuda.synchronize()
 with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
-    train_iteration(render_fn, pc, cams, gts, bg, bucket, 0, 1)
+    train_iteration(render_fn, pc, cams, gts, bg, bucket, 0, 1, loss_fn=fused_loss)
     torch.cuda.synchronize()
 evs = [e for e in prof.events() if e.device_type == torch.autograd.DeviceType.CUDA]
 evs.sort(key=lambda e: e.time_range.start)
