@@ -1,0 +1,73 @@
+"""Whole hot path, end to end: one training iteration (deformation -> activations -> rasterize -> L1 -> backward over
+all views, gradient bucket) through fdgs vs. the reference arm (the reference's PyTorch deformation ops,
+oracle/ref_port.py, + the UNMODIFIED reference CUDA rasterizer built into oracle/_ref) on the same seeded scene.
+This is the drop-in claim of INTEGRATION.md checked in one piece: same images, same loss, same gradients for every
+Gaussian parameter, HexPlane plane and MLP weight."""
+import pytest
+import torch
+
+import util
+
+pytestmark = pytest.mark.gpu
+
+
+def _run(impl, cfg_name, views, points, fused_loss):
+    import bench
+    import fdgs  # noqa: F401
+    from fdgs.dp import train_iteration
+    dev = "cuda:0"
+    cfg, args, pc, net, cams, gts_host = bench.build_scene(cfg_name, impl, dev, views, points)
+    bucket = bench.make_bucket(pc, net, dev)
+    bg = torch.ones(3, device=dev)
+    gts = [g.to(dev) for g in gts_host]
+    if impl == "fdgs":
+        from fdgs.render import render as render_fn
+        loss_fn = None
+        if fused_loss:
+            from fdgs.losses import l1_view_loss as loss_fn
+    else:
+        import build_ref
+        import ref_port
+        from fdgs.diff_gaussian_rasterization import GaussianRasterizationSettings as SettingsTuple
+        refC = build_ref.load()
+
+        def render_fn(cam, pc_, bg_color=None, stage="fine"):
+            return ref_port.ref_render(refC, SettingsTuple, cam, pc_, bg_color, stage=stage)
+        loss_fn = None
+    with torch.no_grad():
+        images = [render_fn(c, pc, bg_color=bg, stage="fine")["render"].clone() for c in cams]
+    loss, radii = train_iteration(render_fn, pc, cams, gts, bg, bucket, 0, 1, read_loss=True, loss_fn=loss_fn)
+    grads = {"viewspace": bucket.extra["viewspace"].clone()}
+    for name in ("_xyz", "_scaling", "_rotation", "_opacity", "_features_dc", "_features_rest"):
+        grads[name] = getattr(pc, name).grad.clone()
+    for k, p in net.named_parameters():
+        if p.grad is not None:
+            grads["net." + k] = p.grad.clone()
+    return images, loss, radii.clone(), grads
+
+
+@pytest.mark.parametrize("cfg_name,views,points", [("tiny", 2, 0), ("dnerf50k", 2, 20000)])
+def test_train_iteration_matches_reference_arm(cfg_name, views, points):
+    import build_ref
+    if not build_ref.available():
+        pytest.skip("oracle/_ref (reference rasterizer built from /root/reference) is not in this snapshot")
+    img_r, loss_r, radii_r, g_r = _run("reference", cfg_name, views, points, False)
+    img_f, loss_f, radii_f, g_f = _run("fdgs", cfg_name, views, points, True)
+    assert torch.equal(radii_f, radii_r)
+    for a, b in zip(img_f, img_r):
+        # images: 1e-5 bar + 1 ulp of the fused activations.  A Gaussian whose alpha sits within an ulp of the 1/255 skip
+        # threshold may be taken on one side and skipped on the other (libm-level differences upstream): a handful of
+        # pixels may then differ by up to 1/255 of a colour.
+        d = (a - b).abs() / b.abs().max()
+        assert int((d > 2e-5).sum()) <= max(4, a.numel() // 20000), float(d.max())
+        assert float(d.max()) < 5e-3
+    assert abs(loss_f - loss_r) <= 2e-6 * abs(loss_r)
+    assert set(g_f) == set(g_r)
+    for k in sorted(g_r):
+        # float-atomic sums on both sides (the reference's own run-to-run spread is ~1e-5 of the largest entry); the
+        # few Gaussians whose alpha flips across the 1/255 threshold (see above) carry a different gradient on the two
+        # sides, so the bar is: all but a handful of entries within 2e-4 of the largest, and 2e-3 in the L2 sense
+        a, b = g_f[k].double(), g_r[k].double()
+        d = (a - b).abs() / (b.abs().max() + 1e-30)
+        assert int((d > 2e-4).sum()) <= max(8, a.numel() // 2000), (k, float(d.max()))
+        assert float((a - b).norm() / (b.norm() + 1e-30)) < 2e-3, k
