@@ -142,7 +142,7 @@ static inline SmemPlan make_smem_plan(const Layout& lo) {
     s.off_b0 = o; o += al(Wn);
     s.off_b1 = o; o += al(FDGS_NUM_HEADS * Wn);
     s.off_b2 = o; o += al(64);
-    s.off_out = o; o += al(48 * 128);          // output staging [row][out]
+    s.off_out = o; o += al(52 * 128);          // output staging [row][out], row stride 52 for the 48-wide head
     s.off_bars = o; o += 256;
     s.off_ring = o;
     const int slot_floats = 32 * Wn;
@@ -399,6 +399,7 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
             for (int i = 0; i < plan.nheads; ++i) {
                 const int h = plan.heads[i];
                 const int NO = head_out(h);
+                const int OS = NO == 48 ? 52 : NO;                      // staging row stride
                 // base values (the head's input rows of this tile, contiguous) are fetched now: their DRAM latency hides
                 // behind the two GEMMs.  Thread t owns float4s t, t + 256, ... of the tile's rows * NO floats.
                 float* outp = h == 0 ? io.o_xyz : h == 1 ? io.o_scales : h == 2 ? io.o_rot : h == 3 ? io.o_opacity : io.o_shs;
@@ -466,6 +467,7 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
                 PT(5)
                 {
                     const int npt = plan.nop[i] >> 1;                 // output columns per thread: 8 or 24
+                    // (row stride OS: 48 floats would put a warp's 32 rows on two banks, 52 spreads them over eight)
                     for (int c0 = 0; c0 < npt; c0 += 8) {
                         uint32_t v[8];
                         tmem_ld8(acc + hf * npt + c0, v);
@@ -473,7 +475,7 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
 #pragma unroll
                         for (int j = 0; j < 8; ++j) {
                             const int n = hf * npt + c0 + j;
-                            if (n < NO) OUTs[row * NO + n] = __uint_as_float(v[j]) + B2s[b2_row0(h) + n];
+                            if (n < NO) OUTs[row * OS + n] = __uint_as_float(v[j]) + B2s[b2_row0(h) + n];
                         }
                     }
                 }
@@ -490,20 +492,20 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
                         for (int k = 0; k < 6; ++k) {
                             const int i4 = tid + k * NEPI;
                             if (i4 * 4 < total) {
-                                const float4 d = o4[i4];
+                                const float4 d = NO == 48 ? o4[(i4 / 12) * 13 + (i4 % 12)] : o4[i4];
                                 dst4[i4] = make_float4(base[k].x + d.x, base[k].y + d.y, base[k].z + d.z, base[k].w + d.w);
                             }
                         }
                     } else if (h == 4 && io.sh_coeffs != 16) {        // M = 1 broadcast: base index (p, n % 3)
                         for (int idx = tid; idx < total; idx += NEPI) {
                             const int r = idx / NO, n = idx % NO;
-                            dst[idx] = inp[(size_t)(p0 + r) * io.sh_coeffs * 3 + (n % 3)] + OUTs[idx];
+                            dst[idx] = inp[(size_t)(p0 + r) * io.sh_coeffs * 3 + (n % 3)] + OUTs[r * OS + n];
                         }
                     } else if (nobase) {
-                        for (int idx = tid; idx < total; idx += NEPI) dst[idx] = OUTs[idx];
+                        for (int idx = tid; idx < total; idx += NEPI) dst[idx] = OUTs[(idx / NO) * OS + idx % NO];
                     } else {
                         const float* src = inp + (size_t)p0 * NO;
-                        for (int idx = tid; idx < total; idx += NEPI) dst[idx] = src[idx] + OUTs[idx];
+                        for (int idx = tid; idx < total; idx += NEPI) dst[idx] = src[idx] + OUTs[(idx / NO) * OS + idx % NO];
                     }
                 }
                 epi_bar();                                            // staging buffer free for the next head
