@@ -5,6 +5,7 @@
 // Replaces CudaRasterizer::Rasterizer::forward
 // (RAST/cuda_rasterizer/rasterizer_impl.cu:198-339, forward.cu:155-379).
 #include "raster_math.cuh"
+#include <cstdint>
 #include <cstdio>
 #include "prof.cuh"
 
@@ -55,11 +56,29 @@ k_preprocess(int P, int D, int M,
              const float* __restrict__ campos,
              int W, int H, float tanfovx, float tanfovy, float focal_x, float focal_y,
              int gx, int gy, int prefiltered,
-             int* __restrict__ radii, FdgsGeom g, uint32_t* __restrict__ tile_count)
+             int* __restrict__ radii, FdgsGeom g, uint32_t* __restrict__ tile_count, int sh_staged)
 {
     __shared__ float sV[16], sPm[16], sCam[3];
+    extern __shared__ float s_sh[];              // [256][SH_STRIDE] when the SH block is staged (sh_staged)
     if (threadIdx.x < 16) { sV[threadIdx.x] = viewmatrix[threadIdx.x]; sPm[threadIdx.x] = projmatrix[threadIdx.x]; }
     if (threadIdx.x < 3) sCam[threadIdx.x] = campos[threadIdx.x];
+    // A thread's 3M SH floats are contiguous, so thread-per-Gaussian loads touch 32 different lines per instruction.
+    // Stage the CTA's [256][3M] block with coalesced float4 loads instead (row stride 3M + 1: conflict-free reads).
+    if (sh_staged) {
+        const int rowf = 3 * M;
+        const long long base = (long long)blockIdx.x * blockDim.x * rowf;
+        const long long avail = (long long)P * rowf - base;
+        const int n = (int)(avail < (long long)blockDim.x * rowf ? avail : (long long)blockDim.x * rowf);
+        const float4* src = reinterpret_cast<const float4*>(shs + base);          // base is a multiple of 4 floats
+        for (int i = threadIdx.x; i * 4 < n; i += blockDim.x) {
+            const float4 v = src[i];                                              // n is a multiple of 4 (rowf = 48)
+            const int e = i * 4;
+            s_sh[(e / rowf) * (rowf + 1) + e % rowf] = v.x;
+            s_sh[((e + 1) / rowf) * (rowf + 1) + (e + 1) % rowf] = v.y;
+            s_sh[((e + 2) / rowf) * (rowf + 1) + (e + 2) % rowf] = v.z;
+            s_sh[((e + 3) / rowf) * (rowf + 1) + (e + 3) % rowf] = v.w;
+        }
+    }
     __syncthreads();
 
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
@@ -109,7 +128,7 @@ k_preprocess(int P, int D, int M,
                         float3 dir = make_float3(p.x - sCam[0], p.y - sCam[1], p.z - sCam[2]);
                         const float len = sqrtf(dir.x * dir.x + dir.y * dir.y + dir.z * dir.z);
                         dir.x = dir.x / len; dir.y = dir.y / len; dir.z = dir.z / len;
-                        const float* sh = shs + (size_t)idx * M * 3;
+                        const float* sh = sh_staged ? s_sh + threadIdx.x * (3 * M + 1) : shs + (size_t)idx * M * 3;
                         float rgb[3];
                         uint8_t clampbits = 0;
 #pragma unroll
@@ -520,11 +539,14 @@ int fdgs_raster_forward_plan(const FdgsRasterForward* a, void* stream_) {
     const float focal_x = a->W / (2.0f * a->tanfovx);
     // tile_count, tile_cursor, tile_start, scalars are contiguous: one memset
     FDGS_CUDA(cudaMemsetAsync(im.tile_count, 0, (size_t)((char*)im.scalars - (char*)im.tile_count) + 32, stream));
+    const int sh_staged = (a->shs && !a->colors_precomp && a->M == 16 && ((uintptr_t)a->shs & 15) == 0) ? 1 : 0;
+    const size_t sh_smem = sh_staged ? (size_t)256 * (3 * a->M + 1) * sizeof(float) : 0;
+    if (sh_staged) FDGS_CUDA(cudaFuncSetAttribute(k_preprocess, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh_smem));
     { FDGS_PROF("k_preprocess", stream);
-    k_preprocess<<<(a->P + 255) / 256, 256, 0, stream>>>(
+    k_preprocess<<<(a->P + 255) / 256, 256, sh_smem, stream>>>(
         a->P, a->D, a->M, a->means3D, a->scales, a->scale_modifier, a->rotations, a->opacities, a->shs,
         a->cov3D_precomp, a->colors_precomp, a->viewmatrix, a->projmatrix, a->campos, a->W, a->H,
-        a->tanfovx, a->tanfovy, focal_x, focal_y, gx, gy, a->prefiltered, a->radii, g, im.tile_count);
+        a->tanfovx, a->tanfovy, focal_x, focal_y, gx, gy, a->prefiltered, a->radii, g, im.tile_count, sh_staged);
     }
     FDGS_LAUNCH_CHECK(a->debug, stream);
     { FDGS_PROF("k_tile_scan", stream);
