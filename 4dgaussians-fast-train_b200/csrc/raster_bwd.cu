@@ -297,32 +297,28 @@ __device__ __forceinline__ float3 normalize_vjp(float3 v, float3 dv) {
     return r;
 }
 
-// Fused K9 + K10 (backward.cu:144-274 and :346-396).
-__global__ void __launch_bounds__(256)
-k_preprocess_bwd(int P, int D, int M, const float* __restrict__ means3D, const int* __restrict__ radii,
-                 const float* __restrict__ shs, const uint8_t* __restrict__ clamped,
-                 const float* __restrict__ scales, const float* __restrict__ rotations, float scale_modifier,
-                 const float* __restrict__ cov3Ds, const float* __restrict__ viewmatrix,
-                 const float* __restrict__ projmatrix, float fx, float fy, float tanfovx, float tanfovy,
-                 const float* __restrict__ campos,
-                 const float* __restrict__ dL_dmean2D, const float* __restrict__ dL_dconic,
-                 const float* __restrict__ dL_dcolor,
-                 float* __restrict__ dL_dmeans3D, float* __restrict__ dL_dcov3D, float* __restrict__ dL_dsh,
-                 float* __restrict__ dL_dscales, float* __restrict__ dL_drots, int write_cov_grad_only)
+// Fused K9 + K10 (backward.cu:144-274 and :346-396): one Gaussian.  sh_row != nullptr: shared-memory row holding the SH
+// coefficients on entry and their gradient on return (see k_preprocess_bwd).
+__device__ __forceinline__ void
+preprocess_bwd_one(int idx, int D, int M, const float* __restrict__ means3D, const int* __restrict__ radii,
+                   const float* __restrict__ shs, const uint8_t* __restrict__ clamped,
+                   const float* __restrict__ scales, const float* __restrict__ rotations, float scale_modifier,
+                   const float* __restrict__ cov3Ds, const float* V, const float* Pm, const float* cam,
+                   float fx, float fy, float tanfovx, float tanfovy,
+                   const float* __restrict__ dL_dmean2D, const float* __restrict__ dL_dconic,
+                   const float* __restrict__ dL_dcolor,
+                   float* __restrict__ dL_dmeans3D, float* __restrict__ dL_dcov3D, float* __restrict__ dL_dsh,
+                   float* __restrict__ dL_dscales, float* __restrict__ dL_drots, float* sh_row)
 {
-    __shared__ float V[16], Pm[16], cam[3];
-    if (threadIdx.x < 16) { V[threadIdx.x] = viewmatrix[threadIdx.x]; Pm[threadIdx.x] = projmatrix[threadIdx.x]; }
-    if (threadIdx.x < 3) cam[threadIdx.x] = campos[threadIdx.x];
-    __syncthreads();
-    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= P) return;
     const size_t i3 = 3 * (size_t)idx;
 
     if (!(radii[idx] > 0)) {      // invisible: the reference leaves its zero-initialised outputs untouched
         dL_dmeans3D[i3] = 0.f; dL_dmeans3D[i3 + 1] = 0.f; dL_dmeans3D[i3 + 2] = 0.f;
 #pragma unroll
         for (int k = 0; k < 6; ++k) dL_dcov3D[6 * (size_t)idx + k] = 0.f;
-        if (dL_dsh) {
+        if (sh_row) {
+            for (int k = 0; k < M * 3; ++k) sh_row[k] = 0.f;       // staged: the CTA writes the rows out together
+        } else if (dL_dsh) {
             float4* d4 = reinterpret_cast<float4*>(dL_dsh + (size_t)idx * M * 3);
             if ((M * 3) % 4 == 0 && ((uintptr_t)d4 % 16) == 0) {
                 for (int k = 0; k < (M * 3) / 4; ++k) d4[k] = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -411,8 +407,9 @@ k_preprocess_bwd(int P, int D, int M, const float* __restrict__ means3D, const i
         float g[3];
 #pragma unroll
         for (int ch = 0; ch < 3; ++ch) g[ch] = ((cl >> ch) & 1) ? 0.f : dL_dcolor[i3 + ch];
-        const float* sh = shs + (size_t)idx * M * 3;
-        float* dsh = dL_dsh + (size_t)idx * M * 3;
+        // staged: the row holds this Gaussian's SH coefficients and is overwritten in place by their gradient
+        const float* sh = sh_row ? sh_row : shs + (size_t)idx * M * 3;
+        float* dsh = sh_row ? sh_row : dL_dsh + (size_t)idx * M * 3;
         // basis values and their x/y/z derivatives for the active degree
         float bas[16], bx[16], by[16], bz[16];
 #pragma unroll
@@ -511,7 +508,57 @@ k_preprocess_bwd(int P, int D, int M, const float* __restrict__ means3D, const i
         dL_dscales[i3] = 0.f; dL_dscales[i3 + 1] = 0.f; dL_dscales[i3 + 2] = 0.f;
         reinterpret_cast<float4*>(dL_drots)[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
     }
-    (void)write_cov_grad_only;
+}
+
+// Thread per Gaussian.  A thread's 3M SH floats (read) and their gradient (written) are contiguous, so thread-per-Gaussian
+// accesses touch 32 different lines per instruction: with sh_staged the CTA's [256][3M] block goes through shared memory
+// (row stride 3M + 1) with coalesced float4 loads and stores, the gradient overwriting the coefficients in place.
+__global__ void __launch_bounds__(256)
+k_preprocess_bwd(int P, int D, int M, const float* __restrict__ means3D, const int* __restrict__ radii,
+                 const float* __restrict__ shs, const uint8_t* __restrict__ clamped,
+                 const float* __restrict__ scales, const float* __restrict__ rotations, float scale_modifier,
+                 const float* __restrict__ cov3Ds, const float* __restrict__ viewmatrix,
+                 const float* __restrict__ projmatrix, float fx, float fy, float tanfovx, float tanfovy,
+                 const float* __restrict__ campos,
+                 const float* __restrict__ dL_dmean2D, const float* __restrict__ dL_dconic,
+                 const float* __restrict__ dL_dcolor,
+                 float* __restrict__ dL_dmeans3D, float* __restrict__ dL_dcov3D, float* __restrict__ dL_dsh,
+                 float* __restrict__ dL_dscales, float* __restrict__ dL_drots, int sh_staged)
+{
+    __shared__ float V[16], Pm[16], cam[3];
+    extern __shared__ float s_sh[];
+    if (threadIdx.x < 16) { V[threadIdx.x] = viewmatrix[threadIdx.x]; Pm[threadIdx.x] = projmatrix[threadIdx.x]; }
+    if (threadIdx.x < 3) cam[threadIdx.x] = campos[threadIdx.x];
+    const int rowf = 3 * M;
+    const long long base = (long long)blockIdx.x * blockDim.x * rowf;
+    const long long avail = (long long)P * rowf - base;
+    const int n = (int)(avail < (long long)blockDim.x * rowf ? avail : (long long)blockDim.x * rowf);
+    if (sh_staged) {
+        const float4* src = reinterpret_cast<const float4*>(shs + base);
+        for (int i = threadIdx.x; i * 4 < n; i += blockDim.x) {
+            const float4 v = src[i];
+            const int e = i * 4;
+            s_sh[(e / rowf) * (rowf + 1) + e % rowf] = v.x;
+            s_sh[((e + 1) / rowf) * (rowf + 1) + (e + 1) % rowf] = v.y;
+            s_sh[((e + 2) / rowf) * (rowf + 1) + (e + 2) % rowf] = v.z;
+            s_sh[((e + 3) / rowf) * (rowf + 1) + (e + 3) % rowf] = v.w;
+        }
+    }
+    __syncthreads();
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx < P)
+        preprocess_bwd_one(idx, D, M, means3D, radii, shs, clamped, scales, rotations, scale_modifier, cov3Ds, V, Pm, cam, fx, fy,
+                           tanfovx, tanfovy, dL_dmean2D, dL_dconic, dL_dcolor, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drots,
+                           sh_staged ? s_sh + threadIdx.x * (rowf + 1) : nullptr);
+    if (sh_staged) {
+        __syncthreads();
+        float4* dst = reinterpret_cast<float4*>(dL_dsh + base);
+        for (int i = threadIdx.x; i * 4 < n; i += blockDim.x) {
+            const int e = i * 4;
+            dst[i] = make_float4(s_sh[(e / rowf) * (rowf + 1) + e % rowf], s_sh[((e + 1) / rowf) * (rowf + 1) + (e + 1) % rowf],
+                                 s_sh[((e + 2) / rowf) * (rowf + 1) + (e + 2) % rowf], s_sh[((e + 3) / rowf) * (rowf + 1) + (e + 3) % rowf]);
+        }
+    }
 }
 
 }  // namespace
@@ -547,11 +594,14 @@ extern "C" int fdgs_raster_backward(const FdgsRasterBackward* a, void* stream_) 
         FDGS_LAUNCH_CHECK(a->debug, stream);
     }
     const float* cov3D_ptr = a->cov3D_precomp ? a->cov3D_precomp : g.cov3D;
+    const int sh_staged = (a->shs && a->dL_dsh && a->M == 16 && (((uintptr_t)a->shs | (uintptr_t)a->dL_dsh) & 15) == 0) ? 1 : 0;
+    const size_t sh_smem = sh_staged ? (size_t)256 * (3 * a->M + 1) * sizeof(float) : 0;
+    if (sh_staged) FDGS_CUDA(cudaFuncSetAttribute(k_preprocess_bwd, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh_smem));
     { FDGS_PROF("k_preprocess_bwd", stream);
-    k_preprocess_bwd<<<(P + 255) / 256, 256, 0, stream>>>(
+    k_preprocess_bwd<<<(P + 255) / 256, 256, sh_smem, stream>>>(
         P, a->D, a->M, a->means3D, a->radii, a->shs, g.clamped, a->scales, a->rotations, a->scale_modifier, cov3D_ptr,
         a->viewmatrix, a->projmatrix, focal_x, focal_y, a->tanfovx, a->tanfovy, a->campos, a->dL_dmeans2D, a->dL_dconic,
-        a->dL_dcolors, a->dL_dmeans3D, a->dL_dcov3D, a->dL_dsh, a->dL_dscales, a->dL_drots, 0);
+        a->dL_dcolors, a->dL_dmeans3D, a->dL_dcov3D, a->dL_dsh, a->dL_dscales, a->dL_drots, sh_staged);
     }
     FDGS_LAUNCH_CHECK(a->debug, stream);
     return FDGS_OK;
