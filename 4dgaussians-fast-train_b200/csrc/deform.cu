@@ -66,30 +66,35 @@ __global__ void k_time_rows(Layout lo, const float* __restrict__ packed, float* 
     }
 }
 
-// d_planes[c][y][x] += packed_grad[y][x][c]                      (spatial planes)
-__global__ void k_unpack_spatial(float* __restrict__ dst /*[C][H][W]*/, const float* __restrict__ g /*[H][W][C]*/,
-                                 int C, int HW) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;      // over C*HW, dst-major
-    if (i >= HW * C) return;
-    const int c = i / HW, p = i % HW;
-    const float v = g[(size_t)p * C + c];
-    if (v != 0.f) dst[i] += v;
-}
-// time planes: only rows y0 and y0+1 receive gradient
-__global__ void k_unpack_time(float* __restrict__ dst /*[C][H][W]*/, const float* __restrict__ gt /*[W][C]*/,
-                              int C, int H, int W, float time_h, const float* __restrict__ time_dev) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;      // over C*W
-    if (i >= C * W) return;
-    const float time = time_dev ? *time_dev : time_h;
-    const int c = i / W, x = i % W;
-    const float iy = unnorm_clip(time, H);
-    const float y0f = floorf(iy);
-    const int y0 = (int)y0f;
-    const float wy0 = (y0f + 1.f) - iy, wy1 = iy - y0f;
-    const float v = gt[(size_t)x * C + c];
-    if (v == 0.f) return;
-    dst[((size_t)c * H + y0) * W + x] += wy0 * v;
-    if (y0 + 1 < H) dst[((size_t)c * H + y0 + 1) * W + x] += wy1 * v;
+// d_planes[c][y][x] += packed_grad[y][x][c] (spatial planes); time planes: only rows y0 and y0+1 receive gradient.
+// All planes of all levels in ONE launch (blockIdx.y = plane): the twelve per-plane launches above are 7-8 us each,
+// i.e. launch latency (the planes are 64 KB - 1 MB).  Same arithmetic as k_unpack_spatial / k_unpack_time.
+struct UnpackPlane { float* dst; const float* src; int H, W, is_time; };
+struct UnpackArgs { UnpackPlane p[FDGS_MAX_LEVELS * 6]; int n, C; float time_h; const float* time_dev; };
+__global__ void __launch_bounds__(256) k_unpack_all(UnpackArgs a) {
+    const UnpackPlane pl = a.p[blockIdx.y];
+    const int C = a.C, H = pl.H, W = pl.W;
+    if (pl.is_time) {
+        const float time = a.time_dev ? *a.time_dev : a.time_h;
+        const float iy = unnorm_clip(time, H);
+        const float y0f = floorf(iy);
+        const int y0 = (int)y0f;
+        const float wy0 = (y0f + 1.f) - iy, wy1 = iy - y0f;
+        for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < C * W; i += gridDim.x * blockDim.x) {
+            const int c = i / W, x = i % W;
+            const float v = pl.src[(size_t)x * C + c];
+            if (v == 0.f) continue;
+            pl.dst[((size_t)c * H + y0) * W + x] += wy0 * v;
+            if (y0 + 1 < H) pl.dst[((size_t)c * H + y0 + 1) * W + x] += wy1 * v;
+        }
+    } else {
+        const int HW = H * W;
+        for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < HW * C; i += gridDim.x * blockDim.x) {
+            const int c = i / HW, q = i % HW;
+            const float v = pl.src[(size_t)q * C + c];
+            if (v != 0.f) pl.dst[i] += v;
+        }
+    }
 }
 
 // ---- shared-memory tile GEMM (FP32 SIMT) ------------------------------------------------------------
@@ -782,23 +787,27 @@ int fdgs_deform_backward(const FdgsDeformBackward* a, void* stream_) {
         }
     }
     FDGS_LAUNCH_CHECK(a->debug, stream);
-    // scatter the packed plane grads back into the reference layout (+=)
-    for (int l = 0; l < lo.L; ++l)
-        for (int k = 0; k < 6; ++k) {
-            if (!a->d_planes[l][k]) return FDGS_E_BADARG;
-            const int W = lo.pw[l][k], H = lo.ph[l][k];
-            if (h_tslot[k] >= 0) {
-                const int n = lo.C * W;
-                { FDGS_PROF("k_unpack_time", stream);
-                k_unpack_time<<<(n + 255) / 256, 256, 0, stream>>>(a->d_planes[l][k], gtrow + lo.toff[l][h_tslot[k]], lo.C, H, W, a->time, a->time_dev);
-                }
-            } else {
-                const int n = lo.C * W * H;
-                { FDGS_PROF("k_unpack_spatial", stream);
-                k_unpack_spatial<<<(n + 255) / 256, 256, 0, stream>>>(a->d_planes[l][k], gpacked + lo.poff[l][k], lo.C, W * H);
-                }
+    // scatter the packed plane grads back into the reference layout (+=): one launch for all planes
+    {
+        UnpackArgs ua;
+        ua.n = 0; ua.C = lo.C; ua.time_h = a->time; ua.time_dev = a->time_dev;
+        int maxel = 0;
+        for (int l = 0; l < lo.L; ++l)
+            for (int k = 0; k < 6; ++k) {
+                if (!a->d_planes[l][k]) return FDGS_E_BADARG;
+                const int W = lo.pw[l][k], H = lo.ph[l][k];
+                UnpackPlane pl;
+                pl.dst = a->d_planes[l][k]; pl.H = H; pl.W = W;
+                if (h_tslot[k] >= 0) { pl.src = gtrow + lo.toff[l][h_tslot[k]]; pl.is_time = 1; if (lo.C * W > maxel) maxel = lo.C * W; }
+                else { pl.src = gpacked + lo.poff[l][k]; pl.is_time = 0; if (lo.C * W * H > maxel) maxel = lo.C * W * H; }
+                ua.p[ua.n++] = pl;
             }
+        int bx = (maxel + 255) / 256;
+        if (bx > 592) bx = 592;                                  // grid-stride loops cover the rest
+        { FDGS_PROF("k_unpack_all", stream);
+        k_unpack_all<<<dim3(bx, ua.n), 256, 0, stream>>>(ua);
         }
+    }
     FDGS_LAUNCH_CHECK(a->debug, stream);
     return FDGS_OK;
 }
