@@ -91,16 +91,48 @@ def l1_view_loss(image, gt, n_views_total):
     return (image - gt).abs().mean() / float(n_views_total)
 
 
-def train_iteration(render_fn, pc, cams, gts, bg, bucket, rank=0, world=1, read_loss=False, loss_fn=None):
+class _SharedFeatures:
+    """Stand-in for `pc` during one iteration: everything is `pc`'s, except that `get_features` hands out ONE
+    [P,16,3] leaf for all of the rank's views instead of a fresh cat(_features_dc, _features_rest) per render()
+    (scene/gaussian_model.py:123-127 cats on every access; the parameters cannot change inside an iteration)."""
+
+    def __init__(self, pc, leaf):
+        object.__setattr__(self, "_pc", pc)
+        object.__setattr__(self, "_leaf", leaf)
+
+    @property
+    def get_features(self):
+        return self._leaf
+
+    def __getattr__(self, name):
+        return getattr(self._pc, name)
+
+    def __setattr__(self, name, value):
+        setattr(self._pc, name, value)
+
+
+def train_iteration(render_fn, pc, cams, gts, bg, bucket, rank=0, world=1, read_loss=False, loss_fn=None,
+                    share_features=True):
     """One fwd+bwd iteration over the batch `cams` (all B views; this rank renders its shard).
     loss_fn(image, gt, B): per-view loss; default = the ATen l1_view_loss above (fdgs.losses.l1_view_loss is the fused one).
+    share_features: concatenate the SH coefficients once per iteration, let the views' SH gradients sum in one [P,16,3]
+    buffer and split it into _features_dc / _features_rest gradients once (same additions, in the same view order, as the
+    reference's per-view cat backward; saves a cat and a strided two-way gradient accumulation per view).
     Returns (local loss sum as a tensor, max radii, visibility) like train.py:229-232 needs."""
     B = len(cams)
     bucket.zero()
     loss_sum = None
     radii_max = None
-    for i in shard_views(B, rank, world):
-        out = render_fn(cams[i], pc, bg_color=bg, stage="fine")
+    mine = shard_views(B, rank, world)
+    feats = leaf = None
+    pc_it = pc
+    if share_features and len(mine) > 1 and isinstance(getattr(type(pc), "get_features", None), property):
+        feats = pc.get_features
+        if feats.requires_grad:
+            leaf = feats.detach().requires_grad_(True)
+            pc_it = _SharedFeatures(pc, leaf)
+    for i in mine:
+        out = render_fn(cams[i], pc_it, bg_color=bg, stage="fine")
         loss = (loss_fn or l1_view_loss)(out["render"], gts[i], B)
         loss.backward()
         vs = out["viewspace_points"].grad
@@ -108,6 +140,8 @@ def train_iteration(render_fn, pc, cams, gts, bg, bucket, rank=0, world=1, read_
             bucket.extra["viewspace"].add_(vs)
         loss_sum = loss.detach() if loss_sum is None else loss_sum + loss.detach()
         radii_max = out["radii"] if radii_max is None else torch.maximum(radii_max, out["radii"])
+    if leaf is not None and leaf.grad is not None:
+        feats.backward(leaf.grad)
     bucket.all_reduce()
     if read_loss and loss_sum is not None:
         return float(loss_sum), radii_max

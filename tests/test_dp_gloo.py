@@ -115,3 +115,45 @@ def test_world2_gloo_matches_single_process(B):
         assert nbytes == 4 * (128 + 64 + 128)      # 111 -> 128, 5 -> 64, 111 -> 128 floats
     assert torch.equal(res[0][4], res[1][4])       # the view-space accumulator is reduced too
     assert float(res[0][4].abs().sum()) > 0
+
+
+class _PCFeat(_PC):
+    """_PC plus the reference's split SH storage: get_features cats on every access (scene/gaussian_model.py:123-127)."""
+
+    def __init__(self):
+        super().__init__()
+        g = torch.Generator().manual_seed(5)
+        self._features_dc = torch.nn.Parameter(torch.randn(37, 1, 3, generator=g))
+        self._features_rest = torch.nn.Parameter(torch.randn(37, 15, 3, generator=g))
+        self.cats = 0
+
+    @property
+    def get_features(self):
+        self.cats += 1
+        return torch.cat((self._features_dc, self._features_rest), dim=1)
+
+
+def _render_feat(cam, pc, bg_color=None, stage="fine"):
+    out = _render(cam, pc, bg_color, stage)
+    w = torch.linspace(0.1, 1.0, 16)[None, :, None] * cam
+    out["render"] = out["render"] + (pc.get_features * w).sum((0, 1))[:, None, None]
+    return out
+
+
+@pytest.mark.parametrize("B", [1, 4])
+def test_shared_features_gradients_equal_per_view_cat(B):
+    cams, gts = _batch(B)
+    res = []
+    for share in (False, True):
+        pc = _PCFeat()
+        bucket = dp.GradBucket(pc.parameters(), extra={"viewspace": (37, 3)}, device="cpu")
+        loss, _ = dp.train_iteration(_render_feat, pc, cams, gts, torch.ones(3), bucket, share_features=share)
+        slot = {id(p): v for p, v in zip(bucket.params, bucket.views)}
+        assert pc._features_dc.grad.data_ptr() == slot[id(pc._features_dc)].data_ptr()
+        assert pc._features_rest.grad.data_ptr() == slot[id(pc._features_rest)].data_ptr()
+        res.append((float(loss), pc.cats, [p.grad.clone() for p in bucket.params]))
+    assert res[0][1] == B and res[1][1] == 1          # one cat per view vs one per iteration
+    assert res[0][0] == res[1][0]
+    for g0, g1 in zip(res[0][2], res[1][2]):
+        assert torch.equal(g0, g1)                    # same additions in the same order: bit-identical
+    assert pc._features_rest.grad.abs().sum() > 0
