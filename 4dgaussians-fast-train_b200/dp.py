@@ -91,6 +91,40 @@ def l1_view_loss(image, gt, n_views_total):
     return (image - gt).abs().mean() / float(n_views_total)
 
 
+class ViewStager:
+    """Host -> device staging of a batch's ground-truth images for train_iteration (the reference's loop does
+    `viewpoint_cam.original_image.cuda()` per view on the compute stream, train.py:222-226).
+
+    The images are copied from pinned host memory into persistent device buffers on a separate copy stream, one event per
+    view; `stager[i]` (what train_iteration's `gts[i]` evaluates) makes the current stream wait for view i's copy only, so
+    the upload of view i+1 runs under the kernels of view i instead of in front of them."""
+
+    def __init__(self, like, device):
+        self.stream = torch.cuda.Stream(device=device)
+        self.buf = [None if t is None else torch.empty(t.shape, dtype=t.dtype, device=device) for t in like]
+        self.events = [None if t is None else torch.cuda.Event() for t in like]
+        self.nbytes = 0
+
+    def upload(self, host, views):
+        """Queues this step's copies (views: the indices this rank renders).  The copies start once everything already
+        queued on the current stream - i.e. the previous step's reads of the buffers - has finished."""
+        self.stream.wait_stream(torch.cuda.current_stream())
+        self.nbytes = 0
+        with torch.cuda.stream(self.stream):
+            for i in views:
+                self.buf[i].copy_(host[i], non_blocking=True)
+                self.events[i].record(self.stream)
+                self.nbytes += host[i].numel() * host[i].element_size()
+        return self
+
+    def __len__(self):
+        return len(self.buf)
+
+    def __getitem__(self, i):
+        torch.cuda.current_stream().wait_event(self.events[i])
+        return self.buf[i]
+
+
 class _SharedFeatures:
     """Stand-in for `pc` during one iteration: everything is `pc`'s, except that `get_features` hands out ONE
     [P,16,3] leaf for all of the rank's views instead of a fresh cat(_features_dc, _features_rest) per render()

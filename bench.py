@@ -283,6 +283,11 @@ def main():
     use_dist = world > 1 and a.impl == "fdgs"
     if use_dist:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        # NCCL writes its version banner to file descriptor 1: keep stdout to the ONE JSON line
+        sys.stdout.flush()
+        json_fd = os.dup(1)
+        os.dup2(2, 1)
+        sys.stdout = os.fdopen(json_fd, "w")
         dist.init_process_group("nccl", device_id=torch.device(dev))
     eff_world, eff_rank = (world, rank) if use_dist else (1, 0)
 
@@ -325,15 +330,17 @@ def main():
     def step_resident():
         train_iteration(render_fn, pc, cams, gts_dev, bg, bucket, eff_rank, eff_world, loss_fn=fused_loss)
 
-    stage_gt = [None] * B
+    from fdgs.dp import ViewStager
+    stager = ViewStager([gts_host[i] if i in mine else None for i in range(B)], dev)
 
     def step_e2e():
-        # host -> device: this step's GT images and camera tensors (pinned), device -> host: the loss
+        # host -> device: this step's GT images (pinned -> device on the stager's copy stream, one event per view, so the
+        # copy of view i+1 runs under the kernels of view i) and camera tensors; device -> host: the loss
         cs = list(cams)
+        stager.upload(gts_host, mine)
         for i in mine:
-            stage_gt[i] = gts_host[i].to(dev, non_blocking=True)
             cs[i] = upload_camera(cams[i], cams_host[i], dev)
-        loss, _ = train_iteration(render_fn, pc, cs, stage_gt, bg, bucket, eff_rank, eff_world, read_loss=True, loss_fn=fused_loss)
+        loss, _ = train_iteration(render_fn, pc, cs, stager, bg, bucket, eff_rank, eff_world, read_loss=True, loss_fn=fused_loss)
         return loss
 
     def timed(fn, steps):

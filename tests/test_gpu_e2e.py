@@ -71,3 +71,34 @@ def test_train_iteration_matches_reference_arm(cfg_name, views, points):
         d = (a - b).abs() / (b.abs().max() + 1e-30)
         assert int((d > 2e-4).sum()) <= max(8, a.numel() // 2000), (k, float(d.max()))
         assert float((a - b).norm() / (b.norm() + 1e-30)) < 2e-3, k
+
+
+def test_view_stager_and_shared_features_change_nothing():
+    """fdgs.dp.ViewStager (GT images uploaded on a copy stream, one event per view) and the once-per-iteration SH cat are
+    scheduling changes only: same loss and SH gradients as device-resident targets / a cat per view (up to the run-to-run
+    spread of the float atomics in the loss reduction and the blend backward)."""
+    import bench
+    import fdgs  # noqa: F401
+    from fdgs.dp import train_iteration, ViewStager
+    from fdgs.render import render as render_fn
+    from fdgs.losses import l1_view_loss as loss_fn
+    dev = "cuda:0"
+    cfg, args, pc, net, cams, gts_host = bench.build_scene("tiny", "fdgs", dev, 3, 0)
+    bucket = bench.make_bucket(pc, net, dev)
+    bg = torch.ones(3, device=dev)
+    gts = [g.to(dev) for g in gts_host]
+    res = []
+    for targets, share in ((gts, False), (gts, True), ("stager", True)):
+        if targets == "stager":
+            targets = ViewStager(gts_host, dev).upload(gts_host, range(len(gts_host)))
+            assert targets.nbytes == sum(g.numel() * 4 for g in gts_host)
+            for i, g in enumerate(gts):
+                assert torch.equal(targets[i], g)
+        loss, _ = train_iteration(render_fn, pc, cams, targets, bg, bucket, 0, 1, read_loss=True, loss_fn=loss_fn,
+                                  share_features=share)
+        res.append((loss, pc._features_dc.grad.clone(), pc._features_rest.grad.clone()))
+    assert float(res[0][1].abs().sum()) > 0 and float(res[0][2].abs().sum()) > 0
+    for r in res[1:]:
+        assert abs(r[0] - res[0][0]) <= 1e-6 * abs(res[0][0])
+        for a, b in ((r[1], res[0][1]), (r[2], res[0][2])):
+            assert float((a - b).abs().max()) <= 1e-4 * float(b.abs().max())
