@@ -327,8 +327,10 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    overlap_sh = os.environ.get("FDGS_OVERLAP_SH", "0") != "0"    # A/B switch for the early SH all-reduce (N > 1)
+
     def step_resident():
-        train_iteration(render_fn, pc, cams, gts_dev, bg, bucket, eff_rank, eff_world, loss_fn=fused_loss)
+        train_iteration(render_fn, pc, cams, gts_dev, bg, bucket, eff_rank, eff_world, loss_fn=fused_loss, overlap_sh=overlap_sh)
 
     from fdgs.dp import ViewStager
     stager = ViewStager([gts_host[i] if i in mine else None for i in range(B)], dev)
@@ -340,7 +342,8 @@ def main():
         stager.upload(gts_host, mine)
         for i in mine:
             cs[i] = upload_camera(cams[i], cams_host[i], dev)
-        loss, _ = train_iteration(render_fn, pc, cs, stager, bg, bucket, eff_rank, eff_world, read_loss=True, loss_fn=fused_loss)
+        loss, _ = train_iteration(render_fn, pc, cs, stager, bg, bucket, eff_rank, eff_world, read_loss=True, loss_fn=fused_loss,
+                                  overlap_sh=overlap_sh)
         return loss
 
     def timed(fn, steps):

@@ -157,3 +157,47 @@ def test_shared_features_gradients_equal_per_view_cat(B):
     for g0, g1 in zip(res[0][2], res[1][2]):
         assert torch.equal(g0, g1)                    # same additions in the same order: bit-identical
     assert pc._features_rest.grad.abs().sum() > 0
+
+
+def _worker_feat(rank, world, port, B, overlap, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        pc = _PCFeat()
+        bucket = dp.GradBucket(pc.parameters(), extra={"viewspace": (37, 3)}, device="cpu")
+        assert bucket.span([pc._features_dc, pc._features_rest]) is not None
+        assert bucket.span([pc._features_rest, pc._features_dc]) is None
+        calls = []
+        orig = bucket.all_reduce_range
+        bucket.all_reduce_range = lambda lo, hi, **kw: (calls.append((lo, hi, kw.get("async_op", False))), orig(lo, hi, **kw))[1]
+        cams, gts = _batch(B)
+        dp.train_iteration(_render_feat, pc, cams, gts, torch.ones(3), bucket, rank=rank, world=world, overlap_sh=overlap)
+        q.put((rank, bucket.flat.clone(), calls))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("B", [4, 2])            # 2 views per rank: shared SH leaf; 1 view per rank: per-parameter hooks
+def test_world2_early_sh_all_reduce_equals_single_collective(B):
+    ctx = mp.get_context("spawn")
+    flats = {}
+    for overlap in (False, True):
+        q = ctx.Queue()
+        port = _free_port()
+        procs = [ctx.Process(target=_worker_feat, args=(r, 2, port, B, overlap, q)) for r in range(2)]
+        for p in procs:
+            p.start()
+        res = [q.get(timeout=120) for _ in procs]
+        for p in procs:
+            p.join(timeout=60)
+            assert p.exitcode == 0
+        assert torch.equal(res[0][1], res[1][1])
+        flats[overlap] = res[0][1]
+        if overlap:
+            calls = res[0][2]
+            assert len(calls) == 3 and calls[0][2] is True        # SH span first and asynchronous, then the two remainders
+            assert calls[1][0] == 0 and calls[1][1] == calls[0][0] and calls[2][0] == calls[0][1]
+        else:
+            assert res[0][2] == []
+    assert torch.equal(flats[False], flats[True])                 # two-rank sums: order-independent, bit-identical
+    assert float(flats[True].abs().sum()) > 0
