@@ -125,22 +125,36 @@ class ViewStager:
         self.nbytes = 0
 
     def upload(self, host, views):
-        """Queues this step's copies (views: the indices this rank renders).  The copies start once everything already
-        queued on the current stream - i.e. the previous step's reads of the buffers - has finished."""
+        """Starts this step's copies (views: the indices this rank renders, in render order).  Only the first view's copy is
+        queued here; view k+1's is queued when view k's image is fetched, so that the step's first kernels are not held up
+        behind the host work of issuing every copy.  Copies start once everything already queued on the current stream -
+        i.e. the previous step's reads of the buffers - has finished."""
         self.stream.wait_stream(torch.cuda.current_stream())
         self.nbytes = 0
-        with torch.cuda.stream(self.stream):
-            for i in views:
-                self.buf[i].copy_(host[i], non_blocking=True)
-                self.events[i].record(self.stream)
-                self.nbytes += host[i].numel() * host[i].element_size()
+        self._host = host
+        self._pending = list(views)
+        self._issued = set()
+        self._issue_next()
         return self
+
+    def _issue_next(self):
+        if not self._pending:
+            return
+        i = self._pending.pop(0)
+        with torch.cuda.stream(self.stream):
+            self.buf[i].copy_(self._host[i], non_blocking=True)
+            self.events[i].record(self.stream)
+        self._issued.add(i)
+        self.nbytes += self._host[i].numel() * self._host[i].element_size()
 
     def __len__(self):
         return len(self.buf)
 
     def __getitem__(self, i):
+        while i not in self._issued and self._pending:       # out-of-order access: issue up to and including view i
+            self._issue_next()
         torch.cuda.current_stream().wait_event(self.events[i])
+        self._issue_next()
         return self.buf[i]
 
 

@@ -335,15 +335,22 @@ def main():
     from fdgs.dp import ViewStager
     stager = ViewStager([gts_host[i] if i in mine else None for i in range(B)], dev)
 
+    class StepCameras:
+        """This step's cameras: view i's matrices are uploaded (pinned -> device) when train_iteration reaches view i."""
+
+        def __len__(self):
+            return len(cams)
+
+        def __getitem__(self, i):
+            return upload_camera(cams[i], cams_host[i], dev)
+
     def step_e2e():
         # host -> device: this step's GT images (pinned -> device on the stager's copy stream, one event per view, so the
         # copy of view i+1 runs under the kernels of view i) and camera tensors; device -> host: the loss
-        cs = list(cams)
         stager.upload(gts_host, mine)
-        for i in mine:
-            cs[i] = upload_camera(cams[i], cams_host[i], dev)
-        loss, _ = train_iteration(render_fn, pc, cs, stager, bg, bucket, eff_rank, eff_world, read_loss=True, loss_fn=fused_loss,
-                                  overlap_sh=overlap_sh)
+        loss, _ = train_iteration(render_fn, pc, StepCameras(), stager, bg, bucket, eff_rank, eff_world, read_loss=True,
+                                  loss_fn=fused_loss, overlap_sh=overlap_sh)
+        assert stager.nbytes == sum(gts_host[i].numel() * 4 for i in mine)
         return loss
 
     def timed(fn, steps):

@@ -91,9 +91,13 @@ def test_view_stager_and_shared_features_change_nothing():
     for targets, share in ((gts, False), (gts, True), ("stager", True)):
         if targets == "stager":
             targets = ViewStager(gts_host, dev).upload(gts_host, range(len(gts_host)))
-            assert targets.nbytes == sum(g.numel() * 4 for g in gts_host)
+            assert targets.nbytes == gts_host[0].numel() * 4           # the first view's copy is queued by upload() ...
             for i, g in enumerate(gts):
                 assert torch.equal(targets[i], g)
+            assert targets.nbytes == sum(g.numel() * 4 for g in gts_host)   # ... the others as their predecessor is fetched
+            targets.upload(gts_host, range(len(gts_host)))
+            assert torch.equal(targets[2], gts[2]) and torch.equal(targets[0], gts[0])     # out-of-order access
+            targets.upload(gts_host, range(len(gts_host)))
         loss, _ = train_iteration(render_fn, pc, cams, targets, bg, bucket, 0, 1, read_loss=True, loss_fn=loss_fn,
                                   share_features=share)
         res.append((loss, pc._features_dc.grad.clone(), pc._features_rest.grad.clone()))
