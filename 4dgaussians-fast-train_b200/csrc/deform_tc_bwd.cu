@@ -1192,10 +1192,12 @@ k_deform_bwd_weights(WArgs args)
 }
 
 // =====================================================================================================================
-static int sm_count() {
-    static int n = 0;
-    if (!n) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev); if (n <= 0) n = 148; }
-    return n;
+static int sm_count() {          // of the CURRENT device (one process may drive several)
+    static int n[64] = {0};
+    int dev = 0; cudaGetDevice(&dev);
+    if (dev < 0 || dev >= 64) dev = 0;
+    if (!n[dev]) { cudaDeviceGetAttribute(&n[dev], cudaDevAttrMultiProcessorCount, dev); if (n[dev] <= 0) n[dev] = 148; }
+    return n[dev];
 }
 
 bool supported(const Layout& lo) { return tc_supported(lo); }

@@ -587,14 +587,13 @@ int fdgs_raster_forward_render(const FdgsRasterForward* a, int64_t R, void* stre
             k_tile_sort<2048><<<T, 256, 2048 * 8, stream>>>(im.ranges, bn.bucket, g, colors, bn.records, a->keys_out, a->point_list_out);
             }
         } else if (maxc <= 8192) {
-            static bool attr_set8 = false;
-            if (!attr_set8) { FDGS_CUDA(cudaFuncSetAttribute(k_tile_sort<8192>, cudaFuncAttributeMaxDynamicSharedMemorySize, 8192 * 8)); attr_set8 = true; }
+            // function attributes are per device: set unconditionally (one driver call), never cached per process
+            FDGS_CUDA(cudaFuncSetAttribute(k_tile_sort<8192>, cudaFuncAttributeMaxDynamicSharedMemorySize, 8192 * 8));
             { FDGS_PROF("k_tile_sort", stream);
             k_tile_sort<8192><<<T, 256, 8192 * 8, stream>>>(im.ranges, bn.bucket, g, colors, bn.records, a->keys_out, a->point_list_out);
             }
         } else {
-            static bool attr_set28 = false;
-            if (!attr_set28) { FDGS_CUDA(cudaFuncSetAttribute(k_tile_sort<28672>, cudaFuncAttributeMaxDynamicSharedMemorySize, 28672 * 8)); attr_set28 = true; }
+            FDGS_CUDA(cudaFuncSetAttribute(k_tile_sort<28672>, cudaFuncAttributeMaxDynamicSharedMemorySize, 28672 * 8));
             { FDGS_PROF("k_tile_sort", stream);
             k_tile_sort<28672><<<T, 256, 28672 * 8, stream>>>(im.ranges, bn.bucket, g, colors, bn.records, a->keys_out, a->point_list_out);
             }

@@ -143,6 +143,11 @@ class _DeformFunction(torch.autograd.Function):
             del keep
         ctx.mod = net_mod
         ctx.time_host = time_host
+        # the backward re-reads the live parameter storage and the module-level packed-plane cache through raw pointers,
+        # which autograd's version counters cannot see: remember the versions and refuse a stale backward ourselves
+        ctx.param_versions = tuple(p._version for p in params)
+        ctx.params = params
+        ctx.plane_key = net_mod._packed_key
         ctx.save_for_backward(point_c, packed, trow, *([time_dev] if time_dev is not None else []))
         ctx.saved_act = saved
         ctx.has_time_dev = time_dev is not None
@@ -154,6 +159,11 @@ class _DeformFunction(torch.autograd.Function):
     def backward(ctx, *gouts):
         lib = L.load()
         mod = ctx.mod
+        if tuple(p._version for p in ctx.params) != ctx.param_versions or mod._packed_key != ctx.plane_key:
+            raise RuntimeError("one of the variables needed for gradient computation has been modified by an inplace "
+                               "operation: a deformation parameter (or the packed-plane cache) changed between this "
+                               "forward and its backward (fdgs re-reads parameters through raw pointers; run backward "
+                               "before optimizer.step(), see INTEGRATION.md)")
         saved = ctx.saved_tensors
         point_c, packed, trow = saved[0], saved[1], saved[2]
         time_dev = saved[3] if ctx.has_time_dev else None
@@ -218,12 +228,16 @@ class Deformation(nn.Module):
                                           "and is not supported by the fused kernels")
         if grid_pe not in (0, 1):
             raise NotImplementedError("grid_pe > 1 is not supported by the fused kernels")
+        if D > 1:
+            raise NotImplementedError("defor_depth > 1 is not supported by the fused kernels (every shipped config of the "
+                                      "reference uses 0 or 1, arguments/*/*.py): the backward has no multi-layer trunk")
         self.grid = HexPlaneField(args.bounds, args.kplanes_config, args.multires)
         self.args = args
         self.ratio = 0
         self.precision = 0      # 0: FP32-equivalent (3xTF32 on tcgen05), 1: single-pass TF32, 2: FP32 CUDA-core kernels
         self.grads_in_place = False    # see _alloc_param_grads
         self.save_activations = True   # training forward keeps the hidden activations (~3.2 KB/point) instead of recomputing
+        self.validate_time = False     # True: check (one device sync) that times_sel is one constant per call, see forward_dynamic
         self._packed = None
         self._packed_key = None
         self.create_net()
@@ -390,8 +404,15 @@ class Deformation(nn.Module):
         hm = self.head_mask
         # the fused kernel uses ONE timestamp per call: render() builds time as scalar.repeat(P,1)
         # (gaussian_renderer/__init__.py:52).  A python float / 0-d tensor is accepted too.
+        # Per-point timestamps (which the reference's API shape would allow) are NOT supported: a CPU tensor is checked
+        # here, a CUDA tensor only with `validate_time` (the comparison costs a device sync).
         time_dev, time_host = None, None
         if isinstance(time_emb, torch.Tensor):
+            if time_emb.numel() > 1 and (self.validate_time or not time_emb.is_cuda):
+                flat = time_emb.detach().reshape(-1)
+                if not bool((flat == flat[0]).all()):
+                    raise ValueError("fdgs deformation takes ONE timestamp per call (times_sel must be a constant column, "
+                                     "as gaussian_renderer/__init__.py:52 builds it); got per-point times")
             if time_emb.is_cuda:
                 time_dev = time_emb.detach().reshape(-1)[:1].to(torch.float32)
             else:

@@ -179,7 +179,7 @@ class _SharedFeatures:
 
 
 def train_iteration(render_fn, pc, cams, gts, bg, bucket, rank=0, world=1, read_loss=False, loss_fn=None,
-                    share_features=True, overlap_sh=False):
+                    share_features=True, overlap_sh=False, reduce_stats=True):
     """One fwd+bwd iteration over the batch `cams` (all B views; this rank renders its shard).
     loss_fn(image, gt, B): per-view loss; default = the ATen l1_view_loss above (fdgs.losses.l1_view_loss is the fused one).
     share_features: concatenate the SH coefficients once per iteration, let the views' SH gradients sum in one [P,16,3]
@@ -187,10 +187,14 @@ def train_iteration(render_fn, pc, cams, gts, bg, bucket, rank=0, world=1, read_
     reference's per-view cat backward; saves a cat and a strided two-way gradient accumulation per view).
     overlap_sh (world > 1): the SH gradients are two thirds of the bucket and are final as soon as the LAST view's rasterizer
     backward has run, before its deformation backward; their part of the all-reduce is started there (asynchronously, on
-    the process group's stream) and the rest of the bucket follows at the end - the sums are the same, in two or three
-    collectives instead of one.  Off by default: measured at 2 / 4 GPUs it gains nothing (13.31 vs 13.28, 6.92 vs 6.87 ms per
-    iteration) - the deformation backward kernels fill every SM, so NCCL's kernel only gets to run between them.
-    Returns (local loss sum as a tensor, max radii, visibility) like train.py:229-232 needs."""
+    the process group's stream) and the rest of the bucket follows at the end - the sums are the same, in three
+    collectives instead of one.  The collective SCHEDULE depends only on rank-independent inputs (overlap_sh, the
+    process group, the bucket layout): a rank that owns no view (world > B) issues the same three range all-reduces.
+    reduce_stats (world > 1): the densifier's inputs are made identical on every rank - `radii` is all-reduced with MAX
+    (train.py:229 takes the max over ALL B views) and visibility is derived from it (train.py:230: any over views ==
+    max radius > 0), so that replicas take the same split / prune decisions and keep the same P.
+    Returns (local loss sum, radii max over all B views [P] int32, visibility [P] bool) - what train.py:229-232,346-349
+    feed to max_radii2D / add_densification_stats."""
     B = len(cams)
     bucket.zero()
     loss_sum = None
@@ -206,8 +210,8 @@ def train_iteration(render_fn, pc, cams, gts, bg, bucket, rank=0, world=1, read_
             pc_it = _SharedFeatures(pc, leaf)
     distributed = dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1
     span = None
-    if overlap_sh and distributed and mine and has_feats and hasattr(pc, "_features_dc") and hasattr(pc, "_features_rest"):
-        span = bucket.span([pc._features_dc, pc._features_rest])
+    if overlap_sh and distributed and has_feats and hasattr(pc, "_features_dc") and hasattr(pc, "_features_rest"):
+        span = bucket.span([pc._features_dc, pc._features_rest])      # rank-independent: same bucket layout everywhere
     early = []          # [async work handle] once the SH part of the all-reduce is in flight
     hooks = []
     for i in mine:
@@ -240,14 +244,30 @@ def train_iteration(render_fn, pc, cams, gts, bg, bucket, rank=0, world=1, read_
         radii_max = out["radii"] if radii_max is None else torch.maximum(radii_max, out["radii"])
     for h in hooks:
         h.remove()
-    if early:
+    if span is not None:
+        # every rank issues the same three collectives in the same order: [SH span], [0, lo), [hi, end)
+        if not early:
+            # no hook fired on this rank (it owns no view, or its SH parameters received no gradient)
+            if leaf is not None and leaf.grad is not None:
+                feats.backward(leaf.grad)
+            early.append(bucket.all_reduce_range(*span, async_op=True))
         bucket.all_reduce_range(0, span[0])
         bucket.all_reduce_range(span[1], bucket.flat.numel())
-        early[0].wait()
+        if early[0] is not None:
+            early[0].wait()
     else:
         if leaf is not None and leaf.grad is not None:
             feats.backward(leaf.grad)
         bucket.all_reduce()
-    if read_loss and loss_sum is not None:
-        return float(loss_sum), radii_max
-    return loss_sum, radii_max
+    if radii_max is None:           # this rank owns no view of the batch
+        P = bucket.extra["viewspace"].shape[0] if "viewspace" in bucket.extra else pc.get_xyz.shape[0]
+        radii_max = torch.zeros((P,), dtype=torch.int32, device=bucket.flat.device)
+    if distributed and reduce_stats:
+        radii_max = radii_max.contiguous()
+        dist.all_reduce(radii_max, op=dist.ReduceOp.MAX)
+    visibility = radii_max > 0
+    if loss_sum is None:
+        loss_sum = torch.zeros((), dtype=torch.float32, device=bucket.flat.device)
+    if read_loss:
+        return float(loss_sum), radii_max, visibility
+    return loss_sum, radii_max, visibility

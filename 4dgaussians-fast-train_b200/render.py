@@ -28,6 +28,11 @@ def render(viewpoint_camera, pc, pipe=None, bg_color=None, scaling_modifier=1.0,
         pass
     means3D = xyz
     debug = bool(getattr(pipe, "debug", False)) if pipe is not None else False
+    for flag in ("compute_cov3D_python", "convert_SHs_python"):
+        # the reference's render() crashes on the first and only reaches the second from the GUI
+        if pipe is not None and getattr(pipe, flag, False):
+            raise NotImplementedError(f"pipe.{flag}=True is not supported by fdgs.render (covariances and SH colours are "
+                                      "computed inside the rasterizer kernels); pass override_color for precomputed colours")
     if cam_type != "PanopticSports":
         tanfovx = math.tan(viewpoint_camera.FoVx * 0.5)
         tanfovy = math.tan(viewpoint_camera.FoVy * 0.5)

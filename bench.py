@@ -348,7 +348,7 @@ def main():
         # host -> device: this step's GT images (pinned -> device on the stager's copy stream, one event per view, so the
         # copy of view i+1 runs under the kernels of view i) and camera tensors; device -> host: the loss
         stager.upload(gts_host, mine)
-        loss, _ = train_iteration(render_fn, pc, StepCameras(), stager, bg, bucket, eff_rank, eff_world, read_loss=True,
+        loss, _, _ = train_iteration(render_fn, pc, StepCameras(), stager, bg, bucket, eff_rank, eff_world, read_loss=True,
                                   loss_fn=fused_loss, overlap_sh=overlap_sh)
         assert stager.nbytes == sum(gts_host[i].numel() * 4 for i in mine)
         return loss

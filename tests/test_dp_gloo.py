@@ -29,7 +29,14 @@ def _render(cam, pc, bg_color=None, stage="fine"):
     vs = torch.zeros(37, 3, requires_grad=True)
     img = (pc.a * cam).sum(0)[:, None, None] * torch.ones(3, 4, 6) + pc.b.sum() * cam + bg_color[:, None, None] + vs.sum() * cam
     vs.retain_grad()
-    return dict(render=img, viewspace_points=vs, radii=torch.full((37,), int(cam * 10), dtype=torch.int32))
+    # radii differ per view AND per Gaussian; Gaussian 36 is invisible in every view, Gaussian k only in view k
+    radii = torch.full((37,), int(cam * 10), dtype=torch.int32)
+    radii[36] = 0
+    k = int(round((cam - 0.3) / 0.2))
+    radii[:8] = 0
+    if k < 8:
+        radii[k] = 50 + k
+    return dict(render=img, viewspace_points=vs, radii=radii)
 
 
 def _batch(B):
@@ -57,11 +64,11 @@ def _worker(rank, world, port, B, q):
         bucket = dp.GradBucket(pc.parameters(), extra={"viewspace": (37, 3)}, device="cpu")
         assert pc.a.grad.data_ptr() == bucket.views[0].data_ptr()
         cams, gts = _batch(B)
-        loss, radii = dp.train_iteration(_render, pc, cams, gts, torch.ones(3), bucket, rank=rank, world=world)
+        loss, radii, vis = dp.train_iteration(_render, pc, cams, gts, torch.ones(3), bucket, rank=rank, world=world)
         tot = loss.clone()
         dist.all_reduce(tot)
         q.put((rank, float(tot), pc.a.grad.clone(), pc.b.grad.clone(), bucket.extra["viewspace"].clone(),
-               int(radii.max()), bucket.nbytes()))
+               radii.clone(), bucket.nbytes(), vis.clone()))
     finally:
         dist.destroy_process_group()
 
@@ -109,10 +116,16 @@ def test_world2_gloo_matches_single_process(B):
     for p in procs:
         p.join(timeout=60)
         assert p.exitcode == 0
-    for rank, loss, a, b, vs, rmax, nbytes in res:
+    cams, _ = _batch(B)
+    per_view = torch.stack([_render(c, _PC(), torch.ones(3))["radii"] for c in cams])
+    for rank, loss, a, b, vs, radii, nbytes, vis in res:
         assert loss == pytest.approx(ref_loss, rel=1e-6)
         assert torch.allclose(a, ga, rtol=1e-5, atol=1e-7) and torch.allclose(b, gb, rtol=1e-5, atol=1e-7)
         assert nbytes == 4 * (128 + 64 + 128)      # 111 -> 128, 5 -> 64, 111 -> 128 floats
+        # densification inputs are those of the WHOLE batch on every rank (train.py:229-230): max / any over all B views
+        assert torch.equal(radii, per_view.max(0).values)
+        assert torch.equal(vis, (per_view > 0).any(0))
+    assert not bool(res[0][7][36]) and bool(res[0][7][:B].all()) and not bool(res[0][7][B:8].any())
     assert torch.equal(res[0][4], res[1][4])       # the view-space accumulator is reduced too
     assert float(res[0][4].abs().sum()) > 0
 
@@ -147,7 +160,7 @@ def test_shared_features_gradients_equal_per_view_cat(B):
     for share in (False, True):
         pc = _PCFeat()
         bucket = dp.GradBucket(pc.parameters(), extra={"viewspace": (37, 3)}, device="cpu")
-        loss, _ = dp.train_iteration(_render_feat, pc, cams, gts, torch.ones(3), bucket, share_features=share)
+        loss, _, _ = dp.train_iteration(_render_feat, pc, cams, gts, torch.ones(3), bucket, share_features=share)
         slot = {id(p): v for p, v in zip(bucket.params, bucket.views)}
         assert pc._features_dc.grad.data_ptr() == slot[id(pc._features_dc)].data_ptr()
         assert pc._features_rest.grad.data_ptr() == slot[id(pc._features_rest)].data_ptr()
@@ -177,8 +190,8 @@ def _worker_feat(rank, world, port, B, overlap, q):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("B", [4, 2])            # 2 views per rank: shared SH leaf; 1 view per rank: per-parameter hooks
-def test_world2_early_sh_all_reduce_equals_single_collective(B):
+@pytest.mark.parametrize("B", [4, 2, 1])         # 2 views per rank: shared SH leaf; 1 view per rank: per-parameter hooks;
+def test_world2_early_sh_all_reduce_equals_single_collective(B):     # B = 1 < world: rank 1 owns no view, same collectives
     ctx = mp.get_context("spawn")
     flats = {}
     for overlap in (False, True):
@@ -194,9 +207,11 @@ def test_world2_early_sh_all_reduce_equals_single_collective(B):
         assert torch.equal(res[0][1], res[1][1])
         flats[overlap] = res[0][1]
         if overlap:
-            calls = res[0][2]
-            assert len(calls) == 3 and calls[0][2] is True        # SH span first and asynchronous, then the two remainders
-            assert calls[1][0] == 0 and calls[1][1] == calls[0][0] and calls[2][0] == calls[0][1]
+            for r in res:                                         # EVERY rank, with or without views, issues the same schedule
+                calls = r[2]
+                assert len(calls) == 3 and calls[0][2] is True    # SH span first and asynchronous, then the two remainders
+                assert calls[1][0] == 0 and calls[1][1] == calls[0][0] and calls[2][0] == calls[0][1]
+            assert res[0][2] == res[1][2]
         else:
             assert res[0][2] == []
     assert torch.equal(flats[False], flats[True])                 # two-rank sums: order-independent, bit-identical

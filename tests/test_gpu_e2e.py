@@ -36,7 +36,7 @@ def _run(impl, cfg_name, views, points, fused_loss):
         loss_fn = None
     with torch.no_grad():
         images = [render_fn(c, pc, bg_color=bg, stage="fine")["render"].clone() for c in cams]
-    loss, radii = train_iteration(render_fn, pc, cams, gts, bg, bucket, 0, 1, read_loss=True, loss_fn=loss_fn)
+    loss, radii, _vis = train_iteration(render_fn, pc, cams, gts, bg, bucket, 0, 1, read_loss=True, loss_fn=loss_fn)
     grads = {"viewspace": bucket.extra["viewspace"].clone()}
     for name in ("_xyz", "_scaling", "_rotation", "_opacity", "_features_dc", "_features_rest"):
         grads[name] = getattr(pc, name).grad.clone()
@@ -98,7 +98,7 @@ def test_view_stager_and_shared_features_change_nothing():
             targets.upload(gts_host, range(len(gts_host)))
             assert torch.equal(targets[2], gts[2]) and torch.equal(targets[0], gts[0])     # out-of-order access
             targets.upload(gts_host, range(len(gts_host)))
-        loss, _ = train_iteration(render_fn, pc, cams, targets, bg, bucket, 0, 1, read_loss=True, loss_fn=loss_fn,
+        loss, _, _ = train_iteration(render_fn, pc, cams, targets, bg, bucket, 0, 1, read_loss=True, loss_fn=loss_fn,
                                   share_features=share)
         res.append((loss, pc._features_dc.grad.clone(), pc._features_rest.grad.clone()))
     assert float(res[0][1].abs().sum()) > 0 and float(res[0][2].abs().sum()) > 0
