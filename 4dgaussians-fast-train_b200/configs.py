@@ -26,6 +26,10 @@ CONFIGS = {
     "tiny": dict(args=lambda: hidden_params(kplanes_config=_kp(8, [16, 16, 16, 20]), multires=[1], defor_depth=0,
                                             net_width=32, no_do=False, no_dshs=False),
                  W=200, H=120, P=2000, views=1, fovx=0.6911, extent=1.3, logscale=-3.5),
+    # the DyNeRF net (C=16, L=2, Wn=128, five heads: the tcgen05 kernels) on small planes and a small image
+    "dynerf_small": dict(args=lambda: hidden_params(kplanes_config=_kp(16, [16, 16, 16, 20]), multires=[1, 2], defor_depth=0,
+                                                    net_width=128, no_do=False, no_dshs=False),
+                         W=200, H=120, P=3000, views=2, fovx=0.6911, extent=1.3, logscale=-3.5),
     "dnerf": dict(args=lambda: hidden_params(kplanes_config=_kp(32, [64, 64, 64, 75]), multires=[1, 2], defor_depth=0,
                                              net_width=64, bounds=1.6),
                   W=800, H=800, P=200_000, views=1, fovx=0.6911, extent=1.3, logscale=-4.828),

@@ -494,6 +494,38 @@ k_blend_fwd(const uint2* __restrict__ ranges, const FdgsRecord* __restrict__ rec
     }
 }
 
+// Diagnostic (bench / roofline, never on the training path): the blend's algorithmic work of one rendered view.
+// counts[0] += sum over pixels of n_contrib  = pixel x instance pairs a per-pixel walk has to TEST (forward.cu:321-366)
+// counts[1] += pairs that CONTRIBUTE (alpha >= 1/255 before the pixel saturates) = the pairs the backward differentiates
+__global__ void __launch_bounds__(256)
+k_count_pairs(const uint2* __restrict__ ranges, const FdgsRecord* __restrict__ records, int W, int H,
+              const uint32_t* __restrict__ n_contrib, unsigned long long* __restrict__ counts)
+{
+    const int tiles_x = (W + FDGS_TILE - 1) / FDGS_TILE;
+    const int tile = blockIdx.y * tiles_x + blockIdx.x;
+    const int px = blockIdx.x * FDGS_TILE + (threadIdx.x & 15), py = blockIdx.y * FDGS_TILE + (threadIdx.x >> 4);
+    unsigned long long walked = 0, hits = 0;
+    if (px < W && py < H) {
+        const uint2 rg = ranges[tile];
+        const uint32_t n = n_contrib[(size_t)py * W + px];
+        walked = n;
+        for (uint32_t i = 0; i < n && rg.x + i < rg.y; ++i) {
+            const FdgsRecord r = records[rg.x + i];
+            const float dx = r.x - (float)px, dy = r.y - (float)py;
+            const float power = -0.5f * (r.ca * dx * dx + r.cc * dy * dy) - r.cb * dx * dy;
+            if (power > 0.0f) continue;
+            const float alpha = fminf(0.99f, r.opacity * expf(power));
+            if (alpha < 1.0f / 255.0f) continue;
+            ++hits;
+        }
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        walked += __shfl_xor_sync(FULL, walked, o);
+        hits += __shfl_xor_sync(FULL, hits, o);
+    }
+    if ((threadIdx.x & 31) == 0) { atomicAdd(&counts[0], walked); atomicAdd(&counts[1], hits); }
+}
+
 // checkFrustum (rasterizer_impl.cu:54-66)
 __global__ void k_mark_visible(int P, const float* __restrict__ means3D, const float* __restrict__ V, uint8_t* present) {
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
@@ -614,6 +646,21 @@ int fdgs_raster_copy_ranges(const void* img_ws, int W, int H, uint32_t* ranges_o
     FdgsImg im = FdgsImg::carve(const_cast<void*>(img_ws), W, H);
     const size_t T = (size_t)((W + FDGS_TILE - 1) / FDGS_TILE) * ((H + FDGS_TILE - 1) / FDGS_TILE);
     FDGS_CUDA(cudaMemcpyAsync(ranges_out, im.ranges, T * sizeof(uint2), cudaMemcpyDeviceToDevice, (cudaStream_t)stream_));
+    return FDGS_OK;
+}
+
+int fdgs_raster_count_pairs(const void* img_ws, const void* bin_ws, int64_t R, int W, int H, unsigned long long* counts,
+                            void* stream_) {
+    if (!img_ws || !counts || W <= 0 || H <= 0 || R < 0) return FDGS_E_BADARG;
+    cudaStream_t stream = (cudaStream_t)stream_;
+    FDGS_CUDA(cudaMemsetAsync(counts, 0, 2 * sizeof(unsigned long long), stream));
+    if (R == 0) return FDGS_OK;
+    if (!bin_ws) return FDGS_E_BADARG;
+    FdgsImg im = FdgsImg::carve(const_cast<void*>(img_ws), W, H);
+    FdgsBin bn = FdgsBin::carve(const_cast<void*>(bin_ws), R);
+    dim3 grid((W + FDGS_TILE - 1) / FDGS_TILE, (H + FDGS_TILE - 1) / FDGS_TILE);
+    k_count_pairs<<<grid, 256, 0, stream>>>(im.ranges, bn.records, W, H, im.n_contrib, counts);
+    FDGS_LAUNCH_CHECK(0, stream);
     return FDGS_OK;
 }
 

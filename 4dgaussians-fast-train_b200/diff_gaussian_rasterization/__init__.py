@@ -44,6 +44,8 @@ def cpu_deep_copy_tuple(input_tuple):
 
 _pinned = {}
 _last_R = 0
+_keep_last = False       # diagnostics only: keep a reference to the last forward's workspaces (see count_pairs)
+_last_ws = None
 
 
 def last_num_rendered():
@@ -139,6 +141,9 @@ def _forward_native(bg, means3D, colors_precomp, opacities, scales, rotations, s
             a.keys_out = extras["keys"].data_ptr() if R else None
             a.point_list_out = extras["point_list"].data_ptr() if R else None
         L.check(lib.fdgs_raster_forward_render(C.byref(a), R, st), "fdgs_raster_forward_render")
+        if _keep_last:
+            global _last_ws
+            _last_ws = (img, binb, R, W, H)
         out = (R, color, depth, radii, geom, binb, img)
         if want_debug_lists:
             T = ((W + TILE - 1) // TILE) * ((H + TILE - 1) // TILE)
@@ -149,6 +154,27 @@ def _forward_native(bg, means3D, colors_precomp, opacities, scales, rotations, s
             extras.update(_img_views(img, W, H))
             return out + (extras,)
         return out
+
+
+def count_pairs(render_fn, cam, pc, bg):
+    """Diagnostic for the blend kernels' roofline (bench.py): renders one view forward-only and counts, on the device,
+    the pixel x Gaussian pairs a per-pixel walk tests (sum of n_contrib) and those that contribute (alpha >= 1/255)."""
+    global _keep_last, _last_ws
+    lib = L.load()
+    _keep_last = True
+    try:
+        with torch.no_grad():
+            render_fn(cam, pc, bg_color=bg, stage="fine")
+        img, binb, R, W, H = _last_ws
+    finally:
+        _keep_last = False
+        _last_ws = None
+    counts = torch.zeros(2, dtype=torch.int64, device=img.device)
+    with torch.cuda.device(img.device):
+        L.check(lib.fdgs_raster_count_pairs(img.data_ptr(), binb.data_ptr() if binb.numel() else None, int(R), W, H,
+                                            counts.data_ptr(), _stream()), "fdgs_raster_count_pairs")
+    c = counts.cpu().tolist()
+    return {"num_rendered": int(R), "tested": int(c[0]), "contributing": int(c[1])}
 
 
 def _geom_views(geom, P):

@@ -112,6 +112,13 @@ int fdgs_raster_forward_render(const FdgsRasterForward* a, int64_t R, void* stre
  * rasterizer_impl.cu:311-319 leaves them) into a device buffer — parity/debug. */
 int fdgs_raster_copy_ranges(const void* img_ws, int W, int H, uint32_t* ranges_out, void* stream);
 
+/* Diagnostic for the roofline of the blend kernels (bench only; not on the training path): after a forward call,
+ * counts[0] = sum over pixels of n_contrib (pixel x instance pairs a per-pixel walk tests, RAST/cuda_rasterizer/
+ * forward.cu:321-366), counts[1] = pairs that contribute (alpha >= 1/255 before saturation): what the backward
+ * differentiates (backward.cu:459-555).  counts: 2 DEVICE uint64, zeroed by the call.                           */
+int fdgs_raster_count_pairs(const void* img_ws, const void* bin_ws, int64_t R, int W, int H,
+                            unsigned long long* counts, void* stream);
+
 typedef struct FdgsRasterBackward {
     /* reference: RasterizeGaussiansBackwardCUDA args, RAST/rasterize_points.cu:119-142 */
     int32_t P, D, M, W, H;

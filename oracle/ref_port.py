@@ -169,6 +169,32 @@ class ref_deform_network(nn.Module):
         return self.deformation_net(point_emb, scales_emb, rotations_emb, opacity, shs, None, times_sel)
 
 
+def relu_danger_mask(net, xyz, t, eps=2e-5):
+    """[P] bool: points with a hidden pre-activation so close to zero that FP32 re-association can flip its ReLU gate.
+
+    Runs an FP64 copy of `net` (this port's ref_deform_network or the real reference deform_network: same attribute
+    names) and flags a point when |h_k| or |z_{j,k}| < eps * (rms of that layer) for any unit k of the trunk
+    output h = feature_out(grid(xyz, t)) or of an active head's hidden layer z_j = head_j[1](relu(h)).  A flipped gate
+    changes that ONE point's gradient contribution by O(1) in ANY FP32 implementation (the reference's own GPU ops
+    included, profiles/r01_deform_relu_flips.log), so parity tests zero the upstream gradient of these few points and
+    then hold everything else to the plain tolerance."""
+    import copy
+    n64 = copy.deepcopy(net).double()
+    d = n64.deformation_net
+    a = d.args
+    with torch.no_grad():
+        h = d.feature_out(d.grid(xyz.double()[:, :3], t.double()[:, :1]))
+        bad = (h.abs() < eps * float(h.pow(2).mean().sqrt())).any(dim=1)
+        rh = torch.relu(h)
+        for name, off in (("pos_deform", a.no_dx), ("scales_deform", a.no_ds), ("rotations_deform", a.no_dr),
+                          ("opacity_deform", a.no_do), ("shs_deform", a.no_dshs)):
+            if off:
+                continue
+            z = getattr(d, name)[1](rh)
+            bad |= (z.abs() < eps * float(z.pow(2).mean().sqrt())).any(dim=1)
+    return bad
+
+
 class _RefRasterize(torch.autograd.Function):
     @staticmethod
     def forward(ctx, refC, means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, s):

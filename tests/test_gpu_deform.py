@@ -9,8 +9,10 @@ up to 3e5 points accumulated with float atomics in both implementations).
 ReLU gate flips: a hidden pre-activation that is within an ulp of zero gets a different ReLU derivative
 under a different FP32 summation order, which changes that ONE point's gradient by O(1) — in this kernel
 and in the reference's own GPU ops alike (measured against an FP64 arbiter: 1-4 such points per 20k in
-both, profiles/r01_deform_relu_flips.log).  At >= 20k points the gradient comparison is therefore
-flip-robust: all but a 2e-4 fraction of the entries within tolerance, and the L2 error below 1e-2."""
+both, profiles/r01_deform_relu_flips.log).  The >= 20k-point comparisons are flip-AWARE rather than loose: an
+FP64 copy of the reference net flags the points with a pre-activation within 2e-5 of zero (about 1 % of
+them, ref_port.relu_danger_mask), their upstream gradient is zeroed on both sides, and every gradient is
+then held to the plain 2e-5 max-norm bar plus an L2 bar of 1e-5.  Observed values: profiles/r02_parity_deform.log."""
 import os
 
 import numpy as np
@@ -28,6 +30,9 @@ GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 OUT_TOL, GRAD_TOL = 2e-6, 2e-5
 
 GOLDEN_CASES = {
+    # the DyNeRF net (arguments/dynerf/default.py:1-20: C=16, L=2, Wn=128, all five heads) on small planes: the tcgen05 path
+    "dynerf128": dict(kplanes_config=_kp(16, [16, 16, 16, 20]), multires=[1, 2], defor_depth=0, net_width=128, no_do=False,
+                      no_dshs=False),
     "tiny": dict(kplanes_config=_kp(8, [16, 16, 16, 20]), multires=[1], defor_depth=0, net_width=32, no_do=False, no_dshs=False),
     "small3": dict(kplanes_config=_kp(16, [12, 10, 8, 9]), multires=[1, 2], defor_depth=1, net_width=64),
     "bcast": dict(kplanes_config=_kp(8, [8, 8, 8, 6]), multires=[1], defor_depth=0, net_width=32, no_do=False, no_dshs=False),
@@ -75,7 +80,16 @@ def test_golden(name):
             n += 1
         else:
             assert p.grad is None or not bool(p.grad.abs().max() > 0), k      # timenet / disabled heads / aabb
-    assert n >= 12 + 2 + 3 * 4
+    assert n >= 6 * len(GOLDEN_CASES[name]["multires"]) + 2 + 3 * 4
+    if name == "dynerf128":     # this fixture must have run on the tensor cores (tcgen05 forward + both backward kernels)
+        from fdgs import _lib
+        _lib.profile_enable(True)
+        o2 = net(inp["xyz"].detach(), inp["scales"].detach().requires_grad_(True), inp["rot"].detach(), inp["opacity"].detach(),
+                 inp["shs"].detach(), t)
+        o2[1].sum().backward()
+        prof = _lib.profile_collect()
+        _lib.profile_enable(False)
+        assert "k_deform_fwd_tc" in prof and "k_deform_bwd_weights" in prof, sorted(prof)
 
 
 def _pair(args, seed=1234):
@@ -99,18 +113,26 @@ def _run(net, inp, t, ws):
     return outs, leaves
 
 
-def _grad_close(a, b, what, robust):
-    if not robust:
-        assert util.rel_err(a, b) < GRAD_TOL, what
-        return
+L2_TOL = 1e-5
+_worst = {}
+
+
+def _grad_close(a, b, what, tag=None):
     a, b = a.detach().double().reshape(-1), b.detach().double().reshape(-1)
-    scale = float(b.abs().max()) + 1e-30
-    bad = ((a - b).abs() > 20 * GRAD_TOL * scale).double().mean()
-    assert float(bad) <= 2e-2, (what, "fraction of entries off", float(bad))
-    assert float((a - b).norm() / (b.norm() + 1e-30)) < 1e-2, (what, "L2")
+    e = float((a - b).abs().max() / (b.abs().max() + 1e-30))
+    l2 = float((a - b).norm() / (b.norm() + 1e-30))
+    if tag is not None:
+        w = _worst.setdefault(tag, [0.0, "", 0.0, ""])
+        if e > w[0]:
+            w[0], w[1] = e, what
+        if l2 > w[2]:
+            w[2], w[3] = l2, what
+    assert e < GRAD_TOL, (what, "max-norm", e)
+    assert l2 < L2_TOL, (what, "L2", l2)
 
 
-def _compare(args, P, tval, extent=1.0, sh_coeffs=16, aabb=None, robust=False):
+def _compare(args, P, tval, extent=1.0, sh_coeffs=16, aabb=None, flip_aware=False, tag=None):
+    import ref_port
     ours, ref = _pair(args)
     if aabb is not None:
         ours.deformation_net.set_aabb(*aabb); ref.deformation_net.set_aabb(*aabb)
@@ -123,6 +145,12 @@ def _compare(args, P, tval, extent=1.0, sh_coeffs=16, aabb=None, robust=False):
     with torch.no_grad():
         outs_r = ref(inp["xyz"], inp["scales"], inp["rot"], inp["opacity"], inp["shs"], t)
     ws = [torch.randn(o.shape, generator=g).cuda() for o in outs_r]
+    if flip_aware:
+        danger = ref_port.relu_danger_mask(ref, inp["xyz"], t)
+        assert float(danger.double().mean()) < 0.05, "danger mask covers more than a few percent of the points"
+        ws = [w * (~danger).to(w.dtype).reshape([-1] + [1] * (w.dim() - 1)) for w in ws]
+        if tag:
+            util.plog("deform", f"{tag}: P={P} flip-prone points masked: {int(danger.sum())}")
     o_ref, l_ref = _run(ref, inp, t, ws)
     o_our, l_our = _run(ours, inp, t, ws)
     for i, (a, b) in enumerate(zip(o_our, o_ref)):
@@ -132,25 +160,24 @@ def _compare(args, P, tval, extent=1.0, sh_coeffs=16, aabb=None, robust=False):
         ga, gb = l_our[k].grad, l_ref[k].grad
         if gb is None:
             assert ga is None or not bool(ga.abs().max() > 0), k
-        elif robust and k == "xyz":
-            err = (ga - gb).abs().max(dim=1).values / (float(gb.abs().max()) + 1e-30)
-            assert float((err > GRAD_TOL).double().mean()) <= 2e-4, "xyz: more points off than ReLU flips explain"
-            assert float(err.median()) < 1e-6
         else:
-            _grad_close(ga, gb, k, robust)
+            _grad_close(ga, gb, k, tag)
     for (k, p), (_, q) in zip(ours.named_parameters(), ref.named_parameters()):
         if q.grad is None:
             assert p.grad is None or not bool(p.grad.abs().max() > 0), k
         else:
             assert p.grad is not None, k
-            _grad_close(p.grad, q.grad, k, robust)
+            _grad_close(p.grad, q.grad, k, tag)
+    if tag and tag in _worst:
+        w = _worst[tag]
+        util.plog("deform", f"{tag}: worst max-norm grad err {w[0]:.3e} ({w[1]}), worst L2 {w[2]:.3e} ({w[3]}); bars {GRAD_TOL:g} / {L2_TOL:g}")
 
 
 @pytest.mark.parametrize("cfg", ["dnerf", "hypernerf", "dynerf"])
 def test_baseline_shapes_vs_reference_ops(cfg):
     c = CONFIGS[cfg]
     _compare(c["args"](), P=20_011, tval=0.4375, extent=c["extent"],
-             aabb=([c["extent"]] * 3, [-c["extent"]] * 3), robust=True)
+             aabb=([c["extent"]] * 3, [-c["extent"]] * 3), flip_aware=True, tag=f"baseline_shapes[{cfg}]")
 
 
 @pytest.mark.parametrize("tval", [0.0, 0.5, 299 / 300])

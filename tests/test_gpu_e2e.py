@@ -46,7 +46,7 @@ def _run(impl, cfg_name, views, points, fused_loss):
     return images, loss, radii.clone(), grads
 
 
-@pytest.mark.parametrize("cfg_name,views,points", [("tiny", 2, 0), ("dnerf50k", 2, 20000)])
+@pytest.mark.parametrize("cfg_name,views,points", [("tiny", 2, 0), ("dynerf_small", 2, 0), ("dnerf50k", 2, 20000)])
 def test_train_iteration_matches_reference_arm(cfg_name, views, points):
     import build_ref
     if not build_ref.available():
@@ -59,6 +59,8 @@ def test_train_iteration_matches_reference_arm(cfg_name, views, points):
         # threshold may be taken on one side and skipped on the other (libm-level differences upstream): a handful of
         # pixels may then differ by up to 1/255 of a colour.
         d = (a - b).abs() / b.abs().max()
+        util.plog("e2e", f"{cfg_name}: image {tuple(a.shape)}: pixels-values off by > 2e-5: {int((d > 2e-5).sum())} of {a.numel()} "
+                         f"(allowance {max(4, a.numel() // 20000)}), worst {float(d.max()):.2e}")
         assert int((d > 2e-5).sum()) <= max(4, a.numel() // 20000), float(d.max())
         assert float(d.max()) < 5e-3
     assert abs(loss_f - loss_r) <= 2e-6 * abs(loss_r)
@@ -69,6 +71,8 @@ def test_train_iteration_matches_reference_arm(cfg_name, views, points):
         # sides, so the bar is: all but a handful of entries within 2e-4 of the largest, and 2e-3 in the L2 sense
         a, b = g_f[k].double(), g_r[k].double()
         d = (a - b).abs() / (b.abs().max() + 1e-30)
+        util.plog("e2e", f"{cfg_name}: grad {k}: entries off by > 2e-4: {int((d > 2e-4).sum())} of {a.numel()}, worst {float(d.max()):.2e}, "
+                         f"L2 {float((a - b).norm() / (b.norm() + 1e-30)):.2e}")
         assert int((d > 2e-4).sum()) <= max(8, a.numel() // 2000), (k, float(d.max()))
         assert float((a - b).norm() / (b.norm() + 1e-30)) < 2e-3, k
 

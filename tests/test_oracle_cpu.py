@@ -21,6 +21,8 @@ import raster_oracle as RO
 GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 
 DEFORM_CASES = {
+    "dynerf128": dict(kplanes_config=_kp(16, [16, 16, 16, 20]), multires=[1, 2], defor_depth=0, net_width=128, no_do=False,
+                      no_dshs=False),
     "tiny": dict(kplanes_config=_kp(8, [16, 16, 16, 20]), multires=[1], defor_depth=0, net_width=32, no_do=False, no_dshs=False),
     "small3": dict(kplanes_config=_kp(16, [12, 10, 8, 9]), multires=[1, 2], defor_depth=1, net_width=64),
     "bcast": dict(kplanes_config=_kp(8, [8, 8, 8, 6]), multires=[1], defor_depth=0, net_width=32, no_do=False, no_dshs=False),
@@ -39,6 +41,10 @@ def test_deform_oracle_matches_reference_module(name, dtype, out_tol, grad_tol):
     """FP32 restatement vs the reference's FP32 results: summation-order noise only.  The FP64 copy (the
     arbiter used by the GPU tests) must sit within FP32 rounding of the same fixtures."""
     z = np.load(os.path.join(GOLD, f"deform_{name}.npz"))
+    if name == "dynerf128" and dtype == torch.float64:
+        # 2001 points x five 128-wide heads: the FP32 fixture's own summation error on a plane gradient is 5.5e-6 of
+        # the largest entry (measured against this FP64 copy), above the 5e-6 the smaller cases need
+        grad_tol = 1e-5
     cfg = DO.cfg_from_args(hidden_params(**DEFORM_CASES[name]))
     sd = {k[3:]: torch.tensor(z[k]).to(dtype).requires_grad_(k[3:].startswith("deformation_net.") and "aabb" not in k)
           for k in z.files if k.startswith("sd/")}
@@ -66,6 +72,44 @@ def test_deform_oracle_matches_reference_module(name, dtype, out_tol, grad_tol):
             assert _rel(g.numpy(), z[k]) < grad_tol, k
             n += 1
     assert n >= 14
+
+
+@pytest.mark.parametrize("name", list(DEFORM_CASES))
+def test_ref_port_is_bit_identical_to_the_reference_module(name):
+    """oracle/ref_port.py (fallback reference arm / GPU cross-check) issues the SAME ATen ops as the reference module:
+    on CPU its outputs and gradients equal the fixtures the real module produced BIT FOR BIT; and when the real
+    module is loadable (authoring container, or baseline/_ref on the box) it is compared directly as well."""
+    import ref_port
+    z = np.load(os.path.join(GOLD, f"deform_{name}.npz"))
+    args = hidden_params(**DEFORM_CASES[name])
+    sd = {k[3:]: torch.tensor(z[k]) for k in z.files if k.startswith("sd/")}
+
+    def run(make):
+        net = make(args)
+        net.deformation_net.set_aabb(sd["deformation_net.grid.aabb"][0].tolist(), sd["deformation_net.grid.aabb"][1].tolist())
+        net.load_state_dict(sd)
+        inp = {k[3:]: torch.tensor(z[k]).requires_grad_(True) for k in z.files if k.startswith("in/")}
+        P = inp["xyz"].shape[0]
+        outs = net(inp["xyz"], inp["scales"], inp["rot"], inp["opacity"], inp["shs"], torch.full((P, 1), float(z["meta/t"])))
+        sum((o * torch.tensor(z[f"w/{i}"])).sum() for i, o in enumerate(outs)).backward()
+        return outs, inp, dict(net.named_parameters())
+
+    outs, inp, params = run(ref_port.ref_deform_network)
+    for i, o in enumerate(outs):
+        assert np.array_equal(o.detach().numpy(), z[f"out/{i}"]), f"out[{i}]"
+    for k, v in inp.items():
+        assert np.array_equal(v.grad.numpy() if v.grad is not None else np.zeros_like(z["gin/" + k]), z["gin/" + k]), k
+    for k in z.files:
+        if k.startswith("gp/"):
+            assert np.array_equal(params[k[3:]].grad.numpy(), z[k]), k
+    import ref_deform
+    if ref_deform.available():
+        outs_r, inp_r, params_r = run(ref_deform.make_network)
+        for a, b in zip(outs, outs_r):
+            assert torch.equal(a, b)
+        for k in params_r:
+            ga, gb = params[k].grad, params_r[k].grad
+            assert (ga is None and gb is None) or torch.equal(ga, gb), k
 
 
 RASTER_CASES = ["tiny", "deg0", "dense", "precomp", "ragged"]
