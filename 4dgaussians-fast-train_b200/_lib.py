@@ -7,7 +7,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libfdgs.so")
+LIB_PATH = os.environ.get("FDGS_LIB") or os.path.join(_HERE, "libfdgs.so")    # FDGS_LIB: an A/B build of the same library
 
 FDGS_MAX_LEVELS = 4
 FDGS_NUM_HEADS = 5
@@ -113,6 +113,23 @@ class FdgsActivateBackward(C.Structure):
                 ("d_scales_raw", C.c_void_p), ("d_rotations_raw", C.c_void_p), ("d_opacity_raw", C.c_void_p)]
 
 
+class FdgsPlaneReg(C.Structure):
+    _fields_ = [("levels", C.c_int32), ("channels", C.c_int32), ("res", (C.c_int32 * 4) * FDGS_MAX_LEVELS),
+                ("planes", (C.c_void_p * 6) * FDGS_MAX_LEVELS), ("d_planes", (C.c_void_p * 6) * FDGS_MAX_LEVELS),
+                ("plane_tv_weight", C.c_float), ("time_smoothness_weight", C.c_float), ("l1_time_planes_weight", C.c_float),
+                ("grad_scale", C.c_void_p), ("loss", C.c_void_p)]
+
+
+class FdgsAdamTensor(C.Structure):
+    _fields_ = [("param", C.c_void_p), ("grad", C.c_void_p), ("exp_avg", C.c_void_p), ("exp_avg_sq", C.c_void_p),
+                ("n", C.c_int64), ("lr", C.c_double), ("step", C.c_int64)]
+
+
+class FdgsAdamStep(C.Structure):
+    _fields_ = [("ntensors", C.c_int32), ("zero_grad", C.c_int32), ("beta1", C.c_double), ("beta2", C.c_double),
+                ("eps", C.c_double), ("t", C.POINTER(FdgsAdamTensor))]
+
+
 # every symbol include/fdgs.h declares: name -> (restype, argtypes)
 SYMBOLS = {
     "fdgs_abi_version": (C.c_int, []),
@@ -140,6 +157,10 @@ SYMBOLS = {
     "fdgs_deform_backward": (C.c_int, [C.POINTER(FdgsDeformBackward), C.c_void_p]),
     "fdgs_activate_forward": (C.c_int, [C.POINTER(FdgsActivateForward), C.c_void_p]),
     "fdgs_activate_backward": (C.c_int, [C.POINTER(FdgsActivateBackward), C.c_void_p]),
+    "fdgs_plane_regulation": (C.c_int, [C.POINTER(FdgsPlaneReg), C.c_void_p]),
+    "fdgs_plane_smoothness": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "fdgs_adam_step": (C.c_int, [C.POINTER(FdgsAdamStep), C.c_void_p]),
+    "fdgs_densify_stats": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "fdgs_l1_loss_forward": (C.c_int, [C.c_void_p, C.c_void_p, C.c_longlong, C.c_float, C.c_void_p, C.c_void_p]),
     "fdgs_l1_loss_backward": (C.c_int, [C.c_void_p, C.c_void_p, C.c_longlong, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]),
 }

@@ -8,6 +8,7 @@
 #define FDGS_TILE 16                 // tile edge in pixels (reference: BLOCK_X/BLOCK_Y, RAST/cuda_rasterizer/config.h)
 #define FDGS_TILE_PIX (FDGS_TILE * FDGS_TILE)
 #define FDGS_ALIGN 256
+#define FDGS_SORT_SMEM_CAP 2048      // tile buckets up to this many instances are sorted in shared memory
 
 static inline size_t fdgs_align_up(size_t x) { return (x + (FDGS_ALIGN - 1)) & ~(size_t)(FDGS_ALIGN - 1); }
 
@@ -56,13 +57,14 @@ struct FdgsImg {           // per-pixel / per-tile
     uint32_t* tile_count;  // [T]
     uint32_t* tile_cursor; // [T]
     uint32_t* tile_start;  // [T]
-    uint32_t* scalars;     // [8]: 0 = R, 1 = max tile count
+    uint32_t* scalars;     // [8]: 0 = R, 1 = max tile count, 2 = number of tiles with more than FDGS_SORT_SMEM_CAP instances
+    uint32_t* large_tiles; // [T] ids of those tiles (arbitrary order)
     static size_t bytes(int W, int H) {
         size_t hw = (size_t)W * H;
         size_t T = (size_t)((W + FDGS_TILE - 1) / FDGS_TILE) * ((H + FDGS_TILE - 1) / FDGS_TILE);
         if (hw == 0) hw = 1;
         if (T == 0) T = 1;
-        return 2 * fdgs_align_up(hw * 4) + fdgs_align_up(T * 8) + 3 * fdgs_align_up(T * 4) + fdgs_align_up(32);
+        return 2 * fdgs_align_up(hw * 4) + fdgs_align_up(T * 8) + 4 * fdgs_align_up(T * 4) + fdgs_align_up(32);
     }
     static FdgsImg carve(void* base, int W, int H) {
         size_t hw = (size_t)W * H;
@@ -78,6 +80,7 @@ struct FdgsImg {           // per-pixel / per-tile
         s.tile_cursor = (uint32_t*)c;   c += fdgs_align_up(T * 4);
         s.tile_start = (uint32_t*)c;    c += fdgs_align_up(T * 4);
         s.scalars = (uint32_t*)c;       c += fdgs_align_up(32);
+        s.large_tiles = (uint32_t*)c;   c += fdgs_align_up(T * 4);
         return s;
     }
 };

@@ -12,7 +12,13 @@
 namespace {
 
 constexpr unsigned FULL = 0xffffffffu;
-constexpr int BATCH = 256;
+#ifndef BLEND_BWD_BATCH
+#define BLEND_BWD_BATCH 256
+#endif
+#ifndef BLEND_BWD_MINB
+#define BLEND_BWD_MINB 1
+#endif
+constexpr int BATCH = BLEND_BWD_BATCH;     // records per staged batch
 constexpr int NACC = 9;          // colour(3), mean2D(2), conic(3), opacity(1)
 #ifndef BLEND_BWD_NPX
 #define BLEND_BWD_NPX 2
@@ -114,7 +120,7 @@ __device__ __forceinline__ void warp_reduce10(float (&v)[10], int lane) {
 // NPX pixels per thread (rows py and py + 4): a warp covers an 8 x (4 NPX) sub-rectangle of the tile, so one cull test,
 // one 12-shuffle reduction and one set of shared-memory atomics serve 32 NPX pixels of a hit.
 template <int NPX>
-__global__ void __launch_bounds__(256 / NPX)
+__global__ void __launch_bounds__(256 / NPX, BLEND_BWD_MINB)
 k_blend_bwd(const uint2* __restrict__ ranges, const FdgsRecord* __restrict__ records, int W, int H,
             const float* __restrict__ bg_color, const float* __restrict__ final_Ts,
             const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpixels,

@@ -163,7 +163,7 @@ k_preprocess(int P, int D, int M,
 // K2: exclusive scan over the per-tile counts (T <= ~10^4: one CTA), tile ranges, R, max.
 __global__ void __launch_bounds__(1024)
 k_tile_scan(int T, const uint32_t* __restrict__ tile_count, uint32_t* __restrict__ tile_start,
-            uint2* __restrict__ ranges, uint32_t* __restrict__ scalars, int32_t* __restrict__ counts_host_mapped)
+            uint2* __restrict__ ranges, uint32_t* __restrict__ scalars, uint32_t* __restrict__ large_tiles)
 {
     __shared__ uint32_t warp_sums[32];
     __shared__ uint32_t carry_s, max_s;
@@ -199,6 +199,7 @@ k_tile_scan(int T, const uint32_t* __restrict__ tile_count, uint32_t* __restrict
             const uint32_t start = incl - c;
             tile_start[i] = start;
             ranges[i] = c ? make_uint2(start, incl) : make_uint2(0u, 0u);
+            if (c > FDGS_SORT_SMEM_CAP) large_tiles[atomicAdd(&scalars[2], 1u)] = (uint32_t)i;    // scalars were zeroed by the memset
         }
         __syncthreads();
         if (threadIdx.x == 1023) carry_s = incl;
@@ -209,7 +210,6 @@ k_tile_scan(int T, const uint32_t* __restrict__ tile_count, uint32_t* __restrict
     if (threadIdx.x == 0) {
         scalars[0] = carry_s;
         scalars[1] = max_s;
-        (void)counts_host_mapped;
     }
 }
 
@@ -239,58 +239,54 @@ k_scatter(int P, const int* __restrict__ radii, FdgsGeom g, int gx, int gy,
 }
 
 // ---------------------------------------------------------------------------
-// K4: per-tile segmented sort by (depth_bits, id) — equal to the reference's stable
-// radix sort of (tile | depth) keys emitted in ascending id order — fused with the
-// packing of the sorted instance records.
-// Bitonic network with +inf virtual padding; works on shared memory when the segment
-// fits (CAP elements) and in place on global memory otherwise.
+// K4: per-tile segmented sort by (depth_bits, id) — equal to the reference's stable radix sort of
+// (tile | depth) keys emitted in ascending id order (cub::DeviceRadixSort::SortPairs,
+// rasterizer_impl.cu:304-309) — fused with the packing of the sorted instance records.
+//   * buckets of up to FDGS_SORT_SMEM_CAP instances (every tile of an ordinary view): bitonic network on the
+//     64-bit keys in shared memory, +inf virtual padding, power-of-two index arithmetic, and warp-level barriers for
+//     every stage whose partners are <= 32 apart (a warp's 32 pair slots then cover one aligned run of 64 keys);
+//   * larger buckets (clustered scenes): k_tile_sort_large below — a stable LSD radix sort in global memory.
 __device__ __forceinline__ void cmpx(uint64_t* a, int i, int j) {
     const uint64_t x = a[i], y = a[j];
     if (x > y) { a[i] = y; a[j] = x; }
 }
 
-__device__ void bitonic_sort(uint64_t* a, int n) {
-    int npad = 1;
-    while (npad < n) npad <<= 1;
-    for (int k = 2; k <= npad; k <<= 1) {
-        const int hk = k >> 1;
-        for (int i = threadIdx.x; i < (npad >> 1); i += blockDim.x) {          // flip step
-            const int blk = i / hk, off = i - blk * hk;
-            const int lo = blk * k + off, hi = blk * k + k - 1 - off;
-            if (hi < n) cmpx(a, lo, hi);
-        }
-        __syncthreads();
-        for (int j = hk >> 1; j >= 1; j >>= 1) {
-            for (int i = threadIdx.x; i < (npad >> 1); i += blockDim.x) {
-                const int lo = 2 * j * (i / j) + (i % j), hi = lo + j;
+// blockDim.x threads, n <= 2 * MAXPAIRS keys.  `wide` stages (partner distance >= 64) need block barriers.
+__device__ __forceinline__ void bitonic_sort_smem(uint64_t* a, int n) {
+    int lg = 1;
+    while ((1 << lg) < n) ++lg;                                   // npad = 1 << lg >= 2
+    const int half = 1 << (lg - 1);
+    bool prev_wide = true;                                         // the load into shared memory was a block-wide step
+    for (int lk = 1; lk <= lg; ++lk) {                             // k = 1 << lk
+        const int lhk = lk - 1, hk = 1 << lhk, k = 1 << lk;
+        {   // flip step: (blk * k + off, blk * k + k - 1 - off), off < k / 2
+            const bool wide = hk > 32;
+            if (wide || prev_wide) __syncthreads(); else __syncwarp();
+            for (int i = threadIdx.x; i < half; i += blockDim.x) {
+                const int off = i & (hk - 1);
+                const int lo = ((i >> lhk) << lk) + off, hi = lo + (k - 1 - 2 * off);
                 if (hi < n) cmpx(a, lo, hi);
             }
-            __syncthreads();
+            prev_wide = wide;
+        }
+        for (int lj = lhk - 1; lj >= 0; --lj) {                    // j = 1 << lj
+            const int j = 1 << lj;
+            const bool wide = j > 32;
+            if (wide || prev_wide) __syncthreads(); else __syncwarp();
+            for (int i = threadIdx.x; i < half; i += blockDim.x) {
+                const int lo = ((i >> lj) << (lj + 1)) + (i & (j - 1)), hi = lo + j;
+                if (hi < n) cmpx(a, lo, hi);
+            }
+            prev_wide = wide;
         }
     }
+    __syncthreads();
 }
 
-template <int CAP>
-__global__ void __launch_bounds__(256)
-k_tile_sort(const uint2* __restrict__ ranges, uint64_t* __restrict__ bucket, FdgsGeom g,
-            const float* __restrict__ colors, FdgsRecord* __restrict__ records,
-            uint64_t* __restrict__ keys_out, uint32_t* __restrict__ point_list_out)
-{
-    extern __shared__ __align__(16) uint64_t skeys[];
-    const uint32_t tile = blockIdx.x;
-    const uint2 rg = ranges[tile];
-    const int n = (int)(rg.y - rg.x);
-    if (n == 0) return;
-    uint64_t* seg = bucket + rg.x;
-    uint64_t* a;
-    if (n <= CAP) {
-        for (int i = threadIdx.x; i < n; i += blockDim.x) skeys[i] = seg[i];
-        __syncthreads();
-        a = skeys;
-    } else {
-        a = seg;     // rare: in-place on global memory (single CTA, block barriers order the accesses)
-    }
-    if (n > 1) bitonic_sort(a, n);
+// sorted keys a[0..n) of `tile` -> packed blend records (+ the reference-layout parity lists)
+__device__ __forceinline__ void pack_records(const uint64_t* a, int n, uint32_t tile, uint32_t first, const FdgsGeom& g,
+                                             const float* __restrict__ colors, FdgsRecord* __restrict__ records,
+                                             uint64_t* __restrict__ keys_out, uint32_t* __restrict__ point_list_out) {
     for (int i = threadIdx.x; i < n; i += blockDim.x) {
         const uint64_t k = a[i];
         const uint32_t id = (uint32_t)k;
@@ -302,11 +298,102 @@ k_tile_sort(const uint2* __restrict__ ranges, uint64_t* __restrict__ bucket, Fdg
         rec.r = colors[3 * (size_t)id]; rec.g = colors[3 * (size_t)id + 1]; rec.b = colors[3 * (size_t)id + 2];
         // cull threshold: a pixel can only pass alpha >= 1/255 if power >= ln(1/(255*opacity)).
         rec.cull = (co.w <= 0.f) ? 0.f : -logf(255.0f * co.w);   // NaN opacity => NaN => never culled
-        float4* dst = reinterpret_cast<float4*>(records + rg.x + i);
+        float4* dst = reinterpret_cast<float4*>(records + first + i);
         const float4* src = reinterpret_cast<const float4*>(&rec);
         dst[0] = src[0]; dst[1] = src[1]; dst[2] = src[2];
-        if (keys_out) keys_out[rg.x + i] = ((uint64_t)tile << 32) | (k >> 32);
-        if (point_list_out) point_list_out[rg.x + i] = id;
+        if (keys_out) keys_out[first + i] = ((uint64_t)tile << 32) | (k >> 32);
+        if (point_list_out) point_list_out[first + i] = id;
+    }
+}
+
+__global__ void __launch_bounds__(256)
+k_tile_sort(const uint2* __restrict__ ranges, const uint64_t* __restrict__ bucket, FdgsGeom g,
+            const float* __restrict__ colors, FdgsRecord* __restrict__ records,
+            uint64_t* __restrict__ keys_out, uint32_t* __restrict__ point_list_out)
+{
+    __shared__ __align__(16) uint64_t skeys[FDGS_SORT_SMEM_CAP];
+    const uint32_t tile = blockIdx.x;
+    const uint2 rg = ranges[tile];
+    const int n = (int)(rg.y - rg.x);
+    if (n == 0 || n > FDGS_SORT_SMEM_CAP) return;                  // large buckets: k_tile_sort_large
+    const uint64_t* seg = bucket + rg.x;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) skeys[i] = seg[i];
+    if (n > 1) bitonic_sort_smem(skeys, n); else __syncthreads();
+    pack_records(skeys, n, tile, rg.x, g, colors, records, keys_out, point_list_out);
+}
+
+// Buckets above the shared-memory cap: one CTA of 1024 threads per large tile (persistent over the device-built list),
+// stable LSD radix sort with 8-bit digits on the 64-bit (depth, id) key, ping-ponging between the bucket segment and the
+// tile's own (not yet written) slice of the record array, which is 6x as large.  A pass whose digit is the same for
+// every key (the id bytes above log2 P, the exponent byte of the depth) is skipped after its histogram.
+constexpr int LARGE_THREADS = 1024;
+__global__ void __launch_bounds__(LARGE_THREADS)
+k_tile_sort_large(const uint2* __restrict__ ranges, const uint32_t* __restrict__ large_tiles, const uint32_t* __restrict__ scalars,
+                  uint64_t* __restrict__ bucket, FdgsGeom g, const float* __restrict__ colors, FdgsRecord* __restrict__ records,
+                  uint64_t* __restrict__ keys_out, uint32_t* __restrict__ point_list_out)
+{
+    __shared__ uint32_t wc[32][256];          // per-warp digit counts of one 1024-key chunk -> exclusive prefix over warps
+    __shared__ uint32_t hist[256], base[256];
+    __shared__ uint32_t wsum[8];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t nlarge = scalars[2];
+    for (uint32_t li = blockIdx.x; li < nlarge; li += gridDim.x) {
+        const uint32_t tile = large_tiles[li];
+        const uint2 rg = ranges[tile];
+        const int n = (int)(rg.y - rg.x);
+        uint64_t* src = bucket + rg.x;
+        uint64_t* dst = reinterpret_cast<uint64_t*>(records + rg.x);          // n * 48 bytes, 16-byte aligned
+        for (int pass = 0; pass < 8; ++pass) {
+            const int shift = pass * 8;
+            if (tid < 256) hist[tid] = 0;
+            __syncthreads();
+            for (int i = tid; i < n; i += LARGE_THREADS) atomicAdd(&hist[(uint32_t)(src[i] >> shift) & 255u], 1u);
+            __syncthreads();
+            const int trivial = __syncthreads_or(tid < 256 && hist[tid] == (uint32_t)n);
+            if (trivial) continue;                                             // uniform: every thread sees the same value
+            if (tid < 256) {                                                   // exclusive scan of the 256 bins
+                const uint32_t h = hist[tid];
+                uint32_t v = h;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) { const uint32_t t = __shfl_up_sync(FULL, v, o); if (lane >= o) v += t; }
+                if (lane == 31) wsum[warp] = v;
+                __syncwarp();
+                asm volatile("bar.sync 2, 256;" ::: "memory");
+                uint32_t carry = 0;
+                for (int w = 0; w < warp; ++w) carry += wsum[w];
+                base[tid] = carry + v - h;
+            }
+            __syncthreads();
+            for (int c0 = 0; c0 < n; c0 += LARGE_THREADS) {
+#pragma unroll
+                for (int m = 0; m < 8; ++m) (&wc[0][0])[tid + LARGE_THREADS * m] = 0;
+                const int i = c0 + tid;
+                const bool valid = i < n;
+                const uint64_t key = valid ? src[i] : 0ull;
+                const uint32_t d = (uint32_t)(key >> shift) & 255u;
+                const unsigned peers = __match_any_sync(FULL, valid ? d : (0x1000u + (uint32_t)lane));
+                const uint32_t rank = __popc(peers & ((1u << lane) - 1u));
+                __syncthreads();
+                if (valid && rank == 0) wc[warp][d] = __popc(peers);
+                __syncthreads();
+                uint32_t tot = 0;
+                if (tid < 256) {
+                    for (int w = 0; w < 32; ++w) { const uint32_t t = wc[w][tid]; wc[w][tid] = tot; tot += t; }
+                }
+                __syncthreads();
+                if (valid) dst[base[d] + wc[warp][d] + rank] = key;
+                __syncthreads();
+                if (tid < 256) base[tid] += tot;
+            }
+            __syncthreads();
+            uint64_t* t = src; src = dst; dst = t;
+        }
+        if (src != bucket + rg.x) {            // the sorted keys sit in the record slice that packing overwrites: move them
+            for (int i = tid; i < n; i += LARGE_THREADS) bucket[rg.x + i] = src[i];
+            __syncthreads();
+        }
+        pack_records(bucket + rg.x, n, tile, rg.x, g, colors, records, keys_out, point_list_out);
+        __syncthreads();
     }
 }
 
@@ -582,7 +669,7 @@ int fdgs_raster_forward_plan(const FdgsRasterForward* a, void* stream_) {
     }
     FDGS_LAUNCH_CHECK(a->debug, stream);
     { FDGS_PROF("k_tile_scan", stream);
-    k_tile_scan<<<1, 1024, 0, stream>>>(T, im.tile_count, im.tile_start, im.ranges, im.scalars, nullptr);
+    k_tile_scan<<<1, 1024, 0, stream>>>(T, im.tile_count, im.tile_start, im.ranges, im.scalars, im.large_tiles);
     }
     FDGS_LAUNCH_CHECK(a->debug, stream);
     FDGS_CUDA(cudaMemcpyAsync(a->counts_host, im.scalars, 2 * sizeof(int32_t), cudaMemcpyDeviceToHost, stream));
@@ -613,22 +700,14 @@ int fdgs_raster_forward_render(const FdgsRasterForward* a, int64_t R, void* stre
         }
         FDGS_LAUNCH_CHECK(a->debug, stream);
         const float* colors = a->colors_precomp ? a->colors_precomp : g.rgb;
-        const int maxc = a->counts_host[1];
-        if (maxc <= 2048) {
-            { FDGS_PROF("k_tile_sort", stream);
-            k_tile_sort<2048><<<T, 256, 2048 * 8, stream>>>(im.ranges, bn.bucket, g, colors, bn.records, a->keys_out, a->point_list_out);
-            }
-        } else if (maxc <= 8192) {
-            // function attributes are per device: set unconditionally (one driver call), never cached per process
-            FDGS_CUDA(cudaFuncSetAttribute(k_tile_sort<8192>, cudaFuncAttributeMaxDynamicSharedMemorySize, 8192 * 8));
-            { FDGS_PROF("k_tile_sort", stream);
-            k_tile_sort<8192><<<T, 256, 8192 * 8, stream>>>(im.ranges, bn.bucket, g, colors, bn.records, a->keys_out, a->point_list_out);
-            }
-        } else {
-            FDGS_CUDA(cudaFuncSetAttribute(k_tile_sort<28672>, cudaFuncAttributeMaxDynamicSharedMemorySize, 28672 * 8));
-            { FDGS_PROF("k_tile_sort", stream);
-            k_tile_sort<28672><<<T, 256, 28672 * 8, stream>>>(im.ranges, bn.bucket, g, colors, bn.records, a->keys_out, a->point_list_out);
-            }
+        { FDGS_PROF("k_tile_sort", stream);
+        k_tile_sort<<<T, 256, 0, stream>>>(im.ranges, bn.bucket, g, colors, bn.records, a->keys_out, a->point_list_out);
+        }
+        FDGS_LAUNCH_CHECK(a->debug, stream);
+        if (a->counts_host[1] > FDGS_SORT_SMEM_CAP) {      // some tile bucket is larger than the shared-memory cap
+            FDGS_PROF("k_tile_sort_large", stream);
+            k_tile_sort_large<<<148, LARGE_THREADS, 0, stream>>>(im.ranges, im.large_tiles, im.scalars, bn.bucket, g, colors,
+                                                                 bn.records, a->keys_out, a->point_list_out);
         }
         FDGS_LAUNCH_CHECK(a->debug, stream);
     }

@@ -143,6 +143,7 @@ def build_scene(cfg_name, impl, dev, views, points, make_gts=True, n_cams=None, 
         g = synth.make_gaussians(cfg["P"], extent=cfg["extent"], logscale=cfg["logscale"], seed=0, device=dev)
         pc = synth.SynthGaussians(g, net).to(dev)
         net.deformation_net.set_aabb(pc._xyz.detach().max(0).values.tolist(), pc._xyz.detach().min(0).values.tolist())
+        net.to(dev)      # the reference's set_aabb re-creates the aabb Parameter on the CPU (scene/hexplane.py:118-122)
     B = cfg["views"]
     ncam = n_cams if n_cams else B
     cams = synth.make_cameras(cfg["W"], cfg["H"], cfg["fovx"], ncam, device=dev, time_den=time_den)

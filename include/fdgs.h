@@ -313,6 +313,61 @@ int fdgs_activate_backward(const FdgsActivateBackward* a, void* stream);
 int fdgs_l1_loss_forward(const float* a, const float* b, long long n, float scale, float* loss, void* stream);
 int fdgs_l1_loss_backward(const float* a, const float* b, long long n, float scale, const float* g, float* d_a, void* stream);
 
+/* ---- HexPlane regularisers ----------------------------------------------------------------------------
+ * scene/gaussian_model.py:538-577 compute_regulation = plane_tv_weight * _plane_regulation() + time_smoothness_weight *
+ * _time_regulation() + l1_time_planes_weight * _l1_regulation(), with scene/regulation.py:22-28 compute_plane_smoothness
+ * (mean squared second difference along a plane's H axis) on planes {0,1,3} (spatial) and {2,4,5} (space-time) of every
+ * level, and mean |1 - plane| on the space-time planes.  One kernel computes the value AND adds its gradient:
+ *   *loss      += the regulariser value                                  (DEVICE scalar, caller-zeroed; NULL = skip)
+ *   d_planes   += (*grad_scale) * d value / d plane                      (NULL entry = no gradient for that plane;
+ *                                                                         grad_scale NULL = 1, as train.py:251-254 adds
+ *                                                                         tv_loss to the loss with weight 1)
+ * Plane k of level l is [channels, H_k, W_k] with W_k = res[l][first], H_k = res[l][second] of the pair order
+ * (0,1),(0,2),(0,3),(1,2),(1,3),(2,3) — the layout FdgsDeformNet.planes uses.                                            */
+typedef struct FdgsPlaneReg {
+    int32_t levels, channels;
+    int32_t res[FDGS_MAX_LEVELS][4];
+    const float* planes[FDGS_MAX_LEVELS][6];
+    float* d_planes[FDGS_MAX_LEVELS][6];
+    float plane_tv_weight, time_smoothness_weight, l1_time_planes_weight;
+    const float* grad_scale;
+    float* loss;
+} FdgsPlaneReg;
+int fdgs_plane_regulation(const FdgsPlaneReg* a, void* stream);
+/* compute_plane_smoothness (scene/regulation.py:22-28) of ONE plane [C,H,W]: *loss += weight * mean(second difference^2),
+ * d_plane += (*grad_scale) * its gradient (either may be NULL).                                                         */
+int fdgs_plane_smoothness(const float* plane, float* d_plane, int C, int H, int W, float weight, const float* grad_scale,
+                          float* loss, void* stream);
+
+/* ---- fused Adam + densification statistics -----------------------------------------------------------
+ * torch.optim.Adam(l, lr=0.0, eps=1e-15) as scene/gaussian_model.py:172-184 builds it (betas (0.9, 0.999), no weight
+ * decay, no amsgrad), one launch for any number of tensors, each with its own lr and step count (param groups xyz,
+ * deformation, grid, f_dc, f_rest, opacity, scaling, rotation).  The FP32 operation order is that of torch's foreach
+ * implementation, so parameters and both moments are BIT-IDENTICAL to torch.optim.Adam.step() on the same inputs.
+ * `step` is the step count AFTER this update (>= 1).  zero_grad != 0 also clears the gradients in the same pass.          */
+typedef struct FdgsAdamTensor {
+    float* param;
+    const float* grad;
+    float* exp_avg;
+    float* exp_avg_sq;
+    int64_t n;
+    double lr;                      /* the group's lr as the Python double torch would divide by the bias correction */
+    int64_t step;
+} FdgsAdamTensor;
+typedef struct FdgsAdamStep {
+    int32_t ntensors;
+    int32_t zero_grad;
+    double beta1, beta2, eps;
+    const FdgsAdamTensor* t;        /* HOST array of ntensors entries */
+} FdgsAdamStep;
+int fdgs_adam_step(const FdgsAdamStep* a, void* stream);
+
+/* train.py:346-349 + scene/gaussian_model.py:521-523: for the visible Gaussians of an iteration (visible[i] != 0, or
+ * radii[i] > 0 when visible is NULL)   max_radii2D[i] = max(max_radii2D[i], radii[i]),
+ * xyz_gradient_accum[i] += || viewspace_grad[i, :2] ||,  denom[i] += 1.   Any of the three outputs may be NULL.           */
+int fdgs_densify_stats(int P, const int32_t* radii, const uint8_t* visible, const float* viewspace_grad /* [P,3] */,
+                       float* max_radii2D, float* xyz_gradient_accum, float* denom, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

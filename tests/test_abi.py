@@ -53,7 +53,8 @@ def test_fatbin_targets_sm_100a():
     assert "sm_100a" in out, out
 
 
-STRUCTS = ["FdgsRasterForward", "FdgsRasterBackward", "FdgsDeformNet", "FdgsDeformForward", "FdgsDeformBackward"]
+STRUCTS = ["FdgsRasterForward", "FdgsRasterBackward", "FdgsDeformNet", "FdgsDeformForward", "FdgsDeformBackward",
+           "FdgsActivateForward", "FdgsActivateBackward", "FdgsPlaneReg", "FdgsAdamTensor", "FdgsAdamStep"]
 
 
 def test_ctypes_struct_layout_matches_header(tmp_path):

@@ -12,7 +12,7 @@ and in the reference's own GPU ops alike (measured against an FP64 arbiter: 1-4 
 both, profiles/r01_deform_relu_flips.log).  The >= 20k-point comparisons are flip-AWARE rather than loose: an
 FP64 copy of the reference net flags the points with a pre-activation within 2e-5 of zero (about 1 % of
 them, ref_port.relu_danger_mask), their upstream gradient is zeroed on both sides, and every gradient is
-then held to the plain 2e-5 max-norm bar plus an L2 bar of 1e-5.  Observed values: profiles/r02_parity_deform.log."""
+then held to the plain 2e-5 max-norm bar plus an L2 bar of 3e-5.  Observed values: profiles/r02_parity_deform.log."""
 import os
 
 import numpy as np
@@ -113,7 +113,7 @@ def _run(net, inp, t, ws):
     return outs, leaves
 
 
-L2_TOL = 1e-5
+L2_TOL = 3e-5      # 2x the worst value observed at the BASELINE nets (1.3e-5, feature_out.0.weight at 20k points)
 _worst = {}
 
 
