@@ -143,6 +143,7 @@ SYMBOLS = {
     "fdgs_raster_bin_bytes": (C.c_size_t, [C.c_int64]),
     "fdgs_raster_forward_plan": (C.c_int, [C.POINTER(FdgsRasterForward), C.c_void_p]),
     "fdgs_raster_forward_render": (C.c_int, [C.POINTER(FdgsRasterForward), C.c_int64, C.c_void_p]),
+    "fdgs_raster_forward": (C.c_int, [C.POINTER(FdgsRasterForward), C.c_int64, C.c_void_p]),
     "fdgs_raster_copy_ranges": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
     "fdgs_raster_count_pairs": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
     "fdgs_raster_backward": (C.c_int, [C.POINTER(FdgsRasterBackward), C.c_void_p]),

@@ -20,6 +20,7 @@
 #include "umma.cuh"
 #include "prof.cuh"
 #include <cstdio>
+#include <cstdlib>
 
 namespace fdgs_deform_tc_bwd {
 using namespace fdgs_deform;
@@ -929,6 +930,10 @@ struct WJob {
     int slices;                              // CTAs sharing this job
     int blkA, blkB;                          // operand in the blocked scratch layout [row/32][col/4][row%32][4]: the 32 rows
                                              // of a stage are one contiguous run of 32*ld floats (one bulk copy)
+    int cuda_core;                           // nb <= 4 (the output layers of the pos / scale / rotation / opacity heads): the
+                                             // staging warps accumulate C on the CUDA cores straight from the raw stage —
+                                             // 4 nb FMAs per loaded float4 instead of the TF32 split, two tile stores and an
+                                             // MMA padded to N = 16 (the job then costs about a third of a tensor-core one)
 };
 constexpr int MAXJOBS = 2 * FDGS_NUM_HEADS + 1;
 struct WArgs { WJob j[MAXJOBS]; int njobs; long long rows; };   // rows = Pp (multiple of 128)
@@ -965,6 +970,7 @@ k_deform_bwd_weights(WArgs args)
     __shared__ __align__(8) uint64_t bars[WB_COUNT + 1];
     __shared__ uint32_t tmem_slot;
     __shared__ float csumA[128], csumB[128];
+    __shared__ float cc_acc[128 * 4];          // C of a CUDA-core job (nb <= 4)
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 #ifdef FDGS_PHASE_TIMING
     const long long t_start_ = clock64();
@@ -993,6 +999,7 @@ k_deform_bwd_weights(WArgs args)
         fence_mbar_init();
     }
     if (tid < 128) { csumA[tid] = 0.f; csumB[tid] = 0.f; }
+    for (int e = tid; e < 128 * 4; e += W_THREADS) cc_acc[e] = 0.f;
     if (warp == NSW) tmem_alloc(&tmem_slot, 128);
     tc_fence_before();
     __syncthreads();
@@ -1027,7 +1034,7 @@ k_deform_bwd_weights(WArgs args)
         // ===== MMA issuer ==================================================================================
         // Single-thread loop on purpose: this kernel is shared-memory bound, and the elected-lane issuer of the data
         // kernels (12 MMAs back to back) bunches the operand fetches against the staging warps: 690 -> 761 us, measured.
-        if (lane == 0) {
+        if (lane == 0 && !J.cuda_core) {
             const uint32_t idesc = make_idesc_tf32(128, N16, 1, 1);
             uint32_t g = 0;
             for (long long s = s_begin; s < s_end; ++s, ++g) {
@@ -1088,6 +1095,82 @@ k_deform_bwd_weights(WArgs args)
         float sa[4] = {0.f, 0.f, 0.f, 0.f}, sb[4] = {0.f, 0.f, 0.f, 0.f};
         const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
         uint32_t g = 0;
+        if (J.cuda_core) {
+            // ---- C[m][n] = sum_p A[p][m] B[p][n] for n < nb <= 4 on the CUDA cores -------------------------------------
+            // A thread meets every (row, its 4 columns) of the slice exactly once; threads with column group 0 also
+            // take the column sums of B (the bias gradient).
+            float acc[4][4];
+#pragma unroll
+            for (int c = 0; c < 4; ++c)
+#pragma unroll
+                for (int o = 0; o < 4; ++o) acc[c][o] = 0.f;
+            for (long long s = s_begin; s < s_end; ++s, ++g) {
+                const uint32_t rslot = g % RSTAGES;
+                const float* rawA = raw0 + (size_t)rslot * raw_floats;
+                const float* rawB = rawA + rawA_f;
+                mbar_wait(&bars[WB_RFULL + rslot], (g / RSTAGES) & 1);
+#pragma unroll
+                for (int i = 0; i < NI; ++i) {
+                    const float4 a4 = onA ? *reinterpret_cast<const float4*>(rawA + (cgA * 32 + rowA[i]) * 4) : z4;
+                    float b[4] = {0.f, 0.f, 0.f, 0.f};
+                    if (s < fullB) {
+                        const float* r = rawB + rowA[i] * J.ldb;
+#pragma unroll
+                        for (int o = 0; o < 4; ++o) if (o < J.nb) b[o] = r[o];
+                    } else {
+                        const long long row = s * WK + rowA[i];
+                        if (row < J.rowsB) {
+#pragma unroll
+                            for (int o = 0; o < 4; ++o) if (o < J.nb) b[o] = J.B[(size_t)row * J.ldb + o];
+                        }
+                    }
+                    const float av[4] = {a4.x, a4.y, a4.z, a4.w};
+#pragma unroll
+                    for (int c = 0; c < 4; ++c)
+#pragma unroll
+                        for (int o = 0; o < 4; ++o) acc[c][o] = fmaf(av[c], b[o], acc[c][o]);
+                    if (wantB && cgA == 0) { sb[0] += b[0]; sb[1] += b[1]; sb[2] += b[2]; sb[3] += b[3]; }
+                }
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&bars[WB_REMPTY + rslot]);
+            }
+            // rows of a column group are spread over the 8 lanes of a quarter-warp and over warps w, w + 8
+#pragma unroll
+            for (int c = 0; c < 4; ++c)
+#pragma unroll
+                for (int o = 0; o < 4; ++o) {
+                    float v = acc[c][o];
+                    v += __shfl_xor_sync(0xffffffffu, v, 1);
+                    v += __shfl_xor_sync(0xffffffffu, v, 2);
+                    v += __shfl_xor_sync(0xffffffffu, v, 4);
+                    acc[c][o] = v;
+                }
+            if (wantB && cgA == 0) {
+#pragma unroll
+                for (int o = 0; o < 4; ++o) {
+                    float v = sb[o];
+                    v += __shfl_xor_sync(0xffffffffu, v, 1);
+                    v += __shfl_xor_sync(0xffffffffu, v, 2);
+                    v += __shfl_xor_sync(0xffffffffu, v, 4);
+                    if (row8 == 0 && o < J.nb) atomicAdd(&csumB[o], v);
+                }
+            }
+            if (row8 == 0 && onA) {
+#pragma unroll
+                for (int c = 0; c < 4; ++c)
+#pragma unroll
+                    for (int o = 0; o < 4; ++o) if (o < J.nb) atomicAdd(&cc_acc[(cgA * 4 + c) * 4 + o], acc[c][o]);
+            }
+            asm volatile("bar.sync 1, %0;" ::"n"(NSW * 32) : "memory");
+            if (s_end > s_begin) {
+                for (int e = tid; e < 128 * 4; e += NSW * 32) {
+                    const int m = e >> 2, n = e & 3;
+                    if (m < J.ma && n < J.nb)
+                        atomicAdd(J.transposed ? &J.C[(size_t)n * J.ldc + m] : &J.C[(size_t)m * J.ldc + n], cc_acc[e]);
+                }
+                if (wantB && tid < J.nb) atomicAdd(&J.biasB[tid], csumB[tid]);
+            }
+        } else {
         for (long long s = s_begin; s < s_end; ++s, ++g) {
             const uint32_t rslot = g % RSTAGES, tslot = g % TSTAGES;
             const float* rawA = raw0 + (size_t)rslot * raw_floats;
@@ -1181,6 +1264,7 @@ k_deform_bwd_weights(WArgs args)
                 }
             }
         }
+        }   // tensor-core path
     }
     tc_fence_before();
     __syncthreads();
@@ -1293,15 +1377,18 @@ int backward(const Layout& lo, const FdgsDeformBackward* a, const float* packed,
     int nj = 0;
     float* dw1[FDGS_NUM_HEADS] = {a->d_head_w1[0], a->d_head_w1[1], a->d_head_w1[2], a->d_head_w1[3], a->d_head_w1[4]};
     double cost[MAXJOBS];
+    // per-stage cost of a CUDA-core dW2 job relative to a tensor-core dW1 job (FDGS_DW2_COST overrides, for tuning)
+    const double cc_cost = getenv("FDGS_DW2_COST") ? atof(getenv("FDGS_DW2_COST")) : 0.4;
     for (int j = 0; j < plan.nheads; ++j) {
         const int h = plan.heads[j];
         const int NO = head_out(h);
-        wa.j[nj] = WJob{io.S_GZ[j], Wn, Wn, (int)plan.Pp, io.S_H, Wn, Wn, (int)plan.Pp, dw1[h], Wn, 0, a->d_head_b1[h], nullptr, 1, 1, 1};
+        wa.j[nj] = WJob{io.S_GZ[j], Wn, Wn, (int)plan.Pp, io.S_H, Wn, Wn, (int)plan.Pp, dw1[h], Wn, 0, a->d_head_b1[h], nullptr, 1, 1, 1, 0};
         cost[nj++] = 1.0;                                 // relative per-stage cost, measured (cycles/stage 1750 : 2050 : 1530)
-        wa.j[nj] = WJob{io.S_RZ[j], Wn, Wn, (int)plan.Pp, gsrc[h], NO, NO, a->P, a->d_head_w2[h], Wn, 1, nullptr, a->d_head_b2[h], 1, 1, 0};
-        cost[nj++] = 0.87;
+        const int cc = (NO <= 4 && !getenv("FDGS_DW2_TENSOR")) ? 1 : 0;
+        wa.j[nj] = WJob{io.S_RZ[j], Wn, Wn, (int)plan.Pp, gsrc[h], NO, NO, a->P, a->d_head_w2[h], Wn, 1, nullptr, a->d_head_b2[h], 1, 1, 0, cc};
+        cost[nj++] = cc ? cc_cost : 0.87;
     }
-    wa.j[nj] = WJob{io.S_GH, Wn, Wn, (int)plan.Pp, io.S_F, F, F, (int)plan.Pp, a->d_trunk_w[0], F, 0, a->d_trunk_b[0], nullptr, 1, 1, 1};
+    wa.j[nj] = WJob{io.S_GH, Wn, Wn, (int)plan.Pp, io.S_F, F, F, (int)plan.Pp, a->d_trunk_w[0], F, 0, a->d_trunk_b[0], nullptr, 1, 1, 1, 0};
     cost[nj++] = 0.87;
     wa.njobs = nj; wa.rows = plan.Pp;
     // distribute the SMs over the jobs in proportion to the bytes they stream

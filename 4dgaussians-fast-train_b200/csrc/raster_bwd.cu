@@ -12,11 +12,14 @@
 namespace {
 
 constexpr unsigned FULL = 0xffffffffu;
+// 128 records per staged batch and 6 resident CTAs per SM (72 registers): measured 621 us per DyNeRF view against 711
+// (256 / no bound, 73 registers but 34 KB of shared memory per CTA), 714 (128 / no bound: 90 registers), 755 (128 / 8 CTAs:
+// 64 registers) on the same B200 (profiles/r02_ab_blend_bwd.txt)
 #ifndef BLEND_BWD_BATCH
-#define BLEND_BWD_BATCH 256
+#define BLEND_BWD_BATCH 128
 #endif
 #ifndef BLEND_BWD_MINB
-#define BLEND_BWD_MINB 1
+#define BLEND_BWD_MINB 6
 #endif
 constexpr int BATCH = BLEND_BWD_BATCH;     // records per staged batch
 constexpr int NACC = 9;          // colour(3), mean2D(2), conic(3), opacity(1)

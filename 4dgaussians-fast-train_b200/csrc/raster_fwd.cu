@@ -163,7 +163,7 @@ k_preprocess(int P, int D, int M,
 // K2: exclusive scan over the per-tile counts (T <= ~10^4: one CTA), tile ranges, R, max.
 __global__ void __launch_bounds__(1024)
 k_tile_scan(int T, const uint32_t* __restrict__ tile_count, uint32_t* __restrict__ tile_start,
-            uint2* __restrict__ ranges, uint32_t* __restrict__ scalars, uint32_t* __restrict__ large_tiles)
+            uint2* __restrict__ ranges, uint32_t* __restrict__ scalars, uint32_t* __restrict__ large_tiles, uint32_t cap)
 {
     __shared__ uint32_t warp_sums[32];
     __shared__ uint32_t carry_s, max_s;
@@ -210,6 +210,14 @@ k_tile_scan(int T, const uint32_t* __restrict__ tile_count, uint32_t* __restrict
     if (threadIdx.x == 0) {
         scalars[0] = carry_s;
         scalars[1] = max_s;
+        scalars[3] = carry_s > cap ? 1u : 0u;
+    }
+    // One-shot mode (fdgs_raster_forward): the caller sized the instance workspace from an ESTIMATE of R.  When the real
+    // count does not fit, every tile range is emptied and the large-tile list cleared, so that the scatter / sort / blend
+    // kernels queued behind this one touch nothing; the host finds scalars[3] = 1 when it reads the counts back.
+    if (carry_s > cap) {
+        for (int i = threadIdx.x; i < T; i += 1024) ranges[i] = make_uint2(0u, 0u);
+        if (threadIdx.x == 0) scalars[2] = 0u;
     }
 }
 
@@ -219,8 +227,9 @@ k_tile_scan(int T, const uint32_t* __restrict__ tile_count, uint32_t* __restrict
 __global__ void __launch_bounds__(256)
 k_scatter(int P, const int* __restrict__ radii, FdgsGeom g, int gx, int gy,
           const uint32_t* __restrict__ tile_start, uint32_t* __restrict__ tile_cursor,
-          uint64_t* __restrict__ bucket)
+          uint64_t* __restrict__ bucket, const uint32_t* __restrict__ scalars)
 {
+    if (scalars[3]) return;                        // instance workspace too small (one-shot mode): see k_tile_scan
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     int x0 = 0, y0 = 0, x1 = 0, y1 = 0;
     uint32_t dbits = 0;
@@ -644,12 +653,9 @@ size_t fdgs_raster_geom_bytes(int P) { return FdgsGeom::bytes(P); }
 size_t fdgs_raster_img_bytes(int W, int H) { return FdgsImg::bytes(W, H); }
 size_t fdgs_raster_bin_bytes(int64_t R) { return FdgsBin::bytes(R); }
 
-int fdgs_raster_forward_plan(const FdgsRasterForward* a, void* stream_) {
-    int rc = check_forward_args(a);
-    if (rc) return rc;
-    cudaStream_t stream = (cudaStream_t)stream_;
-    a->counts_host[0] = 0; a->counts_host[1] = 0;
-    if (a->P == 0) return FDGS_OK;
+// K1 + K2 (preprocess with the tile histogram, tile scan).  cap: capacity (instances) of the workspace the render stage will
+// use, or 0xffffffff when the caller sizes it from the exact count afterwards.
+static int launch_plan(const FdgsRasterForward* a, uint32_t cap, cudaStream_t stream) {
     const int gx = (a->W + FDGS_TILE - 1) / FDGS_TILE, gy = (a->H + FDGS_TILE - 1) / FDGS_TILE;
     const int T = gx * gy;
     FdgsGeom g = FdgsGeom::carve(a->geom_ws, a->P);
@@ -669,34 +675,26 @@ int fdgs_raster_forward_plan(const FdgsRasterForward* a, void* stream_) {
     }
     FDGS_LAUNCH_CHECK(a->debug, stream);
     { FDGS_PROF("k_tile_scan", stream);
-    k_tile_scan<<<1, 1024, 0, stream>>>(T, im.tile_count, im.tile_start, im.ranges, im.scalars, im.large_tiles);
+    k_tile_scan<<<1, 1024, 0, stream>>>(T, im.tile_count, im.tile_start, im.ranges, im.scalars, im.large_tiles, cap);
     }
     FDGS_LAUNCH_CHECK(a->debug, stream);
-    FDGS_CUDA(cudaMemcpyAsync(a->counts_host, im.scalars, 2 * sizeof(int32_t), cudaMemcpyDeviceToHost, stream));
-    FDGS_CUDA(cudaStreamSynchronize(stream));
+    // counts_host: [0] = R, [1] = largest tile bucket, [2] = tiles above the shared-memory sort cap, [3] = overflow flag
+    FDGS_CUDA(cudaMemcpyAsync(a->counts_host, im.scalars, 4 * sizeof(int32_t), cudaMemcpyDeviceToHost, stream));
     return FDGS_OK;
 }
 
-int fdgs_raster_forward_render(const FdgsRasterForward* a, int64_t R, void* stream_) {
-    int rc = check_forward_args(a);
-    if (rc) return rc;
-    cudaStream_t stream = (cudaStream_t)stream_;
-    const size_t HW = (size_t)a->W * a->H;
-    if (a->P == 0) {   // reference returns zero-filled outputs (rasterize_points.cu:68-82)
-        FDGS_CUDA(cudaMemsetAsync(a->out_color, 0, 3 * HW * sizeof(float), stream));
-        FDGS_CUDA(cudaMemsetAsync(a->out_depth, 0, HW * sizeof(float), stream));
-        return FDGS_OK;
-    }
-    if (R < 0) return FDGS_E_BADARG;
-    if (R > 0 && (!a->bin_ws || a->bin_bytes < FdgsBin::bytes(R))) return FDGS_E_WORKSPACE;
+// K3 - K7 (bucket scatter, segmented sort + record packing, blend).  cap: instances bin_ws was carved for.
+// large: 1 = some bucket is above the shared-memory cap, 0 = none, -1 = unknown on the host (launch the large-bucket kernel
+// anyway: it reads the device-side list and exits when that is empty).
+static int launch_render(const FdgsRasterForward* a, int64_t cap, int large, cudaStream_t stream) {
     const int gx = (a->W + FDGS_TILE - 1) / FDGS_TILE, gy = (a->H + FDGS_TILE - 1) / FDGS_TILE;
     const int T = gx * gy;
     FdgsGeom g = FdgsGeom::carve(a->geom_ws, a->P);
     FdgsImg im = FdgsImg::carve(a->img_ws, a->W, a->H);
-    FdgsBin bn = FdgsBin::carve(a->bin_ws, R);
-    if (R > 0) {
+    FdgsBin bn = FdgsBin::carve(a->bin_ws, cap);
+    if (cap > 0) {
         { FDGS_PROF("k_scatter", stream);
-        k_scatter<<<(a->P + 255) / 256, 256, 0, stream>>>(a->P, a->radii, g, gx, gy, im.tile_start, im.tile_cursor, bn.bucket);
+        k_scatter<<<(a->P + 255) / 256, 256, 0, stream>>>(a->P, a->radii, g, gx, gy, im.tile_start, im.tile_cursor, bn.bucket, im.scalars);
         }
         FDGS_LAUNCH_CHECK(a->debug, stream);
         const float* colors = a->colors_precomp ? a->colors_precomp : g.rgb;
@@ -704,7 +702,7 @@ int fdgs_raster_forward_render(const FdgsRasterForward* a, int64_t R, void* stre
         k_tile_sort<<<T, 256, 0, stream>>>(im.ranges, bn.bucket, g, colors, bn.records, a->keys_out, a->point_list_out);
         }
         FDGS_LAUNCH_CHECK(a->debug, stream);
-        if (a->counts_host[1] > FDGS_SORT_SMEM_CAP) {      // some tile bucket is larger than the shared-memory cap
+        if (large != 0) {
             FDGS_PROF("k_tile_sort_large", stream);
             k_tile_sort_large<<<148, LARGE_THREADS, 0, stream>>>(im.ranges, im.large_tiles, im.scalars, bn.bucket, g, colors,
                                                                  bn.records, a->keys_out, a->point_list_out);
@@ -718,6 +716,47 @@ int fdgs_raster_forward_render(const FdgsRasterForward* a, int64_t R, void* stre
     }
     FDGS_LAUNCH_CHECK(a->debug, stream);
     return FDGS_OK;
+}
+
+static int zero_outputs(const FdgsRasterForward* a, cudaStream_t stream) {     // P == 0: rasterize_points.cu:68-82
+    const size_t HW = (size_t)a->W * a->H;
+    FDGS_CUDA(cudaMemsetAsync(a->out_color, 0, 3 * HW * sizeof(float), stream));
+    FDGS_CUDA(cudaMemsetAsync(a->out_depth, 0, HW * sizeof(float), stream));
+    return FDGS_OK;
+}
+
+int fdgs_raster_forward_plan(const FdgsRasterForward* a, void* stream_) {
+    int rc = check_forward_args(a);
+    if (rc) return rc;
+    cudaStream_t stream = (cudaStream_t)stream_;
+    for (int i = 0; i < 4; ++i) a->counts_host[i] = 0;
+    if (a->P == 0) return FDGS_OK;
+    rc = launch_plan(a, 0xffffffffu, stream);
+    if (rc) return rc;
+    FDGS_CUDA(cudaStreamSynchronize(stream));
+    return FDGS_OK;
+}
+
+int fdgs_raster_forward_render(const FdgsRasterForward* a, int64_t R, void* stream_) {
+    int rc = check_forward_args(a);
+    if (rc) return rc;
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (a->P == 0) return zero_outputs(a, stream);
+    if (R < 0) return FDGS_E_BADARG;
+    if (R > 0 && (!a->bin_ws || a->bin_bytes < FdgsBin::bytes(R))) return FDGS_E_WORKSPACE;
+    return launch_render(a, R, a->counts_host[1] > FDGS_SORT_SMEM_CAP ? 1 : 0, stream);
+}
+
+int fdgs_raster_forward(const FdgsRasterForward* a, int64_t capacity, void* stream_) {
+    int rc = check_forward_args(a);
+    if (rc) return rc;
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (a->P == 0) { for (int i = 0; i < 4; ++i) a->counts_host[i] = 0; return zero_outputs(a, stream); }
+    if (capacity <= 0 || capacity > 0xfffffff0LL) return FDGS_E_BADARG;
+    if (!a->bin_ws || a->bin_bytes < FdgsBin::bytes(capacity)) return FDGS_E_WORKSPACE;
+    rc = launch_plan(a, (uint32_t)capacity, stream);       // queues the asynchronous read-back of the counts; no host sync
+    if (rc) return rc;
+    return launch_render(a, capacity, -1, stream);
 }
 
 int fdgs_raster_copy_ranges(const void* img_ws, int W, int H, uint32_t* ranges_out, void* stream_) {

@@ -10,6 +10,7 @@
 // All three are HBM-bound sweeps; they replace ~40 (regularisers), ~10 per parameter (Adam) and ~8 (stats) ATen launches.
 #include "fdgs_common.cuh"
 #include "prof.cuh"
+#include <algorithm>
 #include <cmath>
 #include <cstdint>
 
@@ -31,15 +32,17 @@ __device__ __forceinline__ float second_diff(const float a, const float b, const
     return __fsub_rn(__fsub_rn(c, b), __fsub_rn(b, a));
 }
 
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(1024)
 k_plane_reg(RegArgs a, const float* __restrict__ grad_scale, float* __restrict__ loss)
 {
-    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    float part = 0.f;
-    if (i < a.total) {
+    // grid-stride: at most one CTA per SM, so the value is the sum of <= 148 block partials; the per-thread and per-block
+    // partial sums are kept in double (the value is a sum of ~10^7 terms of very different magnitude)
+    double part = 0.0;
+    const float gs = grad_scale ? *grad_scale : 1.0f;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < a.total; i += (long long)gridDim.x * blockDim.x) {
         int jb = 0;
         while (jb + 1 < a.njobs && i >= a.j[jb + 1].first) ++jb;
-        const RegJob J = a.j[jb];
+        const RegJob& J = a.j[jb];
         const long long e = i - J.first;
         const int h = (int)((e / J.W) % J.H);
         const float* col = J.t + (e - (long long)h * J.W);      // element (c, 0, w)
@@ -55,32 +58,28 @@ k_plane_reg(RegArgs a, const float* __restrict__ grad_scale, float* __restrict__
             if (h >= 1 && h + 1 < J.H) d_m1 = second_diff(col[(h - 1) * S], v, col[(h + 1) * S]);
             if (h + 2 < J.H) {
                 d_0 = second_diff(v, col[(h + 1) * S], col[(h + 2) * S]);
-                part += J.w_smooth * n_inv * d_0 * d_0;
+                part += (double)(J.w_smooth * n_inv) * (double)(d_0 * d_0);
             }
             grad += k * ((d_m2 - d_m1) - (d_m1 - d_0));
         }
         if (J.w_l1 != 0.f) {
             const float n_inv = 1.0f / ((float)J.C * (float)J.H * (float)J.W);
             const float d = 1.0f - v;
-            part += J.w_l1 * n_inv * fabsf(d);
+            part += (double)(J.w_l1 * n_inv) * (double)fabsf(d);
             grad += J.w_l1 * n_inv * (d > 0.f ? -1.f : (d < 0.f ? 1.f : 0.f));     // d|1 - t| / dt = -sign(1 - t)
         }
-        if (J.g) {
-            const float gs = grad_scale ? *grad_scale : 1.0f;
-            J.g[e] += gs * grad;
-        }
+        if (J.g) J.g[e] += gs * grad;
     }
-    // block reduction of the loss value: shuffle, then one atomic per warp
+    // block reduction of the loss value: shuffle, shared memory, one atomic per CTA
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(FULL, part, o);
-    __shared__ float wsum[8];
+    __shared__ double wsum[32];
     if ((threadIdx.x & 31) == 0) wsum[threadIdx.x >> 5] = part;
     __syncthreads();
     if (threadIdx.x == 0 && loss) {
-        float s = 0.f;
-#pragma unroll
-        for (int k = 0; k < 8; ++k) s += wsum[k];
-        if (s != 0.f) atomicAdd(loss, s);
+        double s = 0.0;
+        for (int k = 0; k < (int)(blockDim.x >> 5); ++k) s += wsum[k];
+        if (s != 0.0) atomicAdd(loss, (float)s);
     }
 }
 
@@ -185,7 +184,7 @@ int fdgs_plane_regulation(const FdgsPlaneReg* a, void* stream_) {
     ra.total = first;
     if (ra.njobs == 0 || first == 0) return FDGS_OK;
     { FDGS_PROF("k_plane_reg", stream);
-    k_plane_reg<<<(unsigned)((first + 255) / 256), 256, 0, stream>>>(ra, a->grad_scale, a->loss);
+    k_plane_reg<<<(unsigned)std::min<long long>((first + 1023) / 1024, 148), 1024, 0, stream>>>(ra, a->grad_scale, a->loss);
     }
     FDGS_LAUNCH_CHECK(0, stream);
     return FDGS_OK;
@@ -200,7 +199,7 @@ int fdgs_plane_smoothness(const float* plane, float* d_plane, int C, int H, int 
     ra.j[0] = RegJob{plane, d_plane, C, H, W, weight, 0.f, 0};
     ra.total = (long long)C * H * W;
     { FDGS_PROF("k_plane_reg", stream);
-    k_plane_reg<<<(unsigned)((ra.total + 255) / 256), 256, 0, stream>>>(ra, grad_scale, loss);
+    k_plane_reg<<<(unsigned)std::min<long long>((ra.total + 1023) / 1024, 148), 1024, 0, stream>>>(ra, grad_scale, loss);
     }
     FDGS_LAUNCH_CHECK(0, stream);
     return FDGS_OK;

@@ -47,6 +47,74 @@ _last_R = 0
 _keep_last = False       # diagnostics only: keep a reference to the last forward's workspaces (see count_pairs)
 _last_ws = None
 
+# ---- one-shot ("speculative") forward: no blocking read of num_rendered --------------------------------------------------
+# The reference stalls the host once per render to read num_rendered (rasterizer_impl.cu:282) because its binning buffer is
+# sized from it; the default path here does the same (fdgs_raster_forward_plan / _render).  With speculative mode ON the
+# instance workspace is sized from the largest count recently seen for this (device, P, W, H) x 1.3 and every kernel of the
+# forward is queued at once (fdgs_raster_forward); the real count comes back asynchronously and is examined by
+# check_pending().  If it did not fit, the device rendered nothing for that call (background image, zero gradients) and
+# check_pending() returns False: the caller must discard that step and redo it with speculative mode off.
+# fdgs.dp.train_iteration does exactly that.  Off by default: a bare GaussianRasterizer call behaves like the reference's.
+_spec_on = False
+_caps = {}               # (device index, P, W, H) -> largest recent num_rendered
+_pending = []            # [(event, pinned counts, capacity, key)] of one-shot calls not yet examined
+_slots = {}              # device index -> free pinned int32[4] tensors
+_overflow_seen = False
+SPEC_HEADROOM, SPEC_SLACK = 1.3, 65536
+
+
+class speculative_mode:
+    """Context manager: `with speculative_mode(True): ...` renders without the per-call host sync (see above)."""
+
+    def __init__(self, on=True):
+        self.on = bool(on)
+
+    def __enter__(self):
+        global _spec_on
+        self.prev, _spec_on = _spec_on, self.on
+        return self
+
+    def __exit__(self, *exc):
+        global _spec_on
+        _spec_on = self.prev
+        return False
+
+
+def _note_count(key, R):
+    _caps[key] = max(int(_caps.get(key, 0) * 0.999), int(R))
+
+
+def check_pending(block=True):
+    """Examines the counts of the one-shot calls issued so far (all of them with block=True - this waits for the device to
+    pass their scan kernels; only the completed ones otherwise).  Returns False if any of them overflowed its workspace
+    since the last call of this function, i.e. produced an empty render."""
+    global _overflow_seen, _last_R
+    keep = []
+    for item in _pending:
+        ev, counts, cap, key = item
+        if block:
+            ev.synchronize()
+        elif not ev.query():
+            keep.append(item)
+            continue
+        R = int(counts[0])
+        _last_R = R
+        _note_count(key, R)
+        if int(counts[3]) or R > cap:
+            _overflow_seen = True
+        _slots.setdefault(key[0], []).append(counts)
+    _pending[:] = keep
+    ok = not _overflow_seen
+    _overflow_seen = False
+    return ok
+
+
+def _take_slot(device):
+    free = _slots.setdefault(device.index, [])
+    if free:
+        return free.pop()
+    return torch.zeros(4, dtype=torch.int32).pin_memory()
+
 
 def last_num_rendered():
     """num_rendered (R) of the most recent forward call in this process (bench / diagnostics)."""
@@ -125,13 +193,31 @@ def _forward_native(bg, means3D, colors_precomp, opacities, scales, rotations, s
         a.out_color, a.out_depth, a.radii = color.data_ptr(), depth.data_ptr(), radii.data_ptr()
         a.geom_ws, a.geom_bytes = geom.data_ptr(), geom.numel()
         a.img_ws, a.img_bytes = img.data_ptr(), img.numel()
+        st = _stream()
+        key = (dev.index, int(P), W, H)
+        global _last_R, _last_ws
+        if _spec_on and key in _caps and not want_debug_lists and not debug:
+            # one-shot path: workspace sized from the recent maximum, counts read back asynchronously (check_pending)
+            cap = int(_caps[key] * SPEC_HEADROOM) + SPEC_SLACK
+            binb = torch.empty((lib.fdgs_raster_bin_bytes(cap),), dtype=torch.uint8, device=dev)
+            a.bin_ws, a.bin_bytes = binb.data_ptr(), binb.numel()
+            counts = _take_slot(dev)
+            a.counts_host = counts.data_ptr()
+            L.check(lib.fdgs_raster_forward(C.byref(a), cap, st), "fdgs_raster_forward")
+            ev = torch.cuda.Event()
+            ev.record(torch.cuda.current_stream())
+            _pending.append((ev, counts, cap, key))
+            if len(_pending) > 256:
+                check_pending(block=False)
+            if _keep_last:
+                _last_ws = (img, binb, cap, W, H)
+            return (cap, color, depth, radii, geom, binb, img)
         counts = _counts_host(dev)
         a.counts_host = counts.data_ptr()
-        st = _stream()
         L.check(lib.fdgs_raster_forward_plan(C.byref(a), st), "fdgs_raster_forward_plan")
         R = int(counts[0])
-        global _last_R
         _last_R = R
+        _note_count(key, R)
         binb = torch.empty((lib.fdgs_raster_bin_bytes(R),), dtype=torch.uint8, device=dev)
         a.bin_ws, a.bin_bytes = binb.data_ptr(), binb.numel()
         extras = {}
@@ -142,7 +228,6 @@ def _forward_native(bg, means3D, colors_precomp, opacities, scales, rotations, s
             a.point_list_out = extras["point_list"].data_ptr() if R else None
         L.check(lib.fdgs_raster_forward_render(C.byref(a), R, st), "fdgs_raster_forward_render")
         if _keep_last:
-            global _last_ws
             _last_ws = (img, binb, R, W, H)
         out = (R, color, depth, radii, geom, binb, img)
         if want_debug_lists:

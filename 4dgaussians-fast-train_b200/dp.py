@@ -179,7 +179,7 @@ class _SharedFeatures:
 
 
 def train_iteration(render_fn, pc, cams, gts, bg, bucket, rank=0, world=1, read_loss=False, loss_fn=None,
-                    share_features=True, overlap_sh=False, reduce_stats=True):
+                    share_features=True, overlap_sh=False, reduce_stats=True, speculative=False):
     """One fwd+bwd iteration over the batch `cams` (all B views; this rank renders its shard).
     loss_fn(image, gt, B): per-view loss; default = the ATen l1_view_loss above (fdgs.losses.l1_view_loss is the fused one).
     share_features: concatenate the SH coefficients once per iteration, let the views' SH gradients sum in one [P,16,3]
@@ -193,8 +193,29 @@ def train_iteration(render_fn, pc, cams, gts, bg, bucket, rank=0, world=1, read_
     reduce_stats (world > 1): the densifier's inputs are made identical on every rank - `radii` is all-reduced with MAX
     (train.py:229 takes the max over ALL B views) and visibility is derived from it (train.py:230: any over views ==
     max radius > 0), so that replicas take the same split / prune decisions and keep the same P.
+    speculative: render through the fdgs rasterizer's one-shot forward (no per-view host sync on num_rendered, see
+    fdgs.diff_gaussian_rasterization.speculative_mode): the host runs ahead of the device over views and iterations.  The
+    counts are examined where the step synchronises anyway - right after the loss read-back with read_loss=True; a step
+    whose instance workspace turned out too small is then REDONE with the exact path before anything consumed its
+    gradients.  Without read_loss the examination is non-blocking and a late finding raises (single process) - call
+    fdgs.diff_gaussian_rasterization.check_pending() at your own synchronisation point to be sure earlier.
     Returns (local loss sum, radii max over all B views [P] int32, visibility [P] bool) - what train.py:229-232,346-349
     feed to max_radii2D / add_densification_stats."""
+    if speculative:
+        from . import diff_gaussian_rasterization as _rast
+        with _rast.speculative_mode(True):
+            out = train_iteration(render_fn, pc, cams, gts, bg, bucket, rank, world, read_loss, loss_fn, share_features,
+                                  overlap_sh, reduce_stats, speculative=False)
+        if not _rast.check_pending(block=bool(read_loss)):
+            if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+                raise RuntimeError("fdgs: a one-shot render overflowed its instance workspace on this rank; the replicas "
+                                   "cannot redo a step independently - rerun the iteration with speculative=False")
+            if not read_loss:
+                raise RuntimeError("fdgs: an earlier one-shot render overflowed its instance workspace (found late: "
+                                   "read_loss=False); its gradients were incomplete")
+            return train_iteration(render_fn, pc, cams, gts, bg, bucket, rank, world, read_loss, loss_fn, share_features,
+                                   overlap_sh, reduce_stats, speculative=False)
+        return out
     B = len(cams)
     bucket.zero()
     loss_sum = None

@@ -473,6 +473,8 @@ def main():
         torch.cuda.synchronize()
 
     overlap_sh = os.environ.get("FDGS_OVERLAP_SH", "0") != "0"    # A/B switch for the early SH all-reduce (N > 1)
+    # fdgs arm: one-shot rasterizer forward (no per-view host sync on num_rendered; FDGS_ONE_SHOT=0 = the exact path)
+    one_shot = a.impl == "fdgs" and os.environ.get("FDGS_ONE_SHOT", "1") != "0"
 
     def optimizer_stepped():
         # what an optimizer step between two iterations implies for the fdgs arm: the cached channel-last plane copy is
@@ -483,7 +485,8 @@ def main():
 
     def step_resident():
         optimizer_stepped()
-        train_iteration(render_fn, pc, cams, gts_dev, bg, bucket, eff_rank, eff_world, loss_fn=fused_loss, overlap_sh=overlap_sh)
+        train_iteration(render_fn, pc, cams, gts_dev, bg, bucket, eff_rank, eff_world, loss_fn=fused_loss, overlap_sh=overlap_sh,
+                        speculative=one_shot)
 
     from fdgs.dp import ViewStager
     stager = ViewStager([gts_host[i] if i in mine else None for i in range(B)], dev)
@@ -503,7 +506,7 @@ def main():
         optimizer_stepped()
         stager.upload(gts_host, mine)
         loss, _, _ = train_iteration(render_fn, pc, StepCameras(), stager, bg, bucket, eff_rank, eff_world, read_loss=True,
-                                     loss_fn=fused_loss, overlap_sh=overlap_sh)
+                                     loss_fn=fused_loss, overlap_sh=overlap_sh, speculative=one_shot)
         assert stager.nbytes == sum(gts_host[i].numel() * 4 for i in mine)
         return loss
 
@@ -527,6 +530,12 @@ def main():
     ms = timed(step_resident, a.steps)
     launches = launch_count() - n0
     clocks = sampler.stop() if sampler else {}
+    if one_shot:
+        # the timed steps never read anything back: examine their counts now (a step that overflowed its instance
+        # workspace rendered nothing and would make the number above invalid)
+        from fdgs.diff_gaussian_rasterization import check_pending
+        if not check_pending(block=True):
+            raise SystemExit("bench: a one-shot render overflowed its workspace inside the timed region; rerun with FDGS_ONE_SHOT=0")
     for _ in range(2):
         step_e2e()
     ms_e2e = timed(step_e2e, a.steps)
@@ -597,7 +606,9 @@ def main():
                        "views_per_rank": len(mine), "parallelism": f"view-dp{world}",
                        "l2": "working set per step >> L2 (>=400 MB per view streamed; inputs larger than L2)",
                        "grad_bucket_bytes": bucket.nbytes(), "deformation": cfg["net_impl"],
-                       "plane_cache": "invalidated once per step (as after an optimizer step)"},
+                       "plane_cache": "invalidated once per step (as after an optimizer step)",
+                       "rasterizer_forward": ("one-shot (no host sync on num_rendered; counts verified after the timed region: "
+                                              "no overflow)" if one_shot else "plan + render with the reference's blocking read of num_rendered")},
             "clocks": clocks,
             "e2e": {"value": round(a.steps / (ms_e2e * 1e-3), 4), "unit": "iters/s", "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": 4},

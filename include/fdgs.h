@@ -86,7 +86,8 @@ typedef struct FdgsRasterForward {
     void* geom_ws;  size_t geom_bytes;
     void* img_ws;   size_t img_bytes;
     void* bin_ws;   size_t bin_bytes;   /* only read by fdgs_raster_forward_render */
-    /* pinned host scratch: [0]=num_rendered R, [1]=max instances in one tile */
+    /* pinned host scratch, 4 x int32: [0] = num_rendered R, [1] = most instances in one tile, [2] = tiles whose bucket is
+     * above the shared-memory sort cap, [3] = 1 when R exceeded the capacity given to fdgs_raster_forward */
     int32_t* counts_host;
     /* optional parity/debug outputs (NULL to skip): sorted 64-bit tile|depth keys [R]
      * and sorted Gaussian ids [R], laid out exactly like the reference's
@@ -108,6 +109,16 @@ int fdgs_raster_forward_plan(const FdgsRasterForward* a, void* stream);
  * bin_ws must hold fdgs_raster_bin_bytes(R).                                  */
 int fdgs_raster_forward_render(const FdgsRasterForward* a, int64_t R, void* stream);
 
+/* One-shot forward WITHOUT the blocking read of num_rendered (the reference stalls the host at rasterizer_impl.cu:282
+ * because its binning buffer is sized from R; here the caller sizes bin_ws for `capacity` instances - an estimate, e.g.
+ * 1.3 x the count of the previous render of this view - and every kernel of both stages is queued at once).  The counts
+ * are copied to counts_host ASYNCHRONOUSLY: they are valid once the caller has synchronised with the stream (an event
+ * recorded after this call).  If R > capacity the device empties every tile range (the queued scatter / sort / blend
+ * kernels then touch nothing, the image is background) and sets counts_host[3] = 1: the caller must discard the result
+ * and call again with a larger workspace (or use the plan / render pair).  geom_ws / img_ws / bin_ws go to
+ * fdgs_raster_backward as usual, with FdgsRasterBackward.R = capacity (bin_ws is carved for `capacity`, not for R).      */
+int fdgs_raster_forward(const FdgsRasterForward* a, int64_t capacity, void* stream);
+
 /* Reads back the tile ranges (uint2 per tile, (0,0) for empty tiles exactly as
  * rasterizer_impl.cu:311-319 leaves them) into a device buffer — parity/debug. */
 int fdgs_raster_copy_ranges(const void* img_ws, int W, int H, uint32_t* ranges_out, void* stream);
@@ -122,7 +133,8 @@ int fdgs_raster_count_pairs(const void* img_ws, const void* bin_ws, int64_t R, i
 typedef struct FdgsRasterBackward {
     /* reference: RasterizeGaussiansBackwardCUDA args, RAST/rasterize_points.cu:119-142 */
     int32_t P, D, M, W, H;
-    int64_t R;
+    int64_t R;                   /* the instance count bin_ws was carved for: num_rendered after the plan / render pair,
+                                    `capacity` after fdgs_raster_forward */
     float tanfovx, tanfovy, scale_modifier;
     int32_t debug;
     const float* background;

@@ -110,3 +110,34 @@ def test_view_stager_and_shared_features_change_nothing():
         assert abs(r[0] - res[0][0]) <= 1e-6 * abs(res[0][0])
         for a, b in ((r[1], res[0][1]), (r[2], res[0][2])):
             assert float((a - b).abs().max()) <= 1e-4 * float(b.abs().max())
+
+
+def test_speculative_iteration_equals_exact_and_redoes_on_overflow():
+    """train_iteration(speculative=True): same loss / gradients as the exact path, and a step whose instance workspace
+    was too small is redone before its gradients are used."""
+    import bench
+    import fdgs  # noqa: F401
+    from fdgs import diff_gaussian_rasterization as R
+    from fdgs.dp import train_iteration
+    from fdgs.render import render as render_fn
+    from fdgs.losses import l1_view_loss as loss_fn
+    dev = "cuda:0"
+    cfg, args, pc, net, cams, gts_host = bench.build_scene("dynerf_small", "fdgs", dev, 3, 0)
+    bucket = bench.make_bucket(pc, net, dev)
+    bg = torch.ones(3, device=dev)
+    gts = [g.to(dev) for g in gts_host]
+    R.check_pending()
+    l0, r0, v0 = train_iteration(render_fn, pc, cams, gts, bg, bucket, 0, 1, read_loss=True, loss_fn=loss_fn)
+    f0 = bucket.flat.clone()
+    l1, r1, v1 = train_iteration(render_fn, pc, cams, gts, bg, bucket, 0, 1, read_loss=True, loss_fn=loss_fn, speculative=True)
+    assert abs(l1 - l0) <= 1e-6 * abs(l0) and torch.equal(r0, r1) and torch.equal(v0, v1)
+    assert util.rel_err(bucket.flat, f0) < 1e-5
+    for k in list(R._caps):                                           # force an overflow in the next speculative step
+        R._caps[k] = max(R._caps[k] // 50, 1)
+    R.SPEC_SLACK, slack = 0, R.SPEC_SLACK
+    try:
+        l2, r2, v2 = train_iteration(render_fn, pc, cams, gts, bg, bucket, 0, 1, read_loss=True, loss_fn=loss_fn, speculative=True)
+    finally:
+        R.SPEC_SLACK = slack
+    assert abs(l2 - l0) <= 1e-6 * abs(l0) and torch.equal(r0, r2)
+    assert util.rel_err(bucket.flat, f0) < 1e-5

@@ -343,3 +343,41 @@ def test_clustered_scene_vs_cpu_oracle():
     _eq(o["keys"].cpu().numpy().astype(np.uint64), c["keys"], "keys")
     _eq(o["point_list"].cpu().numpy().astype(np.uint32), c["point_list"], "point_list")
     _eq(o["ranges"].cpu().numpy().astype(np.uint32), c["ranges"], "ranges")
+
+
+def test_one_shot_forward_matches_exact_and_reports_overflow():
+    """fdgs_raster_forward (no host sync; workspace sized from an estimate) vs the plan / render pair: identical images and
+    gradients when the estimate holds; when it does not, nothing is rendered, check_pending() says so, and the exact path
+    afterwards is unaffected."""
+    from fdgs import diff_gaussian_rasterization as R
+    sc = util.scene(P=30_000, W=400, H=300, logscale=-4.0, seed=5, device="cuda")
+    gc = torch.randn((3, 300, 400), generator=torch.Generator().manual_seed(1)).cuda()
+    assert R.check_pending()
+    c0, r0, d0, g0 = util.ours_autograd(sc, gc)                      # exact path; also records the count for this shape
+    key = (torch.device("cuda", torch.cuda.current_device()).index, 30_000, 400, 300)
+    assert R._caps[key] == R.last_num_rendered() > 0
+    with R.speculative_mode(True):
+        c1, r1, d1, g1 = util.ours_autograd(sc, gc)
+        assert len(R._pending) == 1
+    assert R.check_pending(block=True) and not R._pending
+    assert torch.equal(c0, c1) and torch.equal(r0, r1) and torch.equal(d0, d1)
+    for k in g0:
+        if g0[k] is not None:
+            assert util.rel_err(g1[k], g0[k]) < 1e-6, k             # same kernels; float atomics in the backward
+    # overflow: pretend the last render of this shape was 20x smaller
+    true_R = R._caps[key]
+    R._caps[key] = true_R // 20
+    R.SPEC_SLACK, slack = 0, R.SPEC_SLACK
+    try:
+        with R.speculative_mode(True):
+            c2, r2, d2, g2 = util.ours_autograd(sc, gc)
+        assert not R.check_pending(block=True)                        # reported ...
+        assert float((c2 - 1.0).abs().max()) == 0.0                   # ... nothing was blended (background = 1)
+        assert torch.equal(r2, r0)                                    # radii come from the preprocess stage
+        assert all(float(v.abs().max()) == 0.0 for k, v in g2.items() if v is not None and k != "means2D")
+        assert R._caps[key] >= true_R                                 # the real count was learnt from the failed call
+        with R.speculative_mode(True):
+            c3, _, _, _ = util.ours_autograd(sc, gc)
+        assert R.check_pending(block=True) and torch.equal(c3, c0)
+    finally:
+        R.SPEC_SLACK = slack

@@ -17,6 +17,7 @@ from fdgs import synth
 import util
 
 pytestmark = pytest.mark.gpu
+VAL_TOL = 5e-6      # FP32 sums of up to 7e6 terms in two different orders (ATen's mean vs block partials kept in double)
 
 
 def _ref_smoothness():
@@ -60,7 +61,7 @@ def test_regulation_value_and_gradient_vs_reference(cfg):
             p.grad = None
     ours = freg.compute_regulation(grids, *w)
     (ours * 1.0).backward()
-    assert abs(float(ours) - float(ref)) <= 2e-6 * abs(float(ref)), (float(ours), float(ref))
+    assert abs(float(ours) - float(ref)) <= VAL_TOL * abs(float(ref)), (float(ours), float(ref))
     worst = 0.0
     for a, b in zip([p.grad for lv in grids for p in lv], gref):
         e = util.rel_err(a, b)
@@ -79,20 +80,19 @@ def test_regulation_value_and_gradient_vs_reference(cfg):
                 p.grad = None
         o = fn(grids)
         (o * 3.5).backward()
-        assert abs(float(o) - float(r)) <= 2e-6 * abs(float(r))
+        assert abs(float(o) - float(r)) <= VAL_TOL * abs(float(r))
         for p, b in zip([p for lv in grids for p in lv], gr):
             if b is None or not bool(b.abs().max() > 0):
                 assert p.grad is None or not bool(p.grad.abs().max() > 0)
             else:
                 assert util.rel_err(p.grad, b) < 2e-6
-    # fused in-place path: value returned, gradient ADDED to existing .grad tensors
-    for lv in grids:
-        for p in lv:
-            p.grad = torch.full_like(p, 0.25)
-    v = freg.add_regulation_(grids, *w)
-    assert abs(float(v) - float(ref)) <= 2e-6 * abs(float(ref))
+    # fused in-place path: value returned, gradient ADDED to existing .grad tensors (pre-filled at the gradient's own scale)
     for p, b in zip([p for lv in grids for p in lv], gref):
-        assert util.rel_err(p.grad - 0.25, b) < 5e-6
+        p.grad = (0.5 * b).contiguous()
+    v = freg.add_regulation_(grids, *w)
+    assert abs(float(v) - float(ref)) <= VAL_TOL * abs(float(ref))
+    for p, b in zip([p for lv in grids for p in lv], gref):
+        assert util.rel_err(p.grad - 0.5 * b, b) < 5e-6
     util.plog("train_glue", f"regulation[{cfg}] vs {_ref_smoothness()[1]}: value {float(ours):.8e} vs {float(ref):.8e}, worst grad rel err {worst:.2e}")
 
 
@@ -144,8 +144,9 @@ def test_fused_adam_bit_identical_to_torch_adam():
                 assert torch.equal(sa["exp_avg_sq"], sb["exp_avg_sq"]), (it, i)
                 assert float(sa["step"]) == float(sb["step"])
     # state_dict layouts are interchangeable: load ours into a fresh torch Adam and keep stepping identically
-    sd = ours.state_dict()
-    assert set(sd["state"][0]) == {"step", "exp_avg", "exp_avg_sq"}
+    import copy
+    sd = copy.deepcopy(ours.state_dict())        # load_state_dict keeps same-device tensors BY REFERENCE: without the copy
+    assert set(sd["state"][0]) == {"step", "exp_avg", "exp_avg_sq"}      # both optimizers would update the same moments
     ref2 = torch.optim.Adam([{"params": [p], "lr": 0.0} for p in pa], lr=0.0, eps=1e-15)
     ref2.load_state_dict(sd)
     for a, b in zip(pa, pb):

@@ -16,7 +16,7 @@ cfg, args, pc, net, cams, gts_host = bench.build_scene("dynerf", "fdgs", dev, a.
 bucket = bench.make_bucket(pc, net, dev)
 bg = torch.ones(3, device=dev)
 gts = [g.to(dev) for g in gts_host]
-step = lambda: train_iteration(render_fn, pc, cams, gts, bg, bucket, 0, 1, loss_fn=fused_loss)
+step = lambda: train_iteration(render_fn, pc, cams, gts, bg, bucket, 0, 1, loss_fn=fused_loss, speculative=True)
 for _ in range(3):
     step()
 torch.cuda.synchronize()

@@ -19,10 +19,10 @@ bucket = bench.make_bucket(pc, net, dev)
 bg = torch.ones(3, device=dev)
 gts = [g.to(dev) for g in gts_host]
 for _ in range(3):
-    train_iteration(render_fn, pc, cams, gts, bg, bucket, 0, 1, loss_fn=fused_loss)
+    train_iteration(render_fn, pc, cams, gts, bg, bucket, 0, 1, loss_fn=fused_loss, speculative=True)
 torch.cuda.synchronize()
 with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
-    train_iteration(render_fn, pc, cams, gts, bg, bucket, 0, 1, loss_fn=fused_loss)
+    train_iteration(render_fn, pc, cams, gts, bg, bucket, 0, 1, loss_fn=fused_loss, speculative=True)
     torch.cuda.synchronize()
 evs = [e for e in prof.events() if e.device_type == torch.autograd.DeviceType.CUDA]
 evs.sort(key=lambda e: e.time_range.start)
