@@ -31,6 +31,7 @@ class FdgsRasterForward(C.Structure):
         ("bin_ws", C.c_void_p), ("bin_bytes", C.c_size_t),
         ("counts_host", C.c_void_p),
         ("keys_out", C.c_void_p), ("point_list_out", C.c_void_p),
+        ("activate", C.c_int32),
     ]
 
 
@@ -49,6 +50,7 @@ class FdgsRasterBackward(C.Structure):
         ("dL_dmeans2D", C.c_void_p), ("dL_dconic", C.c_void_p), ("dL_dopacity", C.c_void_p),
         ("dL_dcolors", C.c_void_p), ("dL_dmeans3D", C.c_void_p), ("dL_dcov3D", C.c_void_p),
         ("dL_dsh", C.c_void_p), ("dL_dscales", C.c_void_p), ("dL_drots", C.c_void_p),
+        ("activate", C.c_int32),
     ]
 
 
@@ -135,6 +137,7 @@ SYMBOLS = {
     "fdgs_abi_version": (C.c_int, []),
     "fdgs_error_string": (C.c_char_p, [C.c_int]),
     "fdgs_compiled_arch": (C.c_int, []),
+    "fdgs_set_sm_limit": (None, [C.c_int]),
     "fdgs_profile_enable": (None, [C.c_int]),
     "fdgs_profile_collect": (C.c_int, [C.c_char_p, C.c_size_t]),
     "fdgs_launch_count": (C.c_ulonglong, []),
@@ -162,6 +165,11 @@ SYMBOLS = {
     "fdgs_plane_smoothness": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]),
     "fdgs_adam_step": (C.c_int, [C.POINTER(FdgsAdamStep), C.c_void_p]),
     "fdgs_densify_stats": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "fdgs_knn_ws_bytes": (C.c_size_t, [C.c_int]),
+    "fdgs_knn_mean_dist2": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
+    "fdgs_voxel_downsample_ws_bytes": (C.c_size_t, [C.c_int]),
+    "fdgs_voxel_downsample": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_double, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p,
+                                        C.c_void_p, C.c_size_t, C.c_void_p]),
     "fdgs_l1_loss_forward": (C.c_int, [C.c_void_p, C.c_void_p, C.c_longlong, C.c_float, C.c_void_p, C.c_void_p]),
     "fdgs_l1_loss_backward": (C.c_int, [C.c_void_p, C.c_void_p, C.c_longlong, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]),
 }

@@ -10,7 +10,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libfdgs.so")
-SOURCES = ["api.cu", "raster_fwd.cu", "raster_bwd.cu", "deform.cu", "deform_tc.cu", "deform_tc_bwd.cu", "glue.cu", "train_glue.cu"]
+SOURCES = ["api.cu", "raster_fwd.cu", "raster_bwd.cu", "deform.cu", "deform_tc.cu", "deform_tc_bwd.cu", "glue.cu", "train_glue.cu", "init_kernels.cu"]
 HEADERS = ["fdgs_common.cuh", "raster_math.cuh", "prof.cuh", "deform_common.cuh", "umma.cuh", os.path.join("..", "..", "include", "fdgs.h")]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",

@@ -48,6 +48,8 @@ cudaEvent_t get_event() {
 }
 }  // namespace
 
+static int g_sm_limit = 0;
+int fdgs_sm_limit_value() { return g_sm_limit; }
 void fdgs_count_launch() { ++g_launches; }
 void fdgs_prof_begin(const char* name, cudaStream_t s) {
     ++g_launches;
@@ -62,6 +64,7 @@ void fdgs_prof_end(cudaStream_t s) {
 }
 
 extern "C" {
+void fdgs_set_sm_limit(int n) { g_sm_limit = n > 0 ? n : 0; }
 void fdgs_profile_enable(int on) { g_prof_on = on != 0; }
 unsigned long long fdgs_launch_count(void) { return g_launches; }
 // Synchronises the device, then writes "name count total_ms\n" per kernel into buf; clears the records.

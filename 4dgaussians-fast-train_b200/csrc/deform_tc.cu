@@ -527,7 +527,8 @@ static int sm_count() {          // of the CURRENT device (one process may drive
     int dev = 0; cudaGetDevice(&dev);
     if (dev < 0 || dev >= 64) dev = 0;
     if (!n[dev]) { cudaDeviceGetAttribute(&n[dev], cudaDevAttrMultiProcessorCount, dev); if (n[dev] <= 0) n[dev] = 148; }
-    return n[dev];
+    const int lim = fdgs_sm_limit_value();        // fdgs_set_sm_limit: leave SMs to a concurrent kernel (the NCCL all-reduce)
+    return (lim > 0 && lim < n[dev]) ? lim : n[dev];
 }
 
 size_t save_bytes(const Layout& lo, int P) {

@@ -1145,14 +1145,14 @@ k_deform_bwd_weights(WArgs args)
                     v += __shfl_xor_sync(0xffffffffu, v, 4);
                     acc[c][o] = v;
                 }
-            if (wantB && cgA == 0) {
+            if (wantB) {          // warp-uniform condition: every lane takes part in the full-mask shuffles
 #pragma unroll
                 for (int o = 0; o < 4; ++o) {
                     float v = sb[o];
                     v += __shfl_xor_sync(0xffffffffu, v, 1);
                     v += __shfl_xor_sync(0xffffffffu, v, 2);
                     v += __shfl_xor_sync(0xffffffffu, v, 4);
-                    if (row8 == 0 && o < J.nb) atomicAdd(&csumB[o], v);
+                    if (cgA == 0 && row8 == 0 && o < J.nb) atomicAdd(&csumB[o], v);
                 }
             }
             if (row8 == 0 && onA) {
@@ -1281,7 +1281,8 @@ static int sm_count() {          // of the CURRENT device (one process may drive
     int dev = 0; cudaGetDevice(&dev);
     if (dev < 0 || dev >= 64) dev = 0;
     if (!n[dev]) { cudaDeviceGetAttribute(&n[dev], cudaDevAttrMultiProcessorCount, dev); if (n[dev] <= 0) n[dev] = 148; }
-    return n[dev];
+    const int lim = fdgs_sm_limit_value();        // fdgs_set_sm_limit: leave SMs to a concurrent kernel (the NCCL all-reduce)
+    return (lim > 0 && lim < n[dev]) ? lim : n[dev];
 }
 
 bool supported(const Layout& lo) { return tc_supported(lo); }

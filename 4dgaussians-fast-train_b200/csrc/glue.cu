@@ -1,13 +1,11 @@
 // Caller-side glue between the deformation field and the rasterizer (include/fdgs.h: fdgs_activate_*): the scale /
 // rotation / opacity activations of gaussian_renderer/__init__.py:97-99 (torch.exp, F.normalize(dim=1, eps=1e-12),
 // torch.sigmoid; scene/gaussian_model.py:47-58) and their backward, one launch each way instead of ~15 ATen kernels.
-#include "fdgs_common.cuh"
+#include "raster_math.cuh"
 #include "prof.cuh"
 #include <cstdint>
 
 namespace {
-
-constexpr float NORM_EPS = 1e-12f;
 
 __global__ void __launch_bounds__(256)
 k_activate_fwd(int P, const float* __restrict__ s_raw, const float* __restrict__ r_raw, const float* __restrict__ o_raw,
@@ -17,15 +15,10 @@ k_activate_fwd(int P, const float* __restrict__ s_raw, const float* __restrict__
     if (i >= P) return;
     if (s) {
 #pragma unroll
-        for (int k = 0; k < 3; ++k) s[3 * (size_t)i + k] = expf(s_raw[3 * (size_t)i + k]);
+        for (int k = 0; k < 3; ++k) s[3 * (size_t)i + k] = fdgs_act_scale(s_raw[3 * (size_t)i + k]);
     }
-    if (r) {
-        const float4 q = reinterpret_cast<const float4*>(r_raw)[i];
-        const float n = sqrtf(q.x * q.x + q.y * q.y + q.z * q.z + q.w * q.w);
-        const float d = fmaxf(n, NORM_EPS);
-        reinterpret_cast<float4*>(r)[i] = make_float4(q.x / d, q.y / d, q.z / d, q.w / d);
-    }
-    if (o) o[i] = 1.0f / (1.0f + expf(-o_raw[i]));
+    if (r) reinterpret_cast<float4*>(r)[i] = fdgs_act_quat(reinterpret_cast<const float4*>(r_raw)[i]);
+    if (o) o[i] = fdgs_act_opacity(o_raw[i]);
 }
 
 __global__ void __launch_bounds__(256)
@@ -37,24 +30,12 @@ k_activate_bwd(int P, const float* __restrict__ r_raw, const float* __restrict__
     if (i >= P) return;
     if (ds) {
 #pragma unroll
-        for (int k = 0; k < 3; ++k) ds[3 * (size_t)i + k] = gs[3 * (size_t)i + k] * s[3 * (size_t)i + k];
+        for (int k = 0; k < 3; ++k) ds[3 * (size_t)i + k] = fdgs_act_scale_vjp(gs[3 * (size_t)i + k], s[3 * (size_t)i + k]);
     }
-    if (dr) {
-        const float4 q = reinterpret_cast<const float4*>(r_raw)[i];
-        const float4 g = reinterpret_cast<const float4*>(gr)[i];
-        const float n = sqrtf(q.x * q.x + q.y * q.y + q.z * q.z + q.w * q.w);
-        float4 d;
-        if (n >= NORM_EPS) {              // d(q / n): (g - u (u . g)) / n with u = q / n
-            const float4 u = reinterpret_cast<const float4*>(r)[i];
-            const float dot = u.x * g.x + u.y * g.y + u.z * g.z + u.w * g.w;
-            const float inv = 1.0f / n;
-            d = make_float4((g.x - u.x * dot) * inv, (g.y - u.y * dot) * inv, (g.z - u.z * dot) * inv, (g.w - u.w * dot) * inv);
-        } else {                          // clamp_min(eps) is active: the denominator is the constant eps
-            d = make_float4(g.x / NORM_EPS, g.y / NORM_EPS, g.z / NORM_EPS, g.w / NORM_EPS);
-        }
-        reinterpret_cast<float4*>(dr)[i] = d;
-    }
-    if (dopa) { const float v = o[i]; dopa[i] = go[i] * v * (1.0f - v); }
+    if (dr)
+        reinterpret_cast<float4*>(dr)[i] = fdgs_act_quat_vjp(reinterpret_cast<const float4*>(r_raw)[i], reinterpret_cast<const float4*>(r)[i],
+                                                             reinterpret_cast<const float4*>(gr)[i]);
+    if (dopa) dopa[i] = fdgs_act_opacity_vjp(go[i], o[i]);
 }
 
 // L1 loss: grid-stride float4 sweep, per-thread partial -> warp shuffle -> one atomic per warp.

@@ -13,3 +13,6 @@ struct FdgsProfScope {
     ~FdgsProfScope() { fdgs_prof_end(s); }
 };
 #define FDGS_PROF(name, stream) FdgsProfScope prof_scope__(name, stream)
+
+// fdgs_set_sm_limit (include/fdgs.h): upper bound on the CTAs of the persistent one-CTA-per-SM deformation kernels
+int fdgs_sm_limit_value();

@@ -317,7 +317,8 @@ preprocess_bwd_one(int idx, int D, int M, const float* __restrict__ means3D, con
                    const float* __restrict__ dL_dmean2D, const float* __restrict__ dL_dconic,
                    const float* __restrict__ dL_dcolor,
                    float* __restrict__ dL_dmeans3D, float* __restrict__ dL_dcov3D, float* __restrict__ dL_dsh,
-                   float* __restrict__ dL_dscales, float* __restrict__ dL_drots, float* sh_row)
+                   float* __restrict__ dL_dscales, float* __restrict__ dL_drots, float* sh_row,
+                   int activate, const float4* __restrict__ conic_opacity, float* __restrict__ dL_dopacity)
 {
     const size_t i3 = 3 * (size_t)idx;
 
@@ -337,7 +338,10 @@ preprocess_bwd_one(int idx, int D, int M, const float* __restrict__ means3D, con
         }
         dL_dscales[i3] = 0.f; dL_dscales[i3 + 1] = 0.f; dL_dscales[i3 + 2] = 0.f;
         reinterpret_cast<float4*>(dL_drots)[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
-        return;
+        return;                   // (dL_dopacity of an invisible Gaussian is 0 already: nothing blended it)
+    }
+    if (activate) {               // dL/d(opacity logit) in place: sigmoid VJP with the activated opacity kept by the forward
+        dL_dopacity[idx] = fdgs_act_opacity_vjp(dL_dopacity[idx], conic_opacity[idx].w);
     }
 
     const float3 mean = make_float3(means3D[i3], means3D[i3 + 1], means3D[i3 + 2]);
@@ -478,8 +482,13 @@ preprocess_bwd_one(int idx, int D, int M, const float* __restrict__ means3D, con
 
     // ---- cov3D -> scale, rotation ------------------------------------------------------
     if (scales) {
-        const float3 sc = make_float3(scales[i3], scales[i3 + 1], scales[i3 + 2]);
-        const float4 q = reinterpret_cast<const float4*>(rotations)[idx];
+        float3 sc = make_float3(scales[i3], scales[i3 + 1], scales[i3 + 2]);
+        const float4 q_in = reinterpret_cast<const float4*>(rotations)[idx];
+        float4 q = q_in;
+        if (activate) {           // the inputs are the raw deformation outputs: redo exp / normalize (forward did the same)
+            sc = make_float3(fdgs_act_scale(sc.x), fdgs_act_scale(sc.y), fdgs_act_scale(sc.z));
+            q = fdgs_act_quat(q_in);
+        }
         const float r = q.x, x = q.y, y = q.z, z = q.w;
         const M3 R = quat_to_m3(r, x, y, z);
         const float s[3] = { scale_modifier * sc.x, scale_modifier * sc.y, scale_modifier * sc.z };
@@ -506,12 +515,16 @@ preprocess_bwd_one(int idx, int D, int M, const float* __restrict__ means3D, con
 #pragma unroll
             for (int j = 0; j < 3; ++j) n[i][j] = dM.m[j][i] * s[i];
         }
+        if (activate) {           // exp VJP: dL/d(log scale) = dL/ds * s
+            ds[0] = fdgs_act_scale_vjp(ds[0], sc.x); ds[1] = fdgs_act_scale_vjp(ds[1], sc.y); ds[2] = fdgs_act_scale_vjp(ds[2], sc.z);
+        }
         dL_dscales[i3] = ds[0]; dL_dscales[i3 + 1] = ds[1]; dL_dscales[i3 + 2] = ds[2];
         float4 dq;
         dq.x = 2 * z * (n[0][1] - n[1][0]) + 2 * y * (n[2][0] - n[0][2]) + 2 * x * (n[1][2] - n[2][1]);
         dq.y = 2 * y * (n[1][0] + n[0][1]) + 2 * z * (n[2][0] + n[0][2]) + 2 * r * (n[1][2] - n[2][1]) - 4 * x * (n[2][2] + n[1][1]);
         dq.z = 2 * x * (n[1][0] + n[0][1]) + 2 * r * (n[2][0] - n[0][2]) + 2 * z * (n[1][2] + n[2][1]) - 4 * y * (n[2][2] + n[0][0]);
         dq.w = 2 * r * (n[0][1] - n[1][0]) + 2 * x * (n[2][0] + n[0][2]) + 2 * y * (n[1][2] + n[2][1]) - 4 * z * (n[1][1] + n[0][0]);
+        if (activate) dq = fdgs_act_quat_vjp(q_in, q, dq);     // normalize VJP: gradient w.r.t. the raw quaternion
         reinterpret_cast<float4*>(dL_drots)[idx] = dq;
     } else {
         dL_dscales[i3] = 0.f; dL_dscales[i3 + 1] = 0.f; dL_dscales[i3 + 2] = 0.f;
@@ -532,7 +545,8 @@ k_preprocess_bwd(int P, int D, int M, const float* __restrict__ means3D, const i
                  const float* __restrict__ dL_dmean2D, const float* __restrict__ dL_dconic,
                  const float* __restrict__ dL_dcolor,
                  float* __restrict__ dL_dmeans3D, float* __restrict__ dL_dcov3D, float* __restrict__ dL_dsh,
-                 float* __restrict__ dL_dscales, float* __restrict__ dL_drots, int sh_staged)
+                 float* __restrict__ dL_dscales, float* __restrict__ dL_drots, int sh_staged,
+                 int activate, const float4* __restrict__ conic_opacity, float* __restrict__ dL_dopacity)
 {
     __shared__ float V[16], Pm[16], cam[3];
     extern __shared__ float s_sh[];
@@ -558,7 +572,7 @@ k_preprocess_bwd(int P, int D, int M, const float* __restrict__ means3D, const i
     if (idx < P)
         preprocess_bwd_one(idx, D, M, means3D, radii, shs, clamped, scales, rotations, scale_modifier, cov3Ds, V, Pm, cam, fx, fy,
                            tanfovx, tanfovy, dL_dmean2D, dL_dconic, dL_dcolor, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drots,
-                           sh_staged ? s_sh + threadIdx.x * (rowf + 1) : nullptr);
+                           sh_staged ? s_sh + threadIdx.x * (rowf + 1) : nullptr, activate, conic_opacity, dL_dopacity);
     if (sh_staged) {
         __syncthreads();
         float4* dst = reinterpret_cast<float4*>(dL_dsh + base);
@@ -610,7 +624,8 @@ extern "C" int fdgs_raster_backward(const FdgsRasterBackward* a, void* stream_) 
     k_preprocess_bwd<<<(P + 255) / 256, 256, sh_smem, stream>>>(
         P, a->D, a->M, a->means3D, a->radii, a->shs, g.clamped, a->scales, a->rotations, a->scale_modifier, cov3D_ptr,
         a->viewmatrix, a->projmatrix, focal_x, focal_y, a->tanfovx, a->tanfovy, a->campos, a->dL_dmeans2D, a->dL_dconic,
-        a->dL_dcolors, a->dL_dmeans3D, a->dL_dcov3D, a->dL_dsh, a->dL_dscales, a->dL_drots, sh_staged);
+        a->dL_dcolors, a->dL_dmeans3D, a->dL_dcov3D, a->dL_dsh, a->dL_dscales, a->dL_drots, sh_staged,
+        (a->activate && a->scales && !a->cov3D_precomp) ? 1 : 0, g.conic_opacity, a->dL_dopacity);
     }
     FDGS_LAUNCH_CHECK(a->debug, stream);
     return FDGS_OK;

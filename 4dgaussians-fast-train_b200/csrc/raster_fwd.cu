@@ -56,7 +56,7 @@ k_preprocess(int P, int D, int M,
              const float* __restrict__ campos,
              int W, int H, float tanfovx, float tanfovy, float focal_x, float focal_y,
              int gx, int gy, int prefiltered,
-             int* __restrict__ radii, FdgsGeom g, uint32_t* __restrict__ tile_count, int sh_staged)
+             int* __restrict__ radii, FdgsGeom g, uint32_t* __restrict__ tile_count, int sh_staged, int activate)
 {
     __shared__ float sV[16], sPm[16], sCam[3];
     extern __shared__ float s_sh[];              // [256][SH_STRIDE] when the SH block is staged (sh_staged)
@@ -104,8 +104,12 @@ k_preprocess(int P, int D, int M,
 #pragma unroll
                 for (int i = 0; i < 6; ++i) c6[i] = cov3D_precomp[6 * (size_t)idx + i];
             } else {
-                const float3 s = make_float3(scales[3 * idx], scales[3 * idx + 1], scales[3 * idx + 2]);
-                const float4 q = reinterpret_cast<const float4*>(rotations)[idx];
+                float3 s = make_float3(scales[3 * idx], scales[3 * idx + 1], scales[3 * idx + 2]);
+                float4 q = reinterpret_cast<const float4*>(rotations)[idx];
+                if (activate) {         // raw deformation outputs: exp / normalize here (gaussian_renderer/__init__.py:97-98)
+                    s = make_float3(fdgs_act_scale(s.x), fdgs_act_scale(s.y), fdgs_act_scale(s.z));
+                    q = fdgs_act_quat(q);
+                }
                 cov3d_from_scale_rot(s, scale_modifier, q, c6);
 #pragma unroll
                 for (int i = 0; i < 6; ++i) g.cov3D[6 * (size_t)idx + i] = c6[i];
@@ -144,7 +148,8 @@ k_preprocess(int P, int D, int M,
                     }
                     g.depths[idx] = p_view.z;
                     g.means2D[idx] = pix;
-                    g.conic_opacity[idx] = make_float4(conic.x, conic.y, conic.z, opacities[idx]);
+                    g.conic_opacity[idx] = make_float4(conic.x, conic.y, conic.z,
+                                                       activate ? fdgs_act_opacity(opacities[idx]) : opacities[idx]);
                     my_radius_i = (int)my_radius;
                     rx0 = x0; ry0 = y0; rx1 = x1; ry1 = y1;
                     touched = (uint32_t)((y1 - y0) * (x1 - x0));
@@ -642,6 +647,7 @@ int check_forward_args(const FdgsRasterForward* a) {
     if (has_sr == (a->cov3D_precomp != nullptr)) return FDGS_E_BADARG;
     if (a->shs && (a->M <= 0 || a->D < 0 || a->D > 3 || (a->D + 1) * (a->D + 1) > a->M)) return FDGS_E_BADARG;
     if (a->geom_bytes < FdgsGeom::bytes(a->P) || a->img_bytes < FdgsImg::bytes(a->W, a->H)) return FDGS_E_WORKSPACE;
+    if (a->activate && a->cov3D_precomp) return FDGS_E_BADARG;      // raw inputs only make sense with scales / rotations
     return FDGS_OK;
 }
 
@@ -671,7 +677,8 @@ static int launch_plan(const FdgsRasterForward* a, uint32_t cap, cudaStream_t st
     k_preprocess<<<(a->P + 255) / 256, 256, sh_smem, stream>>>(
         a->P, a->D, a->M, a->means3D, a->scales, a->scale_modifier, a->rotations, a->opacities, a->shs,
         a->cov3D_precomp, a->colors_precomp, a->viewmatrix, a->projmatrix, a->campos, a->W, a->H,
-        a->tanfovx, a->tanfovy, focal_x, focal_y, gx, gy, a->prefiltered, a->radii, g, im.tile_count, sh_staged);
+        a->tanfovx, a->tanfovy, focal_x, focal_y, gx, gy, a->prefiltered, a->radii, g, im.tile_count, sh_staged,
+        (a->activate && !a->cov3D_precomp) ? 1 : 0);
     }
     FDGS_LAUNCH_CHECK(a->debug, stream);
     { FDGS_PROF("k_tile_scan", stream);

@@ -9,6 +9,34 @@
 
 struct M3 { float m[3][3]; };   // m[column][row]
 
+// ---- the three activations between the deformation field and the rasterizer (gaussian_renderer/__init__.py:97-99:
+// torch.exp, F.normalize(dim=1, eps=1e-12), torch.sigmoid) and their VJPs.  ONE definition, used by the stand-alone
+// glue kernels (glue.cu) and by the preprocess kernels when they take the raw deformation outputs (`activate`), so both
+// routes produce the same bits.
+constexpr float FDGS_NORM_EPS = 1e-12f;
+__device__ __forceinline__ float fdgs_act_scale(float raw) { return expf(raw); }
+__device__ __forceinline__ float fdgs_act_opacity(float raw) { return 1.0f / (1.0f + expf(-raw)); }
+__device__ __forceinline__ float fdgs_quat_norm(const float4 q) {
+    return sqrtf(__fmaf_rn(q.w, q.w, __fmaf_rn(q.z, q.z, __fmaf_rn(q.y, q.y, __fmul_rn(q.x, q.x)))));
+}
+__device__ __forceinline__ float4 fdgs_act_quat(const float4 q) {
+    const float d = fmaxf(fdgs_quat_norm(q), FDGS_NORM_EPS);
+    return make_float4(q.x / d, q.y / d, q.z / d, q.w / d);
+}
+__device__ __forceinline__ float fdgs_act_scale_vjp(float g, float s) { return g * s; }
+__device__ __forceinline__ float fdgs_act_opacity_vjp(float g, float o) { return g * o * (1.0f - o); }
+// raw: the un-normalised quaternion, u = fdgs_act_quat(raw), g = dL/du
+__device__ __forceinline__ float4 fdgs_act_quat_vjp(const float4 raw, const float4 u, const float4 g) {
+    const float n = fdgs_quat_norm(raw);
+    if (n >= FDGS_NORM_EPS) {             // d(q / n): (g - u (u . g)) / n
+        const float dot = u.x * g.x + u.y * g.y + u.z * g.z + u.w * g.w;
+        const float inv = 1.0f / n;
+        return make_float4((g.x - u.x * dot) * inv, (g.y - u.y * dot) * inv, (g.z - u.z * dot) * inv, (g.w - u.w * dot) * inv);
+    }
+    // clamp_min(eps) is active: the denominator is the constant eps
+    return make_float4(g.x / FDGS_NORM_EPS, g.y / FDGS_NORM_EPS, g.z / FDGS_NORM_EPS, g.w / FDGS_NORM_EPS);
+}
+
 // R = A * B with the left-to-right summation order of a textbook column-major product.
 __device__ __forceinline__ M3 m3_mul(const M3& a, const M3& b) {
     M3 r;

@@ -176,6 +176,14 @@ class _DeformFunction(torch.autograd.Function):
             if (hm >> h) & 1:
                 gh = next(it)
                 g[h] = gh.contiguous() if gh is not None else None
+        # identity paths (mask == 1, scene/deformation.py:104-146): the upstream gradients of the scale / rotation /
+        # opacity / SH outputs ARE the gradients of the matching inputs.  A caller that owns the destination buffers
+        # (fdgs.dp: the all-reduce bucket) may take them here, BEFORE the deformation kernels are queued, and start
+        # reducing them while those kernels run; it returns the set of head indices it consumed.
+        consumed = ()
+        sink = getattr(mod, "identity_sink", None)
+        if sink is not None and not mod.args.apply_rotation and ctx.sh_coeffs == 16:
+            consumed = sink(g) or ()
         with torch.cuda.device(dev):
             a = L.FdgsDeformBackward()
             keep = mod._fill_net(a.net)
@@ -203,11 +211,11 @@ class _DeformFunction(torch.autograd.Function):
             del keep
         # identity paths (mask == 1, scene/deformation.py:104-146)
         d_point = d_xyz + g[0] if g[0] is not None else d_xyz
-        d_scales = g[1]
-        d_rot = g[2] if not mod.args.apply_rotation else None
-        d_opacity = g[3]
+        d_scales = g[1] if 1 not in consumed else None
+        d_rot = g[2] if (not mod.args.apply_rotation and 2 not in consumed) else None
+        d_opacity = g[3] if 3 not in consumed else None
         d_shs = None
-        if g[4] is not None:
+        if g[4] is not None and 4 not in consumed:
             d_shs = g[4] if ctx.sh_coeffs == 16 else g[4].sum(dim=1, keepdim=True)
         return (None, None, None, d_point, d_scales, d_rot, d_opacity, d_shs) + tuple(pgrads)
 
@@ -237,6 +245,7 @@ class Deformation(nn.Module):
         self.precision = 0      # 0: FP32-equivalent (3xTF32 on tcgen05), 1: single-pass TF32, 2: FP32 CUDA-core kernels
         self.grads_in_place = False    # see _alloc_param_grads
         self.save_activations = True   # training forward keeps the hidden activations (~3.2 KB/point) instead of recomputing
+        self.identity_sink = None      # see _DeformFunction.backward (set by fdgs.dp.train_iteration for its last view)
         self.validate_time = False     # True: check (one device sync) that times_sel is one constant per call, see forward_dynamic
         self._packed = None
         self._packed_key = None

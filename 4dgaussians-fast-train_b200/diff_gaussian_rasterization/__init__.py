@@ -152,7 +152,7 @@ class _Workspaces:
 
 def _forward_native(bg, means3D, colors_precomp, opacities, scales, rotations, scale_modifier,
                     cov3Ds_precomp, viewmatrix, projmatrix, tanfovx, tanfovy, image_height,
-                    image_width, sh, degree, campos, prefiltered, debug, want_debug_lists=False):
+                    image_width, sh, degree, campos, prefiltered, debug, want_debug_lists=False, activate=False):
     """Mirror of RasterizeGaussiansCUDA (rasterize_points.cu:35-117).
     Returns (num_rendered, color, depth, radii, geomBuffer, binningBuffer, imgBuffer[, extras])."""
     lib = L.load()
@@ -180,6 +180,7 @@ def _forward_native(bg, means3D, colors_precomp, opacities, scales, rotations, s
         a.P, a.D, a.M, a.W, a.H = P, int(degree), int(M), W, H
         a.tanfovx, a.tanfovy, a.scale_modifier = float(tanfovx), float(tanfovy), float(scale_modifier)
         a.prefiltered, a.debug = int(bool(prefiltered)), int(bool(debug))
+        a.activate = int(bool(activate))
         keep = [
             _f32(bg, "bg", dev), _f32(means3D, "means3D", dev), sh_c, _f32(colors_precomp, "colors_precomp", dev),
             _f32(opacities, "opacities", dev), _f32(scales, "scales", dev), _f32(rotations, "rotations", dev),
@@ -284,7 +285,7 @@ def _img_views(img, W, H):
 
 def _backward_native(bg, means3D, radii, colors_precomp, scales, rotations, scale_modifier, cov3Ds_precomp,
                      viewmatrix, projmatrix, tanfovx, tanfovy, grad_out_color, sh, degree, campos,
-                     geomBuffer, num_rendered, binningBuffer, imgBuffer, debug):
+                     geomBuffer, num_rendered, binningBuffer, imgBuffer, debug, activate=False):
     """Mirror of RasterizeGaussiansBackwardCUDA (rasterize_points.cu:119-198)."""
     lib = L.load()
     dev = means3D.device
@@ -307,6 +308,7 @@ def _backward_native(bg, means3D, radii, colors_precomp, scales, rotations, scal
             a.P, a.D, a.M, a.W, a.H, a.R = P, int(degree), int(M), W, H, int(num_rendered)
             a.tanfovx, a.tanfovy, a.scale_modifier = float(tanfovx), float(tanfovy), float(scale_modifier)
             a.debug = int(bool(debug))
+            a.activate = int(bool(activate))
             keep = [
                 _f32(bg, "bg", dev), _f32(means3D, "means3D", dev), _f32(sh, "sh", dev),
                 _f32(colors_precomp, "colors_precomp", dev), _f32(scales, "scales", dev),
@@ -420,6 +422,42 @@ class _RasterizeGaussians(torch.autograd.Function):
             None,
         )
         return grads
+
+
+class _RasterizeGaussiansRaw(torch.autograd.Function):
+    """The rasterizer fed with the RAW deformation outputs (log-scales, un-normalised quaternions, opacity logits): the
+    activations of gaussian_renderer/__init__.py:97-99 and their VJPs run inside the preprocess kernels
+    (FdgsRasterForward.activate), so the activated tensors never exist.  Same outputs as
+    rasterizer(..., opacities=sigmoid(o), scales=exp(s), rotations=normalize(r)); gradients are w.r.t. the raw inputs."""
+
+    @staticmethod
+    def forward(ctx, means3D, means2D, sh, opacity_logits, log_scales, raw_rotations, raster_settings):
+        e = torch.Tensor([])
+        s = raster_settings
+        num_rendered, color, depth, radii, geomBuffer, binningBuffer, imgBuffer = _forward_native(
+            s.bg, means3D, e, opacity_logits, log_scales, raw_rotations, s.scale_modifier, e, s.viewmatrix, s.projmatrix, s.tanfovx,
+            s.tanfovy, s.image_height, s.image_width, sh, s.sh_degree, s.campos, s.prefiltered, s.debug, activate=True)
+        ctx.raster_settings = raster_settings
+        ctx.num_rendered = num_rendered
+        ctx.save_for_backward(means3D, log_scales, raw_rotations, radii, sh, geomBuffer, binningBuffer, imgBuffer)
+        ctx.mark_non_differentiable(radii)
+        return color, radii, depth
+
+    @staticmethod
+    def backward(ctx, grad_out_color, grad_radii, grad_depth):
+        s = ctx.raster_settings
+        means3D, log_scales, raw_rotations, radii, sh, geomBuffer, binningBuffer, imgBuffer = ctx.saved_tensors
+        e = torch.Tensor([])
+        (grad_means2D, _gc, grad_opacities, grad_means3D, _gcov, grad_sh, grad_scales, grad_rotations) = _backward_native(
+            s.bg, means3D, radii, e, log_scales, raw_rotations, s.scale_modifier, e, s.viewmatrix, s.projmatrix, s.tanfovx,
+            s.tanfovy, grad_out_color, sh, s.sh_degree, s.campos, geomBuffer, ctx.num_rendered, binningBuffer, imgBuffer,
+            s.debug, activate=True)
+        return grad_means3D, grad_means2D, grad_sh.view(sh.shape), grad_opacities, grad_scales, grad_rotations, None
+
+
+def rasterize_gaussians_raw(means3D, means2D, shs, opacity_logits, log_scales, raw_rotations, raster_settings):
+    """(rendered_image, radii, depth) from the raw deformation outputs; see _RasterizeGaussiansRaw."""
+    return _RasterizeGaussiansRaw.apply(means3D, means2D, shs, opacity_logits, log_scales, raw_rotations, raster_settings)
 
 
 class GaussianRasterizationSettings(NamedTuple):

@@ -104,6 +104,20 @@ def grads_in_place(module, on=True):
     return module
 
 
+def _sm_limit(on, spare=8):
+    """Caps the persistent fdgs deformation kernels at (SM count - spare) CTAs while an all-reduce is in flight."""
+    try:
+        from . import _lib
+        lib = _lib.load()
+    except Exception:
+        return
+    if on:
+        n = torch.cuda.get_device_properties(torch.cuda.current_device()).multi_processor_count
+        lib.fdgs_set_sm_limit(max(1, n - spare))
+    else:
+        lib.fdgs_set_sm_limit(0)
+
+
 def l1_view_loss(image, gt, n_views_total):
     """This view's share of the reference's loss: l1_loss(cat(images), cat(gts)) over B equal-size views
     (utils/loss_utils.py l1_loss = mean|a-b|, train.py:231-244) == sum_i mean|img_i - gt_i| / B."""
@@ -185,11 +199,12 @@ def train_iteration(render_fn, pc, cams, gts, bg, bucket, rank=0, world=1, read_
     share_features: concatenate the SH coefficients once per iteration, let the views' SH gradients sum in one [P,16,3]
     buffer and split it into _features_dc / _features_rest gradients once (same additions, in the same view order, as the
     reference's per-view cat backward; saves a cat and a strided two-way gradient accumulation per view).
-    overlap_sh (world > 1): the SH gradients are two thirds of the bucket and are final as soon as the LAST view's rasterizer
-    backward has run, before its deformation backward; their part of the all-reduce is started there (asynchronously, on
-    the process group's stream) and the rest of the bucket follows at the end - the sums are the same, in three
-    collectives instead of one.  The collective SCHEDULE depends only on rank-independent inputs (overlap_sh, the
-    process group, the bucket layout): a rank that owns no view (world > B) issues the same three range all-reduces.
+    overlap_sh: the gradients of scale / rotation / opacity / SH (56 of 59 floats per Gaussian, 80 % of the bucket) are final
+    as soon as the LAST view's rasterizer backward has run, before its deformation backward; their part of the
+    all-reduce is started there (asynchronously, on the process group's stream) and the rest of the bucket follows at
+    the end - the sums are the same, in three collectives instead of one.  The collective SCHEDULE depends only on
+    rank-independent inputs (overlap_sh, the process group, the bucket layout): a rank that owns no view (world > B) issues
+    the same three range all-reduces.  At world size 1 the same code path runs without the collectives.
     reduce_stats (world > 1): the densifier's inputs are made identical on every rank - `radii` is all-reduced with MAX
     (train.py:229 takes the max over ALL B views) and visibility is derived from it (train.py:230: any over views ==
     max radius > 0), so that replicas take the same split / prune decisions and keep the same P.
@@ -230,55 +245,79 @@ def train_iteration(render_fn, pc, cams, gts, bg, bucket, rank=0, world=1, read_
             leaf = feats.detach().requires_grad_(True)
             pc_it = _SharedFeatures(pc, leaf)
     distributed = dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1
+    # ---- early part of the all-reduce (overlap_sh) ---------------------------------------------------------------------
+    # The gradients of _scaling, _rotation, _opacity, _features_dc, _features_rest (56 of the 59 floats per Gaussian; adjacent
+    # bucket slots in that order) pass through the deformation's identity paths unchanged, so they are final as soon as the
+    # LAST view's rasterizer backward has run.  With an fdgs deformation (`identity_sink`) they are added into their bucket
+    # slots right there, BEFORE that view's deformation-backward kernels are queued, and their all-reduce starts on the
+    # process group's stream while those kernels run (which leave it a few SMs: fdgs_set_sm_limit).  Without the sink
+    # (another deformation module) the same three collectives are issued after the loop: same sums, no overlap.
     span = None
-    if overlap_sh and distributed and has_feats and hasattr(pc, "_features_dc") and hasattr(pc, "_features_rest"):
-        span = bucket.span([pc._features_dc, pc._features_rest])      # rank-independent: same bucket layout everywhere
-    early = []          # [async work handle] once the SH part of the all-reduce is in flight
-    hooks = []
-    for i in mine:
-        if span is not None and i == mine[-1]:
-            if leaf is not None:
-                def _sh_ready(t):
-                    # the shared leaf now holds this rank's summed SH gradient: split it into the (zeroed) bucket slots -
-                    # what cat's backward would do after the loop - and start reducing them
-                    with torch.no_grad():
-                        pc._features_dc.grad.add_(t.grad[:, :pc._features_dc.shape[1]])
-                        pc._features_rest.grad.add_(t.grad[:, pc._features_dc.shape[1]:])
-                    early.append(bucket.all_reduce_range(*span, async_op=True))
-                hooks.append(leaf.register_post_accumulate_grad_hook(_sh_ready))
-            else:
-                seen = []
+    early_params = None
+    if overlap_sh and has_feats and hasattr(pc, "_features_dc") and hasattr(pc, "_features_rest"):
+        if all(hasattr(pc, n) for n in ("_scaling", "_rotation", "_opacity")):
+            early_params = [pc._scaling, pc._rotation, pc._opacity, pc._features_dc, pc._features_rest]
+            span = bucket.span(early_params)                        # rank-independent: same bucket layout everywhere
+        if span is None:                                            # other slot order: the SH slots alone (2/3 of the bucket)
+            early_params = [pc._features_dc, pc._features_rest]
+            span = bucket.span(early_params)
+    early = []          # [async work handle or None] once the early part of the all-reduce is in flight
+    sink_mod = getattr(getattr(pc, "_deformation", None), "deformation_net", None) if span is not None else None
+    sink_state = {"leaf_done": False}
 
-                def _sh_part(t):
-                    seen.append(t)
-                    if len(seen) == 2:
-                        early.append(bucket.all_reduce_range(*span, async_op=True))
-                hooks.append(pc._features_dc.register_post_accumulate_grad_hook(_sh_part))
-                hooks.append(pc._features_rest.register_post_accumulate_grad_hook(_sh_part))
-        out = render_fn(cams[i], pc_it, bg_color=bg, stage="fine")
-        loss = (loss_fn or l1_view_loss)(out["render"], gts[i], B)
-        loss.backward()
+    def _start_early():
+        early.append(bucket.all_reduce_range(*span, async_op=True) if distributed else None)
+
+    def _sink(g):
+        """Called by the deformation backward of the rank's LAST view with the upstream gradients of its five outputs."""
+        took = []
+        with torch.no_grad():
+            if len(early_params) == 5:
+                for h, p in ((1, pc._scaling), (2, pc._rotation), (3, pc._opacity)):
+                    if g[h] is not None and p.grad is not None:
+                        p.grad.add_(g[h].view(p.grad.shape))
+                        took.append(h)
+            if g[4] is not None and pc._features_dc.grad is not None and pc._features_rest.grad is not None:
+                n_dc = pc._features_dc.shape[1]
+                tot = g[4] if (leaf is None or leaf.grad is None) else leaf.grad.add_(g[4])   # earlier views' sum + this view
+                pc._features_dc.grad.add_(tot[:, :n_dc])
+                pc._features_rest.grad.add_(tot[:, n_dc:])
+                sink_state["leaf_done"] = True
+                took.append(4)
+        if 4 in took and (len(early_params) == 2 or len(took) == 4):
+            _start_early()
+            if distributed:
+                _sm_limit(True)
+        return took
+
+    for i in mine:
+        last = span is not None and i == mine[-1]
+        if last and sink_mod is not None and hasattr(sink_mod, "identity_sink"):
+            sink_mod.identity_sink = _sink
+        try:
+            out = render_fn(cams[i], pc_it, bg_color=bg, stage="fine")
+            loss = (loss_fn or l1_view_loss)(out["render"], gts[i], B)
+            loss.backward()
+        finally:
+            if last and sink_mod is not None and hasattr(sink_mod, "identity_sink"):
+                sink_mod.identity_sink = None
+                _sm_limit(False)
         vs = out["viewspace_points"].grad
         if vs is not None and "viewspace" in bucket.extra:
             bucket.extra["viewspace"].add_(vs)
         loss_sum = loss.detach() if loss_sum is None else loss_sum + loss.detach()
         radii_max = out["radii"] if radii_max is None else torch.maximum(radii_max, out["radii"])
-    for h in hooks:
-        h.remove()
+    if leaf is not None and leaf.grad is not None and not sink_state["leaf_done"]:
+        feats.backward(leaf.grad)               # the once-per-iteration cat's backward: split into _features_dc / _features_rest
     if span is not None:
-        # every rank issues the same three collectives in the same order: [SH span], [0, lo), [hi, end)
+        # every rank issues the same three collectives in the same order: [early span], [0, lo), [hi, end)
         if not early:
-            # no hook fired on this rank (it owns no view, or its SH parameters received no gradient)
-            if leaf is not None and leaf.grad is not None:
-                feats.backward(leaf.grad)
-            early.append(bucket.all_reduce_range(*span, async_op=True))
-        bucket.all_reduce_range(0, span[0])
-        bucket.all_reduce_range(span[1], bucket.flat.numel())
+            _start_early()                      # no sink on this rank (it owns no view / foreign deformation module)
+        bucket.all_reduce_range(0, span[0]) if distributed else None
+        bucket.all_reduce_range(span[1], bucket.flat.numel()) if distributed else None
         if early[0] is not None:
             early[0].wait()
     else:
-        if leaf is not None and leaf.grad is not None:
-            feats.backward(leaf.grad)
         bucket.all_reduce()
     if radii_max is None:           # this rank owns no view of the batch
         P = bucket.extra["viewspace"].shape[0] if "viewspace" in bucket.extra else pc.get_xyz.shape[0]

@@ -6,15 +6,19 @@ Differences, none observable in the results:
     already on the device;
   * `time` is passed as one device scalar instead of a [P,1] repeat (:52) — the fused deformation
     kernel takes one timestamp per view;
-  * when the model binds the reference's three activations (exp / normalize / sigmoid, :97-99) they run as
-    one fused kernel each way (fdgs.activations); any other callables are used as they are.
+  * when the model binds the reference's three activations (exp / normalize / sigmoid, :97-99) they run INSIDE the
+    rasterizer's preprocess kernels, forward and backward (`rasterize_gaussians_raw`; the activated [P,3] / [P,4] / [P,1]
+    tensors never exist in memory) - or, with `fold_activations = False`, as one fused kernel each way
+    (fdgs.activations); any other callables are used as they are.
 """
 import math
 
 import torch
 
 from .activations import fused_activations, is_reference_activations
-from .diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer
+from .diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer, rasterize_gaussians_raw
+
+fold_activations = True      # False: keep the activations as their own fused kernel pair (fdgs.activations); A/B and parity tests
 
 
 def render(viewpoint_camera, pc, pipe=None, bg_color=None, scaling_modifier=1.0, override_color=None,
@@ -62,6 +66,14 @@ def render(viewpoint_camera, pc, pipe=None, bg_color=None, scaling_modifier=1.0,
     else:
         raise NotImplementedError
 
+    colors_precomp = override_color
+    if (scales_final.is_cuda and is_reference_activations(pc) and colors_precomp is None and not debug
+            and opacity_final.dim() == 2 and fold_activations):
+        # exp / normalize / sigmoid (:97-99) and their VJPs run INSIDE the rasterizer's preprocess kernels
+        rendered_image, radii, depth = rasterize_gaussians_raw(means3D_final, means2D, shs_final, opacity_final, scales_final,
+                                                               rotations_final, raster_settings)
+        return {"render": rendered_image, "viewspace_points": screenspace_points, "visibility_filter": radii > 0,
+                "radii": radii, "depth": depth}
     if scales_final.is_cuda and is_reference_activations(pc):
         scales_final, rotations_final, opacity = fused_activations(scales_final, rotations_final, opacity_final)
     else:
@@ -69,7 +81,6 @@ def render(viewpoint_camera, pc, pipe=None, bg_color=None, scaling_modifier=1.0,
         rotations_final = pc.rotation_activation(rotations_final)
         opacity = pc.opacity_activation(opacity_final)
 
-    colors_precomp = override_color
     rendered_image, radii, depth = rasterizer(
         means3D=means3D_final, means2D=means2D, shs=shs_final if colors_precomp is None else None,
         colors_precomp=colors_precomp, opacities=opacity, scales=scales_final, rotations=rotations_final,

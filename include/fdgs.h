@@ -47,6 +47,9 @@ int fdgs_compiled_arch(void);
  * launch of the library record a start/stop event pair on its stream; collect() synchronises the
  * device and writes one "kernel_name launches total_ms" line per kernel into buf, then clears.
  * fdgs_launch_count() = number of library kernels launched so far in this process.            */
+/* The persistent deformation kernels run one CTA per SM and leave no room for a kernel of another stream.  n > 0 caps
+ * their grids at n CTAs (e.g. SM count - 8 while a gradient all-reduce is in flight, fdgs.dp overlap); 0 = all SMs.  */
+void fdgs_set_sm_limit(int n);
 void fdgs_profile_enable(int on);
 int fdgs_profile_collect(char* buf, size_t n);
 unsigned long long fdgs_launch_count(void);
@@ -94,6 +97,11 @@ typedef struct FdgsRasterForward {
      * point_list_keys / point_list (RAST/cuda_rasterizer/rasterizer_impl.cu:181-194) */
     uint64_t* keys_out;
     uint32_t* point_list_out;
+    /* 1 = `scales`, `rotations`, `opacities` are the RAW deformation outputs (log-scales, un-normalised quaternions, opacity
+     * logits): the preprocess kernel applies the activations of gaussian_renderer/__init__.py:97-99 itself (exp,
+     * F.normalize(dim=1, eps=1e-12), sigmoid - the same device functions fdgs_activate_forward uses, so the same bits), and the
+     * activated [P,3] / [P,4] / [P,1] tensors never exist in memory.  Needs scales + rotations (not cov3D_precomp).          */
+    int32_t activate;
 } FdgsRasterForward;
 
 /* Stage 1 of Rasterizer::forward (RAST/cuda_rasterizer/rasterizer_impl.cu:198-282):
@@ -162,6 +170,9 @@ typedef struct FdgsRasterBackward {
     float* dL_dsh;               /* [P,M,3] or NULL when M == 0 */
     float* dL_dscales;           /* [P,3] */
     float* dL_drots;             /* [P,4] */
+    /* same flag as the forward call's: `scales` / `rotations` are the raw values, and dL_dscales / dL_drots / dL_dopacity come
+     * back as gradients w.r.t. the RAW log-scales / quaternions / logits (the activations' VJPs are applied in the kernel) */
+    int32_t activate;
 } FdgsRasterBackward;
 
 /* Rasterizer::backward (RAST/cuda_rasterizer/rasterizer_impl.cu:343-437):
@@ -379,6 +390,23 @@ int fdgs_adam_step(const FdgsAdamStep* a, void* stream);
  * xyz_gradient_accum[i] += || viewspace_grad[i, :2] ||,  denom[i] += 1.   Any of the three outputs may be NULL.           */
 int fdgs_densify_stats(int P, const int32_t* radii, const uint8_t* visible, const float* viewspace_grad /* [P,3] */,
                        float* max_radii2D, float* xyz_gradient_accum, float* denom, void* stream);
+
+/* ---- init-time native pieces ---------------------------------------------------------------------------
+ * simple_knn's distCUDA2 (submodules/simple-knn/simple_knn.cu:65-215; scene/gaussian_model.py:145 initialises the scales
+ * from it): mean_dist2[i] = mean of the squared distances from point i to its 3 nearest other points.  Exact 3-NN on a
+ * uniform hash grid (the reference prunes Morton-sorted boxes; the three distances, their expression and the mean are the
+ * same, so the result is bit-identical).  ws: fdgs_knn_ws_bytes(P) bytes of device scratch.                               */
+size_t fdgs_knn_ws_bytes(int P);
+int fdgs_knn_mean_dist2(int P, const float* points /* [P,3] */, float* mean_dist2 /* [P] */, void* ws, size_t ws_bytes, void* stream);
+
+/* Instant4D grid pruning (utils/grid_pruning.py:16-41 -> open3d PointCloud::VoxelDownSample): voxel index =
+ * floor((p - (min_bound - voxel_size / 2)) / voxel_size) per axis, one output point per occupied voxel = the mean position
+ * (and mean colour, when colors != NULL) of its points, accumulated in double like open3d.  The order of the output rows is
+ * unspecified (open3d iterates an unordered_map).  *n_out (DEVICE int32) receives the number of occupied voxels; at most
+ * max_out rows are written.  ws: fdgs_voxel_downsample_ws_bytes(P) bytes of device scratch.                             */
+size_t fdgs_voxel_downsample_ws_bytes(int P);
+int fdgs_voxel_downsample(int P, const float* points, const float* colors, double voxel_size, float* out_points,
+                          float* out_colors, int max_out, int32_t* n_out, void* ws, size_t ws_bytes, void* stream);
 
 #ifdef __cplusplus
 }

@@ -141,3 +141,29 @@ def test_speculative_iteration_equals_exact_and_redoes_on_overflow():
         R.SPEC_SLACK = slack
     assert abs(l2 - l0) <= 1e-6 * abs(l0) and torch.equal(r0, r2)
     assert util.rel_err(bucket.flat, f0) < 1e-5
+
+
+@pytest.mark.parametrize("views", [1, 3])
+def test_early_identity_gradients_equal_the_autograd_route(views):
+    """train_iteration(overlap_sh=True): scale / rotation / opacity / SH gradients of the last view are added into their
+    bucket slots by the deformation backward's identity sink (before its kernels run; where the early all-reduce starts at
+    world > 1) instead of by autograd after it.  Same additions: the bucket is identical up to float-atomic noise."""
+    import bench
+    import fdgs  # noqa: F401
+    from fdgs.dp import train_iteration
+    from fdgs.render import render as render_fn
+    from fdgs.losses import l1_view_loss as loss_fn
+    dev = "cuda:0"
+    cfg, args, pc, net, cams, gts_host = bench.build_scene("dynerf_small", "fdgs", dev, views, 0)
+    bucket = bench.make_bucket(pc, net, dev)
+    assert bucket.span([pc._scaling, pc._rotation, pc._opacity, pc._features_dc, pc._features_rest]) is not None
+    bg = torch.ones(3, device=dev)
+    gts = [g.to(dev) for g in gts_host]
+    l0, _, _ = train_iteration(render_fn, pc, cams, gts, bg, bucket, 0, 1, read_loss=True, loss_fn=loss_fn)
+    f0 = bucket.flat.clone()
+    l1, _, _ = train_iteration(render_fn, pc, cams, gts, bg, bucket, 0, 1, read_loss=True, loss_fn=loss_fn, overlap_sh=True)
+    assert net.deformation_net.identity_sink is None
+    assert abs(l1 - l0) <= 1e-6 * abs(l0)
+    assert util.rel_err(bucket.flat, f0) < 1e-5
+    for p in (pc._scaling, pc._rotation, pc._opacity, pc._features_dc, pc._features_rest):
+        assert float(p.grad.abs().sum()) > 0

@@ -97,3 +97,51 @@ def test_fused_l1_loss_matches_aten(shape):
     torch.testing.assert_close(b.grad, b2.grad, rtol=1e-6, atol=0)
     lv = l1_view_loss(a.detach(), b.detach(), 8)
     torch.testing.assert_close(lv, l_ref.detach() / 8, rtol=1e-5, atol=0)
+
+
+def test_activations_folded_into_the_rasterizer_equal_the_separate_kernels():
+    """rasterize_gaussians_raw (exp / normalize / sigmoid and their VJPs inside k_preprocess / k_preprocess_bwd) vs
+    fused_activations followed by the ordinary rasterizer call: the same device functions, so images, radii and depth are
+    bit-identical and the raw-input gradients agree up to the blend backward's float atomics; and both agree with ATen."""
+    import math
+    import util
+    from fdgs import synth
+    from fdgs.activations import fused_activations
+    from fdgs.diff_gaussian_rasterization import GaussianRasterizer, rasterize_gaussians_raw
+    P, W, H = 20_000, 320, 200
+    g = synth.make_gaussians(P, extent=1.3, logscale=-3.8, seed=4, device="cuda")
+    g["rotation"][:5] = 0.0                                 # zero quaternions: the clamp_min(eps) branch of normalize
+    cam = synth.make_camera(W, H, 0.69, angle=0.2, device="cuda")
+    sc = dict(W=W, H=H, tanfovx=math.tan(cam.FoVx * 0.5), tanfovy=math.tan(cam.FoVy * 0.5), bg=torch.ones(3, device="cuda"),
+              viewmatrix=cam.world_view_transform, projmatrix=cam.full_proj_transform, campos=cam.camera_center, sh_degree=3)
+    settings = util.settings(sc)
+    shs0 = torch.cat([g["f_dc"], g["f_rest"]], dim=1)
+    gimg = torch.randn((3, H, W), generator=torch.Generator().manual_seed(2)).cuda()
+
+    def run(mode):
+        leaves = {k: g[k].clone().requires_grad_(True) for k in ("xyz", "scaling", "rotation", "opacity")}
+        shs = shs0.clone().requires_grad_(True)
+        m2d = torch.zeros((P, 3), device="cuda", requires_grad=True)
+        if mode == "folded":
+            color, radii, depth = rasterize_gaussians_raw(leaves["xyz"], m2d, shs, leaves["opacity"], leaves["scaling"],
+                                                          leaves["rotation"], settings)
+        else:
+            if mode == "fused":
+                s, r, o = fused_activations(leaves["scaling"], leaves["rotation"], leaves["opacity"])
+            else:
+                s, r, o = torch.exp(leaves["scaling"]), torch.nn.functional.normalize(leaves["rotation"]), torch.sigmoid(leaves["opacity"])
+            color, radii, depth = GaussianRasterizer(settings)(means3D=leaves["xyz"], means2D=m2d, opacities=o, shs=shs, scales=s,
+                                                               rotations=r)
+        color.backward(gimg)
+        grads = {k: v.grad for k, v in leaves.items()}
+        grads["shs"], grads["m2d"] = shs.grad, m2d.grad
+        return color.detach(), radii, depth.detach(), grads
+
+    cf, rf, df, gf = run("folded")
+    cu, ru, du, gu = run("fused")
+    ca, ra, da, ga = run("aten")
+    assert torch.equal(cf, cu) and torch.equal(rf, ru) and torch.equal(df, du)
+    assert int((rf != ra).sum()) <= 2 and util.rel_err(cf, ca) < 1e-4      # ATen's exp / sigmoid differ by an ulp
+    for k in gf:
+        assert util.rel_err(gf[k], gu[k]) < 2e-6, k
+        assert util.rel_err(gf[k], ga[k]) < 2e-4, k

@@ -188,3 +188,21 @@ def test_raster_oracle_empty_and_culled_inputs():
     o = RO.rasterize(**e)
     assert o["num_rendered"] == 0
     assert np.allclose(o["color"], a["bg"][:, None, None])
+
+
+def test_init_oracle_knn_against_kdtree_and_voxel_counts():
+    """oracle/init_oracle.py: the brute-force 3-NN mean squared distance equals scipy's exact k-d tree query (float64, so
+    equal up to FP32 rounding of the restated expression), and the voxel down-sampling conserves mass."""
+    import init_oracle
+    from scipy.spatial import cKDTree
+    rng = np.random.default_rng(3)
+    p = rng.uniform(-1, 1, size=(3000, 3)).astype(np.float32)
+    got = init_oracle.knn_mean_dist2(p)
+    d, _ = cKDTree(p.astype(np.float64)).query(p.astype(np.float64), k=4)
+    want = (d[:, 1:] ** 2).mean(axis=1)
+    assert np.allclose(got, want, rtol=2e-6, atol=0)
+    c = rng.uniform(0, 1, size=(3000, 3)).astype(np.float32)
+    vp, vc = init_oracle.voxel_downsample(p, c, 0.25)
+    assert 1 < vp.shape[0] < 3000 and vc.shape == vp.shape
+    one, _ = init_oracle.voxel_downsample(p, c, 100.0)          # one voxel: the centroid
+    assert one.shape == (1, 3) and np.allclose(one[0], p.astype(np.float64).mean(0), atol=1e-6)
