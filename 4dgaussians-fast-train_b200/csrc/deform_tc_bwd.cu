@@ -970,7 +970,8 @@ k_deform_bwd_weights(WArgs args)
     __shared__ __align__(8) uint64_t bars[WB_COUNT + 1];
     __shared__ uint32_t tmem_slot;
     __shared__ float csumA[128], csumB[128];
-    __shared__ float cc_acc[128 * 4];          // C of a CUDA-core job (nb <= 4)
+    float* cc_acc = sm;                        // C [128][4] of a CUDA-core job (nb <= 4): the head of the tile-stage area,
+                                               // which such a job never uses (static shared memory is at its limit)
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 #ifdef FDGS_PHASE_TIMING
     const long long t_start_ = clock64();

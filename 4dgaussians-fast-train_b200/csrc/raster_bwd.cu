@@ -120,6 +120,51 @@ __device__ __forceinline__ void warp_reduce10(float (&v)[10], int lane) {
     v[0] += __shfl_xor_sync(FULL, v[0], 1);
 }
 
+// The same transposed butterfly inside each HALF-warp (16 lanes, 11 shuffles: 5 + 3 + 2 + 1): on return lane L holds in v[0] the
+// half-warp total of slot b3*5 + b2*3 + b1*2 + b0 (b_k = bit k of L) when that path did not run through a pad, i.e. for
+// (b2, b1) != (1, 1) and (b2, b1, b0) != (0, 1, 1): ten lanes of sixteen (the tenth slot is the zero pad).
+__device__ __forceinline__ void half_reduce10(float (&v)[10], int lane) {
+    {
+        const bool up = lane & 8;
+#pragma unroll
+        for (int k = 0; k < 5; ++k) {
+            const float send = up ? v[k] : v[k + 5];
+            const float keep = up ? v[k + 5] : v[k];
+            v[k] = keep + __shfl_xor_sync(FULL, send, 8);
+        }
+    }
+    {
+        const bool up = lane & 4;
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            const float hv = (k + 3 < 5) ? v[k + 3] : 0.f;
+            const float send = up ? v[k] : hv;
+            const float keep = up ? hv : v[k];
+            v[k] = keep + __shfl_xor_sync(FULL, send, 4);
+        }
+    }
+    {
+        const bool up = lane & 2;
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+            const float hv = (k + 2 < 3) ? v[k + 2] : 0.f;
+            const float send = up ? v[k] : hv;
+            const float keep = up ? hv : v[k];
+            v[k] = keep + __shfl_xor_sync(FULL, send, 2);
+        }
+    }
+    {
+        const bool up = lane & 1;
+        const float send = up ? v[0] : v[1];
+        const float keep = up ? v[1] : v[0];
+        v[0] = keep + __shfl_xor_sync(FULL, send, 1);
+    }
+}
+
+#ifndef BLEND_BWD_STREAMS
+#define BLEND_BWD_STREAMS 2
+#endif
+
 // NPX pixels per thread (rows py and py + 4): a warp covers an 8 x (4 NPX) sub-rectangle of the tile, so one cull test,
 // one 12-shuffle reduction and one set of shared-memory atomics serve 32 NPX pixels of a hit.
 template <int NPX>
@@ -145,6 +190,14 @@ k_blend_bwd(const uint2* __restrict__ ranges, const FdgsRecord* __restrict__ rec
     const float pxf = (float)px;
     const float cx0 = (float)bx0, cy0 = (float)by0;
     const float cx1 = (float)min(bx0 + 7, W - 1), cy1 = (float)min(by0 + 4 * NPX - 1, H - 1);
+#if BLEND_BWD_STREAMS == 2
+    // two record streams per warp: half-warp h owns the 8 x (2 NPX) block of rows [by0 + 2 NPX h, by0 + 2 NPX (h + 1)), a thread
+    // its column and the rows rp, rp + 2, ... of that block; each half walks only the records that survive ITS block's test
+    static_assert(NPX == 2, "the two-stream mapping is written for two pixels per thread");
+    const int half = lane >> 4, rp = (lane >> 3) & 1;
+    const float cyA1 = (float)min(by0 + 2 * NPX - 1, H - 1), cyB0 = (float)(by0 + 2 * NPX);
+    const bool blockB = by0 + 2 * NPX < H;
+#endif
     const size_t HW = (size_t)H * W;
     const uint2 range = ranges[tile];
 
@@ -154,7 +207,11 @@ k_blend_bwd(const uint2* __restrict__ ranges, const FdgsRecord* __restrict__ rec
     uint32_t lmax = 0;
 #pragma unroll
     for (int j = 0; j < NPX; ++j) {
+#if BLEND_BWD_STREAMS == 2
+        const int py = by0 + 2 * NPX * half + rp + 2 * j;
+#else
         const int py = by0 + (lane >> 3) + 4 * j;
+#endif
         const bool inside = px < W && py < H;
         const size_t pix_id = (size_t)py * W + px;
         pyf[j] = (float)py;
@@ -181,6 +238,9 @@ k_blend_bwd(const uint2* __restrict__ ranges, const FdgsRecord* __restrict__ rec
     for (int i = threadIdx.x; i < BATCH * NACC; i += NT) (&acc[0][0])[i] = 0.f;
     __syncthreads();
     const uint32_t wmax = __reduce_max_sync(FULL, lmax);
+#if BLEND_BWD_STREAMS == 2
+    const uint32_t hmaxA = __reduce_max_sync(FULL, half ? 0u : lmax), hmaxB = __reduce_max_sync(FULL, half ? lmax : 0u);
+#endif
     if (lane == 0 && wmax) atomicMax(&s_maxc, wmax);
     __syncthreads();
     const int total = (int)min(s_maxc, range.y - range.x);     // records beyond the last contributor are dead
@@ -206,22 +266,8 @@ k_blend_bwd(const uint2* __restrict__ ranges, const FdgsRecord* __restrict__ rec
         if (wmax > (uint32_t)lo) {                        // warp-uniform: something here can still matter
             for (int c1 = cnt; c1 > 0; c1 -= 32) {        // chunks of 32, from the back
                 const int j = c1 - 1 - lane;              // lane 0 tests the last record of the chunk
-                bool keep = false;
-                if (j >= 0) {
-                    const float4 q0 = reinterpret_cast<const float4*>(&rec[j])[0];
-                    const float4 q1 = reinterpret_cast<const float4*>(&rec[j])[1];
-                    keep = ((uint32_t)(lo + j) < wmax) && !(q1.y <= 0.f) &&
-                           !rect_culled(q0.x, q0.y, q0.z, q0.w, q1.x, rec[j].cull, cx0, cy0, cx1, cy1);
-                }
-                unsigned m = __ballot_sync(FULL, keep);
-                while (m) {
-                    const int l = __ffs(m) - 1;           // ascending lane == descending position
-                    m &= m - 1;
-                    const int jj = c1 - 1 - l;
-                    const uint32_t pos = (uint32_t)(lo + jj);
-                    float v[10];
-#pragma unroll
-                    for (int k = 0; k < 10; ++k) v[k] = 0.f;
+                // gradient partials of record jj for this thread's pixels -> v[0..8]
+                auto eval = [&](int jj, uint32_t pos, float (&v)[10]) {
 #pragma unroll
                     for (int pj = 0; pj < NPX; ++pj) {
                         if (pos < last_contributor[pj]) {
@@ -266,10 +312,58 @@ k_blend_bwd(const uint2* __restrict__ ranges, const FdgsRecord* __restrict__ rec
                             }
                         }
                     }
+                };
+#if BLEND_BWD_STREAMS == 2
+                bool keepA = false, keepB = false;
+                if (j >= 0) {
+                    const float4 q0 = reinterpret_cast<const float4*>(&rec[j])[0];
+                    const float4 q1 = reinterpret_cast<const float4*>(&rec[j])[1];
+                    if (!(q1.y <= 0.f)) {
+                        const float cull = rec[j].cull;
+                        keepA = ((uint32_t)(lo + j) < hmaxA) && !rect_culled(q0.x, q0.y, q0.z, q0.w, q1.x, cull, cx0, cy0, cx1, cyA1);
+                        keepB = blockB && ((uint32_t)(lo + j) < hmaxB) &&
+                                !rect_culled(q0.x, q0.y, q0.z, q0.w, q1.x, cull, cx0, cyB0, cx1, cy1);
+                    }
+                }
+                unsigned mA = __ballot_sync(FULL, keepA), mB = __ballot_sync(FULL, keepB);
+                unsigned mine = half ? mB : mA;
+                const int hslot = ((lane >> 3) & 1) * 5 + ((lane >> 2) & 1) * 3 + ((lane >> 1) & 1) * 2 + (lane & 1);
+                const bool hvalid = !(((lane >> 2) & 1) && ((lane >> 1) & 1)) && !(!((lane >> 2) & 1) && ((lane >> 1) & 1) && (lane & 1)) &&
+                                    hslot < NACC;
+                while (mA | mB) {
+                    const int l = mine ? __ffs(mine) - 1 : 0;     // ascending lane == descending position
+                    const int jj = c1 - 1 - l;
+                    float v[10];
+#pragma unroll
+                    for (int k = 0; k < 10; ++k) v[k] = 0.f;
+                    if (mine) eval(jj, (uint32_t)(lo + jj), v);
+                    half_reduce10(v, lane);
+                    if (mine && hvalid && v[0] != 0.f) atomicAdd(&acc[jj][hslot], v[0]);
+                    mine &= mine - 1;                             // 0 stays 0
+                    mA &= mA - 1; mB &= mB - 1;
+                }
+#else
+                bool keep = false;
+                if (j >= 0) {
+                    const float4 q0 = reinterpret_cast<const float4*>(&rec[j])[0];
+                    const float4 q1 = reinterpret_cast<const float4*>(&rec[j])[1];
+                    keep = ((uint32_t)(lo + j) < wmax) && !(q1.y <= 0.f) &&
+                           !rect_culled(q0.x, q0.y, q0.z, q0.w, q1.x, rec[j].cull, cx0, cy0, cx1, cy1);
+                }
+                unsigned m = __ballot_sync(FULL, keep);
+                while (m) {
+                    const int l = __ffs(m) - 1;           // ascending lane == descending position
+                    m &= m - 1;
+                    const int jj = c1 - 1 - l;
+                    float v[10];
+#pragma unroll
+                    for (int k = 0; k < 10; ++k) v[k] = 0.f;
+                    eval(jj, (uint32_t)(lo + jj), v);
                     warp_reduce10(v, lane);
                     const int slot = ((lane >> 4) & 1) * 5 + ((lane >> 3) & 1) * 3 + ((lane >> 2) & 1) * 2 + ((lane >> 1) & 1);
                     if (!(lane & 1) && slot < NACC && v[0] != 0.f) atomicAdd(&acc[jj][slot], v[0]);
                 }
+#endif
             }
         }
         __syncthreads();                                   // batch fully accumulated

@@ -479,10 +479,16 @@ __device__ __forceinline__ bool rect_culled(float mx, float my, float A, float B
     return (-0.5f * qmin) < (cull - margin);   // false on NaN => keep
 }
 
-// K7: front-to-back alpha blend of one 16x16 tile per CTA.  8 warps, each owning an 8x4
-// pixel block.  Sorted records arrive in shared memory through double-buffered bulk async
-// copies; every warp culls the batch against its pixel block with one record per lane and
-// only walks the surviving records; a warp whose 32 pixels are saturated stops blending.
+// K7: front-to-back alpha blend of one 16x16 tile per CTA.  8 warps, each owning an 8x4 pixel block split into two 4x4
+// blocks, one per HALF-WARP.  Sorted records arrive in shared memory through double-buffered bulk async copies.  For each
+// chunk of 32 records every lane tests ONE record against both 4x4 blocks (conservative rectangle test); each half-warp then
+// walks only ITS OWN survivors, front to back: in one step the two halves evaluate two different records (two broadcast
+// shared-memory reads), so a warp needs max(|S_A|, |S_B|) steps instead of |S_A u S_B| — small splats touch few 4x4 blocks.
+// Per pixel the surviving records and their order are unchanged, so the result is bit-identical to a per-pixel walk.
+// A warp whose 32 pixels are saturated stops blending.
+#ifndef BLEND_FWD_STREAMS
+#define BLEND_FWD_STREAMS 2
+#endif
 __global__ void __launch_bounds__(256)
 k_blend_fwd(const uint2* __restrict__ ranges, const FdgsRecord* __restrict__ records, int W, int H,
             const float* __restrict__ bg_color, float* __restrict__ final_T, uint32_t* __restrict__ n_contrib,
@@ -497,12 +503,19 @@ k_blend_fwd(const uint2* __restrict__ ranges, const FdgsRecord* __restrict__ rec
     // warp (wx, wy) in a 2 x 4 arrangement of 8x4 pixel blocks
     const int wx = wid & 1, wy = wid >> 1;
     const int bx0 = blockIdx.x * FDGS_TILE + wx * 8, by0 = blockIdx.y * FDGS_TILE + wy * 4;
+#if BLEND_FWD_STREAMS == 2
+    const int half = lane >> 4;                                  // half-warp h owns the 4x4 block at x offset 4h
+    const int px = bx0 + half * 4 + (lane & 3), py = by0 + ((lane >> 2) & 3);
+#else
     const int px = bx0 + (lane & 7), py = by0 + (lane >> 3);
+#endif
     const bool inside = px < W && py < H;
     const float pxf = (float)px, pyf = (float)py;
     // pixel block bounds for the cull test (clipped to the image)
     const float cx0 = (float)bx0, cy0 = (float)by0;
     const float cx1 = (float)min(bx0 + 7, W - 1), cy1 = (float)min(by0 + 3, H - 1);
+    const float cxm0 = (float)min(bx0 + 3, W - 1), cxm1 = (float)(bx0 + 4);       // right edge of block A, left edge of block B
+    const bool blockB = bx0 + 4 < W;
     const bool warp_has_pixels = (bx0 < W) && (by0 < H);
 
     const uint2 range = ranges[tile];
@@ -529,6 +542,31 @@ k_blend_fwd(const uint2* __restrict__ ranges, const FdgsRecord* __restrict__ rec
     uint32_t last_contributor = 0;
     bool done = !inside;
 
+    // one pixel x record evaluation (forward.cu:335-366)
+    auto eval = [&](const FdgsRecord* rec, int jj, int b) {
+        const float4 q0 = reinterpret_cast<const float4*>(&rec[jj])[0];
+        const float4 q1 = reinterpret_cast<const float4*>(&rec[jj])[1];
+        const float dx = q0.x - pxf, dy = q0.y - pyf;
+        const float power = -0.5f * (q0.z * dx * dx + q1.x * dy * dy) - q0.w * dx * dy;
+        if (!(power > 0.0f)) {
+            const float alpha = fminf(0.99f, q1.y * expf(power));
+            if (!(alpha < 1.0f / 255.0f)) {
+                const float test_T = T * (1 - alpha);
+                if (test_T < 0.0001f) {
+                    done = true;
+                } else {
+                    const float4 q2 = reinterpret_cast<const float4*>(&rec[jj])[2];
+                    C0 += q2.x * alpha * T;
+                    C1 += q2.y * alpha * T;
+                    C2 += q2.z * alpha * T;
+                    Dp += q1.z * alpha * T;
+                    T = test_T;
+                    last_contributor = (uint32_t)(b * BATCH + jj + 1);
+                }
+            }
+        }
+    };
+
     for (int b = 0; b < nb; ++b) {
         if (threadIdx.x == 0 && b + 1 < nb) issue(b + 1);
         mbar_wait(&bars[b & 1], (uint32_t)((b >> 1) & 1));
@@ -538,6 +576,26 @@ k_blend_fwd(const uint2* __restrict__ ranges, const FdgsRecord* __restrict__ rec
         if (warp_has_pixels && !__all_sync(FULL, done)) {
             for (int c0 = 0; c0 < cnt; c0 += 32) {
                 const int j = c0 + lane;
+#if BLEND_FWD_STREAMS == 2
+                bool keepA = false, keepB = false;
+                if (j < cnt) {
+                    const float4 q0 = reinterpret_cast<const float4*>(&rec[j])[0];
+                    const float4 q1 = reinterpret_cast<const float4*>(&rec[j])[1];
+                    const float cull = rec[j].cull;
+                    if (!(q1.y <= 0.f)) {
+                        keepA = !rect_culled(q0.x, q0.y, q0.z, q0.w, q1.x, cull, cx0, cy0, cxm0, cy1);
+                        keepB = blockB && !rect_culled(q0.x, q0.y, q0.z, q0.w, q1.x, cull, cxm1, cy0, cx1, cy1);
+                    }
+                }
+                unsigned mA = __ballot_sync(FULL, keepA), mB = __ballot_sync(FULL, keepB);
+                unsigned mine = half ? mB : mA;
+                while (mA | mB) {
+                    if (mine && !done) eval(rec, c0 + (__ffs(mine) - 1), b);
+                    mine &= mine - 1;                 // 0 stays 0
+                    mA &= mA - 1; mB &= mB - 1;
+                    if (__all_sync(FULL, done)) { mA = 0; mB = 0; c0 = cnt; }
+                }
+#else
                 bool keep = false;
                 if (j < cnt) {
                     const float4 q0 = reinterpret_cast<const float4*>(&rec[j])[0];
@@ -549,31 +607,10 @@ k_blend_fwd(const uint2* __restrict__ ranges, const FdgsRecord* __restrict__ rec
                 while (m) {
                     const int jj = c0 + (__ffs(m) - 1);
                     m &= m - 1;
-                    if (!done) {
-                        const float4 q0 = reinterpret_cast<const float4*>(&rec[jj])[0];
-                        const float4 q1 = reinterpret_cast<const float4*>(&rec[jj])[1];
-                        const float dx = q0.x - pxf, dy = q0.y - pyf;
-                        const float power = -0.5f * (q0.z * dx * dx + q1.x * dy * dy) - q0.w * dx * dy;
-                        if (!(power > 0.0f)) {
-                            const float alpha = fminf(0.99f, q1.y * expf(power));
-                            if (!(alpha < 1.0f / 255.0f)) {
-                                const float test_T = T * (1 - alpha);
-                                if (test_T < 0.0001f) {
-                                    done = true;
-                                } else {
-                                    const float4 q2 = reinterpret_cast<const float4*>(&rec[jj])[2];
-                                    C0 += q2.x * alpha * T;
-                                    C1 += q2.y * alpha * T;
-                                    C2 += q2.z * alpha * T;
-                                    Dp += q1.z * alpha * T;
-                                    T = test_T;
-                                    last_contributor = (uint32_t)(b * BATCH + jj + 1);
-                                }
-                            }
-                        }
-                    }
+                    if (!done) eval(rec, jj, b);
                     if (__all_sync(FULL, done)) { m = 0; c0 = cnt; }
                 }
+#endif
             }
         }
         const int ndone = __syncthreads_count(done);

@@ -7,8 +7,8 @@ tail -5 gpurun_out/r02_gputest_4.log
 B="timeout 300 python bench.py --steps 5 --warmup 3 --no-cpu-baseline"
 timeout 300 python bench.py --steps 10 --warmup 3 --no-cpu-baseline > gpurun_out/r02_bench_fdgs_dynerf_2.json 2> gpurun_out/r02_bench_fdgs_dynerf_2.err
 FDGS_ONE_SHOT=0 $B > gpurun_out/r02_ab_exact.json 2> gpurun_out/r02_ab_exact.err
-for v in b256m1 b128m7 b128m5 b256m6 b192m6; do
-  FDGS_LIB=$PWD/tools/_bin/libfdgs_$v.so $B > gpurun_out/r02_ab_blendbwd_$v.json 2> gpurun_out/r02_ab_blendbwd_$v.err
+for v in fwd_s1 bwd_s1 bwd_s1_old bwd_s2_m5 bwd_s2_m4b256; do
+  FDGS_LIB=$PWD/tools/_bin/libfdgs_$v.so $B > gpurun_out/r02_ab_blend_$v.json 2> gpurun_out/r02_ab_blend_$v.err
 done
 FDGS_DW2_TENSOR=1 $B > gpurun_out/r02_ab_dw2_tensor.json 2> gpurun_out/r02_ab_dw2_tensor.err
 FDGS_DW2_COST=0.25 $B > gpurun_out/r02_ab_dw2_c025.json 2> gpurun_out/r02_ab_dw2_c025.err
