@@ -22,7 +22,7 @@
 #ifdef FDGS_PHASE_TIMING
 #define PT_DECL long long pt_[8] = {0,0,0,0,0,0,0,0}; long long pt_t = clock64();
 #define PT(i) { const long long n_ = clock64(); pt_[i] += n_ - pt_t; pt_t = n_; }
-#define PT_PRINT if (blockIdx.x == 0 && tid == 0) printf("fwd phases (cycles, CTA0): sample %lld | wait_trunk %lld | trunk_epi %lld | wait_z %lld | relu_pass %lld | wait_out %lld | out_pass %lld\n", pt_[0], pt_[1], pt_[2], pt_[3], pt_[4], pt_[5], pt_[6]);
+#define PT_PRINT if (blockIdx.x == 0 && tid == 0) printf("fwd phases (cycles, CTA0): sample %lld | wait_trunk %lld | trunk_epi %lld | wait_z %lld | relu_pass %lld | wait_out %lld | out_pass %lld | next_tile_sampling %lld\n", pt_[0], pt_[1], pt_[2], pt_[3], pt_[4], pt_[5], pt_[6], pt_[7]);
 #else
 #define PT_DECL
 #define PT(i)
@@ -424,7 +424,11 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
                 PT(3)
                 float* rz = io.S_RZ[h] ? io.S_RZ[h] + rowoff : nullptr;
                 uint32_t zm0 = 0u, zm1 = 0u;
-#pragma unroll 1
+#ifndef FDGS_RELU_UNROLL
+#define FDGS_RELU_UNROLL 1
+#endif
+                constexpr int RELU_UNROLL = FDGS_RELU_UNROLL;
+#pragma unroll (RELU_UNROLL)
                 for (int c0 = 0; c0 < NH; c0 += 16) {
                     uint32_t v[16], hi[16], lw[16];
                     tmem_ld16(acc + col0 + c0, v);
@@ -458,8 +462,9 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
                 tc_fence_before();
                 epi_bar();
                 if (tid == 0) mbar_arrive(&bars[B_RZFULL]);
-                if (next_tile < ntiles && next_pass < SPASS) sample_pass(next_tile, next_pass++);     // overlaps o_i GEMM
                 PT(4)
+                if (next_tile < ntiles && next_pass < SPASS) sample_pass(next_tile, next_pass++);     // overlaps o_i GEMM
+                PT(7)
 
                 // o = relu(z) W2^T (+ b2): accumulator -> staging [row][NO] -> coalesced base + delta
                 mbar_wait(&bars[B_OUTFULL], ph_out); ph_out ^= 1;

@@ -1380,7 +1380,8 @@ int backward(const Layout& lo, const FdgsDeformBackward* a, const float* packed,
     float* dw1[FDGS_NUM_HEADS] = {a->d_head_w1[0], a->d_head_w1[1], a->d_head_w1[2], a->d_head_w1[3], a->d_head_w1[4]};
     double cost[MAXJOBS];
     // per-stage cost of a CUDA-core dW2 job relative to a tensor-core dW1 job (FDGS_DW2_COST overrides, for tuning)
-    const double cc_cost = getenv("FDGS_DW2_COST") ? atof(getenv("FDGS_DW2_COST")) : 0.4;
+    // measured (cycles per 32-point stage, FDGS_PHASE_TIMING): dW1 1718, dW2 on the CUDA cores 889, dW2 (shs) 1543, dW0 1455
+    const double cc_cost = getenv("FDGS_DW2_COST") ? atof(getenv("FDGS_DW2_COST")) : 0.52;
     for (int j = 0; j < plan.nheads; ++j) {
         const int h = plan.heads[j];
         const int NO = head_out(h);
@@ -1388,10 +1389,10 @@ int backward(const Layout& lo, const FdgsDeformBackward* a, const float* packed,
         cost[nj++] = 1.0;                                 // relative per-stage cost, measured (cycles/stage 1750 : 2050 : 1530)
         const int cc = (NO <= 4 && !getenv("FDGS_DW2_TENSOR")) ? 1 : 0;
         wa.j[nj] = WJob{io.S_RZ[j], Wn, Wn, (int)plan.Pp, gsrc[h], NO, NO, a->P, a->d_head_w2[h], Wn, 1, nullptr, a->d_head_b2[h], 1, 1, 0, cc};
-        cost[nj++] = cc ? cc_cost : 0.87;
+        cost[nj++] = cc ? cc_cost : 0.90;
     }
     wa.j[nj] = WJob{io.S_GH, Wn, Wn, (int)plan.Pp, io.S_F, F, F, (int)plan.Pp, a->d_trunk_w[0], F, 0, a->d_trunk_b[0], nullptr, 1, 1, 1, 0};
-    cost[nj++] = 0.87;
+    cost[nj++] = 0.85;
     wa.njobs = nj; wa.rows = plan.Pp;
     // distribute the SMs over the jobs in proportion to the bytes they stream
     double tot = 0; for (int i = 0; i < nj; ++i) tot += cost[i];

@@ -161,8 +161,10 @@ __device__ __forceinline__ void half_reduce10(float (&v)[10], int lane) {
     }
 }
 
+// (BLEND_BWD_STREAMS = 2: one record stream per half-warp; measured SLOWER, 736 vs 620 us per DyNeRF view - the default stays
+//  one stream per warp.  profiles/r02_ab_blend_streams.txt)
 #ifndef BLEND_BWD_STREAMS
-#define BLEND_BWD_STREAMS 2
+#define BLEND_BWD_STREAMS 1
 #endif
 
 // NPX pixels per thread (rows py and py + 4): a warp covers an 8 x (4 NPX) sub-rectangle of the tile, so one cull test,
@@ -193,7 +195,6 @@ k_blend_bwd(const uint2* __restrict__ ranges, const FdgsRecord* __restrict__ rec
 #if BLEND_BWD_STREAMS == 2
     // two record streams per warp: half-warp h owns the 8 x (2 NPX) block of rows [by0 + 2 NPX h, by0 + 2 NPX (h + 1)), a thread
     // its column and the rows rp, rp + 2, ... of that block; each half walks only the records that survive ITS block's test
-    static_assert(NPX == 2, "the two-stream mapping is written for two pixels per thread");
     const int half = lane >> 4, rp = (lane >> 3) & 1;
     const float cyA1 = (float)min(by0 + 2 * NPX - 1, H - 1), cyB0 = (float)(by0 + 2 * NPX);
     const bool blockB = by0 + 2 * NPX < H;

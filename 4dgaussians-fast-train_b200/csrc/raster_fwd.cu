@@ -236,6 +236,7 @@ k_scatter(int P, const int* __restrict__ radii, FdgsGeom g, int gx, int gy,
 {
     if (scalars[3]) return;                        // instance workspace too small (one-shot mode): see k_tile_scan
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    const int lane = threadIdx.x & 31;
     int x0 = 0, y0 = 0, x1 = 0, y1 = 0;
     uint32_t dbits = 0;
     if (idx < P) {
@@ -246,10 +247,40 @@ k_scatter(int P, const int* __restrict__ radii, FdgsGeom g, int gx, int gy,
             dbits = __float_as_uint(g.depths[idx]);
         }
     }
-    for_each_tile(x0, y0, x1, y1, (uint32_t)idx, dbits, gx, [&](int tile, uint32_t id, uint32_t d) {
-        const uint32_t pos = tile_start[tile] + atomicAdd(&tile_cursor[tile], 1u);
-        bucket[pos] = ((uint64_t)d << 32) | id;
-    });
+    const int w = x1 - x0, n = w * (y1 - y0);
+    const uint64_t key = ((uint64_t)dbits << 32) | (uint32_t)idx;
+    const bool big = n > 32;
+    // Rects of up to 32 tiles (all but a few screen-filling Gaussians): the thread's cursor atomics are issued in batches of
+    // 8 BEFORE any of their results is used.  One atomic per loop iteration left the kernel waiting for a ~1 us round trip per
+    // instance (7 % issue utilisation, ncu: 157 long-scoreboard stalls per issued instruction).
+    if (!big) {
+        for (int base = 0; base < n; base += 8) {
+            uint32_t pos[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                const int i = base + k;
+                if (i < n) {
+                    const int tile = (y0 + i / w) * gx + (x0 + i % w);
+                    pos[k] = tile_start[tile] + atomicAdd(&tile_cursor[tile], 1u);
+                }
+            }
+#pragma unroll
+            for (int k = 0; k < 8; ++k) if (base + k < n) bucket[pos[k]] = key;
+        }
+    }
+    // larger rects: the whole warp walks them, one tile per lane
+    unsigned m = __ballot_sync(FULL, big);
+    while (m) {
+        const int src = __ffs(m) - 1;
+        m &= m - 1;
+        const int sx0 = __shfl_sync(FULL, x0, src), sy0 = __shfl_sync(FULL, y0, src);
+        const int sw = __shfl_sync(FULL, w, src), sn = __shfl_sync(FULL, n, src);
+        const uint32_t klo = __shfl_sync(FULL, (uint32_t)key, src), khi = __shfl_sync(FULL, (uint32_t)(key >> 32), src);
+        for (int i = lane; i < sn; i += 32) {
+            const int tile = (sy0 + i / sw) * gx + (sx0 + i % sw);
+            bucket[tile_start[tile] + atomicAdd(&tile_cursor[tile], 1u)] = ((uint64_t)khi << 32) | klo;
+        }
+    }
 }
 
 // ---------------------------------------------------------------------------
@@ -486,8 +517,12 @@ __device__ __forceinline__ bool rect_culled(float mx, float my, float A, float B
 // shared-memory reads), so a warp needs max(|S_A|, |S_B|) steps instead of |S_A u S_B| — small splats touch few 4x4 blocks.
 // Per pixel the surviving records and their order are unchanged, so the result is bit-identical to a per-pixel walk.
 // A warp whose 32 pixels are saturated stops blending.
+// (BLEND_FWD_STREAMS = 2 below is that variant; MEASURED SLOWER than one stream per warp - 356 vs 302 us per DyNeRF view,
+//  324 M vs ~280 M warp instructions: the steps saved do not pay for the second ballot / mask bookkeeping and the second
+//  shared-memory wavefront of every record read - so the default is the single stream: the warp culls a chunk of 32 records
+//  against its 8x4 block with one record per lane and walks the survivors together.  profiles/r02_ab_blend_streams.txt)
 #ifndef BLEND_FWD_STREAMS
-#define BLEND_FWD_STREAMS 2
+#define BLEND_FWD_STREAMS 1
 #endif
 __global__ void __launch_bounds__(256)
 k_blend_fwd(const uint2* __restrict__ ranges, const FdgsRecord* __restrict__ records, int W, int H,
