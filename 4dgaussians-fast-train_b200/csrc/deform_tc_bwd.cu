@@ -1380,8 +1380,9 @@ int backward(const Layout& lo, const FdgsDeformBackward* a, const float* packed,
     float* dw1[FDGS_NUM_HEADS] = {a->d_head_w1[0], a->d_head_w1[1], a->d_head_w1[2], a->d_head_w1[3], a->d_head_w1[4]};
     double cost[MAXJOBS];
     // per-stage cost of a CUDA-core dW2 job relative to a tensor-core dW1 job (FDGS_DW2_COST overrides, for tuning)
-    // measured (cycles per 32-point stage, FDGS_PHASE_TIMING): dW1 1718, dW2 on the CUDA cores 889, dW2 (shs) 1543, dW0 1455
-    const double cc_cost = getenv("FDGS_DW2_COST") ? atof(getenv("FDGS_DW2_COST")) : 0.52;
+    // measured (cycles per 32-point stage, FDGS_PHASE_TIMING): dW1 1718, dW2 on the CUDA cores 889 (HBM-bound: ~1000 when all four
+    // such jobs stream at once), dW2 (shs) 1543, dW0 1455
+    const double cc_cost = getenv("FDGS_DW2_COST") ? atof(getenv("FDGS_DW2_COST")) : 0.60;
     for (int j = 0; j < plan.nheads; ++j) {
         const int h = plan.heads[j];
         const int NO = head_out(h);
