@@ -1382,7 +1382,7 @@ int backward(const Layout& lo, const FdgsDeformBackward* a, const float* packed,
     // per-stage cost of a CUDA-core dW2 job relative to a tensor-core dW1 job (FDGS_DW2_COST overrides, for tuning)
     // measured (cycles per 32-point stage, FDGS_PHASE_TIMING): dW1 1718, dW2 on the CUDA cores 889 (HBM-bound: ~1000 when all four
     // such jobs stream at once), dW2 (shs) 1543, dW0 1455
-    const double cc_cost = getenv("FDGS_DW2_COST") ? atof(getenv("FDGS_DW2_COST")) : 0.60;
+    const double cc_cost = getenv("FDGS_DW2_COST") ? atof(getenv("FDGS_DW2_COST")) : 0.65;
     for (int j = 0; j < plan.nheads; ++j) {
         const int h = plan.heads[j];
         const int NO = head_out(h);

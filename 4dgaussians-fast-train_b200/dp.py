@@ -104,7 +104,7 @@ def grads_in_place(module, on=True):
     return module
 
 
-def _sm_limit(on, spare=8):
+def _sm_limit(on, spare=None):
     """Caps the persistent fdgs deformation kernels at (SM count - spare) CTAs while an all-reduce is in flight."""
     try:
         from . import _lib
@@ -112,6 +112,8 @@ def _sm_limit(on, spare=8):
     except Exception:
         return
     if on:
+        import os
+        spare = int(os.environ.get("FDGS_OVERLAP_SPARE_SMS", "8")) if spare is None else spare
         n = torch.cuda.get_device_properties(torch.cuda.current_device()).multi_processor_count
         lib.fdgs_set_sm_limit(max(1, n - spare))
     else:
