@@ -34,8 +34,19 @@ using namespace fdgs_deform;
 using namespace fdgs_umma;
 
 constexpr int KCH = 16;            // K columns per streamed weight chunk
-constexpr int NTHREADS = 320;      // 8 epilogue warps + producer + MMA
-constexpr int NEPI = 256;
+// Epilogue / sampler warps: 4 per group of accumulator columns (a warp reaches only the 32 TMEM lanes of its quarter).
+// Wn = 128 runs FOUR groups of 32 columns = 16 warps (4 per scheduler): the epilogue passes are latency-bound (phase timing
+// and ncu: 34 % issue-active with 8 warps), FDGS_FWD_EPI16=0 builds the 8-warp layout (two groups of 64 columns) for A/B.
+#ifndef FDGS_FWD_EPI16
+#define FDGS_FWD_EPI16 1
+#endif
+template <int WN> struct EpiCfg {
+    static constexpr int NG = (FDGS_FWD_EPI16 && WN == 128) ? 4 : 2;   // column groups
+    static constexpr int NH = WN / NG;                                   // accumulator columns per epilogue thread
+    static constexpr int NEPI = 128 * NG;                                // epilogue threads
+    static constexpr int NEW = 4 * NG;                                   // epilogue warps; warp NEW = producer, NEW + 1 = MMA issuer
+    static constexpr int NTHREADS = NEPI + 64;
+};
 constexpr int MAXCH = 96;          // chunks per tile: F/16 + heads * (Wn/16 + Wn/16)
 
 // Pre-formatted weights ("wprep" workspace): a chunk holds KCH=16 reduction columns of an [N rows][K] weight as a hi
@@ -153,7 +164,7 @@ static inline SmemPlan make_smem_plan(const Layout& lo) {
     return s;
 }
 
-__device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void epi_bar_n() { asm volatile("bar.sync 1, %0;" ::"n"(N) : "memory"); }
 
 // TMEM column map (512 columns allocated): two accumulators, relu(z) hi, lo.  Head i uses accumulator i & 1: z_i, then
 // (once relu(z_i) has been read out of it) its first 16 / 48 columns take the output layer o_i.  z_{i+1} is computed into
@@ -165,7 +176,7 @@ constexpr int B_WFULL = 0, B_WEMPTY = 8, B_FEATFULL = 16, B_ACCFULL = 17 /* +1 *
 __device__ __forceinline__ int b2_row0(int h) { return h == 0 ? 0 : h == 1 ? 3 : h == 2 ? 6 : h == 3 ? 10 : 11; }
 
 template <int WN>
-__global__ void __launch_bounds__(NTHREADS, 1)
+__global__ void __launch_bounds__(EpiCfg<WN>::NTHREADS, 1)
 k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, const float* __restrict__ packed,
                 const float* __restrict__ trow, int ntiles, int passes)
 {
@@ -186,7 +197,8 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + B_COUNT + 2);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int S = sp.slots;
-    constexpr int NH = WN / 2;                 // accumulator columns per epilogue thread
+    constexpr int NG = EpiCfg<WN>::NG, NH = EpiCfg<WN>::NH, NEPI = EpiCfg<WN>::NEPI, NEW = EpiCfg<WN>::NEW;
+    auto epi_bar = [] { epi_bar_n<EpiCfg<WN>::NEPI>(); };
     constexpr int SLOT = 32 * WN;              // floats per ring slot
     const int F = lo.F;
 
@@ -195,7 +207,7 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
         for (int i = 0; i < B_COUNT; ++i) mbar_init(&bars[i], 1);
         fence_mbar_init();
     }
-    if (warp == 9) tmem_alloc(tmem_slot, 512);
+    if (warp == NEW + 1) tmem_alloc(tmem_slot, 512);
     if (tid < NEPI) {
         for (int i = tid; i < WN; i += NEPI) B0s[i] = net.b0[i];
         for (int j = 0; j < plan.nheads; ++j) {
@@ -210,7 +222,7 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
     tc_fence_after();
     const uint32_t tmem = *tmem_slot;
 
-    if (warp == 8) {
+    if (warp == NEW) {
         // ===== producer: weight chunks, the same sequence for every tile ==================================
         if (lane == 0) {
             uint32_t g = 0;
@@ -224,7 +236,7 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
                 }
         }
         __syncwarp();
-    } else if (warp == 9) {
+    } else if (warp == NEW + 1) {
         // ===== MMA issuer: the whole warp runs the loop, one elected lane issues (see umma.cuh:elect_one) ============
         {
             const uint32_t tm = __shfl_sync(0xffffffffu, tmem, 0);
@@ -314,14 +326,14 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
         // sampler mapping: LP adjacent lanes share one point and take consecutive channel quads, so a warp-wide gather
         // touches 32/LP points x 64-byte taps instead of 32 unrelated lines (the L1 tag stage serves one line per cycle)
         const int items = F >> 2;
-        const int LP = (items & 7) == 0 ? 8 : 4, IPT = items / LP, PPW = 32 / LP, SPASS = TP / (8 * PPW);
+        const int LP = (items & 7) == 0 ? 8 : 4, IPT = items / LP, PPW = 32 / LP, SPASS = TP / (NEW * PPW);
         const int sg = lane / LP, sq = lane % LP;
         PT_DECL
         // HexPlane sampling of one quarter (8*PPW points) of tile t into registers/local memory.  The passes of tile t+1
         // are issued inside tile t's head loop, where the epilogue warps would otherwise wait for the output-layer GEMM.
         float4 nf[8];                                                // SPASS * IPT <= 8 float4 per thread
         auto sample_pass = [&](int t, int pass) {
-            const int srow = pass * (8 * PPW) + warp * PPW + sg;
+            const int srow = pass * (NEW * PPW) + warp * PPW + sg;
             const int sp_ = t * TP + srow;
             const bool sval = sp_ < io.P;
             float q[4] = {0.f, 0.f, 0.f, 0.f};
@@ -341,7 +353,7 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
             const size_t rowoff = (size_t)tile * TP * WN + (row >> 5) * 32 * WN + (row & 31) * 4;   // blocked save layout
             // ---- feat tile (hi / lo) from the values sampled ahead of time (see sample_pass) -------------------
             for (int pass = 0; pass < SPASS; ++pass) {
-                const int srow = pass * (8 * PPW) + warp * PPW + sg;
+                const int srow = pass * (NEW * PPW) + warp * PPW + sg;
                 for (int it = 0; it < IPT; ++it) {
                     const int item = sq + it * LP;
                     const float4 pr = nf[pass * IPT + it];
@@ -387,7 +399,7 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
                     if (io.S_H)
                         __stcs(reinterpret_cast<float4*>(io.S_H + rowoff + ((col0 + c0 + j) >> 2) * 128), make_float4(x[0], x[1], x[2], x[3]));
                 }
-                if (io.S_M) io.S_M[((size_t)(p0 + row)) * 4 + hf * 2 + (c0 >> 5)] = m;
+                if (io.S_M) io.S_M[((size_t)(p0 + row)) * 4 + hf * (4 / NG) + (c0 >> 5)] = m;    // word layout the backward reads
             }
             fence_async_smem();
             tc_fence_before();
@@ -454,7 +466,7 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
                     tmem_st16(lane_base + TM_ZLO + col0 + c0, lw);
                 }
                 if (io.S_M) {
-                    uint32_t* mp = io.S_M + ((size_t)(1 + h) * io.Pp + (p0 + row)) * 4 + hf * 2;
+                    uint32_t* mp = io.S_M + ((size_t)(1 + h) * io.Pp + (p0 + row)) * 4 + hf * (4 / NG);
                     mp[0] = zm0;
                     if (NH > 32) mp[1] = zm1;
                 }
@@ -471,16 +483,29 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
                 tc_fence_after();
                 PT(5)
                 {
-                    const int npt = plan.nop[i] >> 1;                 // output columns per thread: 8 or 24
+                    const int npt = plan.nop[i] / NG;                 // output columns per thread: 8 / 24 (two groups) or 4 / 12
                     // (row stride OS: 48 floats would put a warp's 32 rows on two banks, 52 spreads them over eight)
-                    for (int c0 = 0; c0 < npt; c0 += 8) {
-                        uint32_t v[8];
-                        tmem_ld8(acc + hf * npt + c0, v);
-                        tmem_wait_ld();
+                    if (NG == 2) {
+                        for (int c0 = 0; c0 < npt; c0 += 8) {
+                            uint32_t v[8];
+                            tmem_ld8(acc + hf * npt + c0, v);
+                            tmem_wait_ld();
 #pragma unroll
-                        for (int j = 0; j < 8; ++j) {
-                            const int n = hf * npt + c0 + j;
-                            if (n < NO) OUTs[row * OS + n] = __uint_as_float(v[j]) + B2s[b2_row0(h) + n];
+                            for (int j = 0; j < 8; ++j) {
+                                const int n = hf * npt + c0 + j;
+                                if (n < NO) OUTs[row * OS + n] = __uint_as_float(v[j]) + B2s[b2_row0(h) + n];
+                            }
+                        }
+                    } else {
+                        for (int c0 = 0; c0 < npt; c0 += 4) {
+                            uint32_t v[4];
+                            tmem_ld4(acc + hf * npt + c0, v);
+                            tmem_wait_ld();
+#pragma unroll
+                            for (int j = 0; j < 4; ++j) {
+                                const int n = hf * npt + c0 + j;
+                                if (n < NO) OUTs[row * OS + n] = __uint_as_float(v[j]) + B2s[b2_row0(h) + n];
+                            }
                         }
                     }
                 }
@@ -524,7 +549,7 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
-    if (warp == 9) tmem_free(tmem, 512);
+    if (warp == NEW + 1) tmem_free(tmem, 512);
 }
 
 static int sm_count() {          // of the CURRENT device (one process may drive several)
@@ -594,12 +619,12 @@ int forward(const Layout& lo, const FdgsDeformForward* a, const float* packed, c
     if (lo.Wn == 128) {
         FDGS_CUDA(cudaFuncSetAttribute(k_deform_fwd_tc<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sp.bytes));
         { FDGS_PROF("k_deform_fwd_tc", stream);
-        k_deform_fwd_tc<128><<<grid, NTHREADS, sp.bytes, stream>>>(lo, plan, sp, net, io, packed, trow, ntiles, passes);
+        k_deform_fwd_tc<128><<<grid, EpiCfg<128>::NTHREADS, sp.bytes, stream>>>(lo, plan, sp, net, io, packed, trow, ntiles, passes);
         }
     } else {
         FDGS_CUDA(cudaFuncSetAttribute(k_deform_fwd_tc<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sp.bytes));
         { FDGS_PROF("k_deform_fwd_tc", stream);
-        k_deform_fwd_tc<64><<<grid, NTHREADS, sp.bytes, stream>>>(lo, plan, sp, net, io, packed, trow, ntiles, passes);
+        k_deform_fwd_tc<64><<<grid, EpiCfg<64>::NTHREADS, sp.bytes, stream>>>(lo, plan, sp, net, io, packed, trow, ntiles, passes);
         }
     }
     FDGS_LAUNCH_CHECK(a->debug, stream);
