@@ -67,8 +67,10 @@ def _worker(rank, world, port, B, q):
         loss, radii, vis = dp.train_iteration(_render, pc, cams, gts, torch.ones(3), bucket, rank=rank, world=world)
         tot = loss.clone()
         dist.all_reduce(tot)
-        q.put((rank, float(tot), pc.a.grad.clone(), pc.b.grad.clone(), bucket.extra["viewspace"].clone(),
-               radii.clone(), bucket.nbytes(), vis.clone()))
+        # numpy copies, not tensors: a tensor travels through the queue as a handle served by THIS process, which may have
+        # exited by the time the parent opens it (FileNotFoundError in multiprocessing.connection, seen once in ~10 runs)
+        q.put((rank, float(tot), pc.a.grad.numpy().copy(), pc.b.grad.numpy().copy(), bucket.extra["viewspace"].numpy().copy(),
+               radii.numpy().copy(), bucket.nbytes(), vis.numpy().copy()))
     finally:
         dist.destroy_process_group()
 
@@ -116,6 +118,7 @@ def test_world2_gloo_matches_single_process(B):
     for p in procs:
         p.join(timeout=60)
         assert p.exitcode == 0
+    res = [tuple(torch.from_numpy(x) if hasattr(x, "dtype") and not isinstance(x, torch.Tensor) else x for x in r) for r in res]
     cams, _ = _batch(B)
     per_view = torch.stack([_render(c, _PC(), torch.ones(3))["radii"] for c in cams])
     for rank, loss, a, b, vs, radii, nbytes, vis in res:
@@ -185,7 +188,7 @@ def _worker_feat(rank, world, port, B, overlap, q):
         bucket.all_reduce_range = lambda lo, hi, **kw: (calls.append((lo, hi, kw.get("async_op", False))), orig(lo, hi, **kw))[1]
         cams, gts = _batch(B)
         dp.train_iteration(_render_feat, pc, cams, gts, torch.ones(3), bucket, rank=rank, world=world, overlap_sh=overlap)
-        q.put((rank, bucket.flat.clone(), calls))
+        q.put((rank, bucket.flat.numpy().copy(), calls))
     finally:
         dist.destroy_process_group()
 
@@ -204,6 +207,7 @@ def test_world2_early_sh_all_reduce_equals_single_collective(B):     # B = 1 < w
         for p in procs:
             p.join(timeout=60)
             assert p.exitcode == 0
+        res = [(r[0], torch.from_numpy(r[1]), r[2]) for r in res]
         assert torch.equal(res[0][1], res[1][1])
         flats[overlap] = res[0][1]
         if overlap:
