@@ -163,6 +163,12 @@ __device__ __forceinline__ void half_reduce10(float (&v)[10], int lane) {
 
 // (BLEND_BWD_STREAMS = 2: one record stream per half-warp; measured SLOWER, 736 vs 620 us per DyNeRF view - the default stays
 //  one stream per warp.  profiles/r02_ab_blend_streams.txt)
+#ifndef BLEND_BWD_SPARSE
+#define BLEND_BWD_SPARSE 0          // 0 = always reduce with the butterfly (default).  N > 0: skip the reduction when no lane had a
+                                    // contributing pixel and let up to N hitting lanes add their partials themselves - measured SLOWER at
+                                    // every N (620 us -> 656 / 676 / 701 / 815 at N = 1 / 2 / 3 / 6): the extra ballot and the divergent
+                                    // branch cost more than the butterflies they save
+#endif
 #ifndef BLEND_BWD_STREAMS
 #define BLEND_BWD_STREAMS 1
 #endif
@@ -360,6 +366,21 @@ k_blend_bwd(const uint2* __restrict__ ranges, const FdgsRecord* __restrict__ rec
 #pragma unroll
                     for (int k = 0; k < 10; ++k) v[k] = 0.f;
                     eval(jj, (uint32_t)(lo + jj), v);
+#if BLEND_BWD_SPARSE
+                    // A surviving record usually touches a handful of the warp's 64 pixels (the cull is a conservative
+                    // rectangle test): v[8] (the opacity partial, G * dL/dalpha with G > 0) is non-zero exactly on the lanes that
+                    // had a contributing pixel.  No such lane: nothing to add.  Up to BLEND_BWD_SPARSE lanes: they add their nine
+                    // partials to the shared accumulator themselves (9 predicated atomics) instead of the 12-shuffle butterfly.
+                    const unsigned hitm = __ballot_sync(FULL, v[8] != 0.f || v[0] != 0.f || v[3] != 0.f);
+                    if (hitm == 0u) continue;
+                    if (__popc(hitm) <= BLEND_BWD_SPARSE) {
+                        if ((hitm >> lane) & 1u) {
+#pragma unroll
+                            for (int k = 0; k < NACC; ++k) if (v[k] != 0.f) atomicAdd(&acc[jj][k], v[k]);
+                        }
+                        continue;
+                    }
+#endif
                     warp_reduce10(v, lane);
                     const int slot = ((lane >> 4) & 1) * 5 + ((lane >> 3) & 1) * 3 + ((lane >> 2) & 1) * 2 + ((lane >> 1) & 1);
                     if (!(lane & 1) && slot < NACC && v[0] != 0.f) atomicAdd(&acc[jj][slot], v[0]);

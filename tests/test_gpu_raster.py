@@ -363,7 +363,7 @@ def test_one_shot_forward_matches_exact_and_reports_overflow():
     assert torch.equal(c0, c1) and torch.equal(r0, r1) and torch.equal(d0, d1)
     for k in g0:
         if g0[k] is not None:
-            assert util.rel_err(g1[k], g0[k]) < 1e-6, k             # same kernels; float atomics in the backward
+            assert util.rel_err(g1[k], g0[k]) < 5e-6, k             # same kernels; float atomics in the backward (run-to-run noise)
     # overflow: pretend the last render of this shape was 20x smaller
     true_R = R._caps[key]
     R._caps[key] = true_R // 20
