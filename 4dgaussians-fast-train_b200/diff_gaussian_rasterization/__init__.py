@@ -42,7 +42,6 @@ def cpu_deep_copy_tuple(input_tuple):
     return tuple(copied_tensors)
 
 
-_pinned = {}
 _last_R = 0
 _keep_last = False       # diagnostics only: keep a reference to the last forward's workspaces (see count_pairs)
 _last_ws = None
@@ -119,15 +118,6 @@ def _take_slot(device):
 def last_num_rendered():
     """num_rendered (R) of the most recent forward call in this process (bench / diagnostics)."""
     return _last_R
-
-
-def _counts_host(device):
-    key = (device.type, device.index)
-    t = _pinned.get(key)
-    if t is None:
-        t = torch.zeros(4, dtype=torch.int32).pin_memory()
-        _pinned[key] = t
-    return t
 
 
 def _f32(t, name, device):
@@ -213,21 +203,25 @@ def _forward_native(bg, means3D, colors_precomp, opacities, scales, rotations, s
             if _keep_last:
                 _last_ws = (img, binb, cap, W, H)
             return (cap, color, depth, radii, geom, binb, img)
-        counts = _counts_host(dev)
-        a.counts_host = counts.data_ptr()
-        L.check(lib.fdgs_raster_forward_plan(C.byref(a), st), "fdgs_raster_forward_plan")
-        R = int(counts[0])
-        _last_R = R
-        _note_count(key, R)
-        binb = torch.empty((lib.fdgs_raster_bin_bytes(R),), dtype=torch.uint8, device=dev)
-        a.bin_ws, a.bin_bytes = binb.data_ptr(), binb.numel()
-        extras = {}
-        if want_debug_lists:
-            extras["keys"] = torch.empty((R,), dtype=torch.int64, device=dev)
-            extras["point_list"] = torch.empty((R,), dtype=torch.int32, device=dev)
-            a.keys_out = extras["keys"].data_ptr() if R else None
-            a.point_list_out = extras["point_list"].data_ptr() if R else None
-        L.check(lib.fdgs_raster_forward_render(C.byref(a), R, st), "fdgs_raster_forward_render")
+        # exact path: a pinned slot of this call's own (two threads rendering on one device must not share the counts)
+        counts = _take_slot(dev)
+        try:
+            a.counts_host = counts.data_ptr()
+            L.check(lib.fdgs_raster_forward_plan(C.byref(a), st), "fdgs_raster_forward_plan")
+            R = int(counts[0])
+            _last_R = R
+            _note_count(key, R)
+            binb = torch.empty((lib.fdgs_raster_bin_bytes(R),), dtype=torch.uint8, device=dev)
+            a.bin_ws, a.bin_bytes = binb.data_ptr(), binb.numel()
+            extras = {}
+            if want_debug_lists:
+                extras["keys"] = torch.empty((R,), dtype=torch.int64, device=dev)
+                extras["point_list"] = torch.empty((R,), dtype=torch.int32, device=dev)
+                a.keys_out = extras["keys"].data_ptr() if R else None
+                a.point_list_out = extras["point_list"].data_ptr() if R else None
+            L.check(lib.fdgs_raster_forward_render(C.byref(a), R, st), "fdgs_raster_forward_render")
+        finally:
+            _slots.setdefault(dev.index, []).append(counts)   # both calls have read it on the host by now
         if _keep_last:
             _last_ws = (img, binb, R, W, H)
         out = (R, color, depth, radii, geom, binb, img)
