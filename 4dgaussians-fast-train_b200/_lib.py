@@ -167,6 +167,8 @@ SYMBOLS = {
     "fdgs_densify_stats": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "fdgs_knn_ws_bytes": (C.c_size_t, [C.c_int]),
     "fdgs_knn_mean_dist2": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
+    "fdgs_knn_static_max_points": (C.c_int, []),
+    "fdgs_knn_mean_dist2_static": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
     "fdgs_voxel_downsample_ws_bytes": (C.c_size_t, [C.c_int]),
     "fdgs_voxel_downsample": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_double, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p,
                                         C.c_void_p, C.c_size_t, C.c_void_p]),

@@ -20,6 +20,7 @@ const char* fdgs_error_string(int code) {
         case FDGS_E_WORKSPACE: return "fdgs: caller-owned workspace too small";
         case FDGS_E_UNSUPPORTED: return "fdgs: configuration not supported by the sm_100a kernels";
         case FDGS_E_SMEM: return "fdgs: configuration exceeds the shared-memory budget";
+        case FDGS_E_TOO_LARGE: return "fdgs: problem size exceeds the fixed maximum of this allocation-free entry point";
         default: break;
     }
     if (code > 0) return cudaGetErrorString((cudaError_t)code);

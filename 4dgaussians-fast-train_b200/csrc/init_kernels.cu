@@ -10,6 +10,7 @@
 #include <cfloat>
 #include <cmath>
 #include <cstdint>
+#include <mutex>
 
 namespace {
 
@@ -255,6 +256,80 @@ int fdgs_knn_mean_dist2(int P, const float* points, float* mean_dist2, void* ws,
     k_knn_scatter<<<(P + 255) / 256, 256, 0, stream>>>(P, cell_of, start, cursor, sorted);
     k_knn_search<<<(P + 127) / 128, 128, 0, stream>>>(P, points, bb, n, start, sorted, mean_dist2);
     FDGS_LAUNCH_CHECK(0, stream);
+    return FDGS_OK;
+}
+
+// ---- the same 3-NN pass with NO caller workspace and NO allocation (include/fdgs.h: fdgs_knn_mean_dist2_static) -----------
+// Scratch = one file-scope device array (below), FDGS_KNN_STATIC_MAX_POINTS points at most.  In host code `g_knn_static` is only
+// a stand-in for the symbol: its device address is taken once per device with cudaGetSymbolAddress, with that device current.
+}  // extern "C"  (the array and its set-up are file-local)
+
+namespace {
+
+constexpr int KNN_STATIC_MAX_N = 51;                                         // knn_cells_per_axis(262144) = 50
+constexpr size_t KNN_STATIC_MAX_CELLS = (size_t)KNN_STATIC_MAX_N * KNN_STATIC_MAX_N * KNN_STATIC_MAX_N;
+constexpr size_t knn_static_align(size_t b) { return (b + 255) & ~(size_t)255; }
+constexpr size_t KNN_STATIC_BYTES = knn_static_align(32) + 2 * knn_static_align((KNN_STATIC_MAX_CELLS + 1) * 4) +
+                                    knn_static_align(KNN_STATIC_MAX_CELLS * 4) +
+                                    2 * knn_static_align((size_t)FDGS_KNN_STATIC_MAX_POINTS * 4);   // = 3 689 728 bytes
+
+static __device__ __align__(256) unsigned char g_knn_static[KNN_STATIC_BYTES];
+
+constexpr int KNN_STATIC_MAX_DEVICES = 64;
+void* g_knn_static_addr[KNN_STATIC_MAX_DEVICES] = {};     // device address of g_knn_static on each device, filled on first use
+std::mutex g_knn_static_mu;
+
+// device address of the scratch array on the CURRENT device (0 = ok, else a cudaError_t / FDGS_E_*)
+int knn_static_ptr(void** out) {
+    int dev = -1;
+    FDGS_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= KNN_STATIC_MAX_DEVICES) return FDGS_E_UNSUPPORTED;
+    std::lock_guard<std::mutex> lock(g_knn_static_mu);
+    if (!g_knn_static_addr[dev]) {
+        void* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_knn_static);
+        if (e != cudaSuccess) return (int)e;
+        if (!p) return FDGS_E_UNSUPPORTED;
+        g_knn_static_addr[dev] = p;
+    }
+    *out = g_knn_static_addr[dev];
+    return FDGS_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int fdgs_knn_static_max_points(void) { return FDGS_KNN_STATIC_MAX_POINTS; }
+
+int fdgs_knn_mean_dist2_static(int P, const float* points, float* mean_dist2, void* stream_) {
+    if (P < 0 || (P > 0 && (!points || !mean_dist2))) return FDGS_E_BADARG;
+    if (P > FDGS_KNN_STATIC_MAX_POINTS) return FDGS_E_TOO_LARGE;
+    if (P == 0) return FDGS_OK;
+    cudaStream_t stream = (cudaStream_t)stream_;
+    const int n = knn_cells_per_axis(P);
+    const size_t cells = (size_t)n * n * n;
+    if (n > KNN_STATIC_MAX_N || fdgs_knn_ws_bytes(P) > KNN_STATIC_BYTES) return FDGS_E_TOO_LARGE;
+    void* base = nullptr;
+    const int rc = knn_static_ptr(&base);
+    if (rc) return rc;
+    char* c = (char*)base;
+    int* bb = (int*)c;                 c += fdgs_align_up(32);
+    uint32_t* count = (uint32_t*)c;    c += fdgs_align_up((cells + 1) * 4);
+    uint32_t* start = (uint32_t*)c;    c += fdgs_align_up((cells + 1) * 4);
+    uint32_t* cursor = (uint32_t*)c;   c += fdgs_align_up(cells * 4);
+    uint32_t* cell_of = (uint32_t*)c;  c += fdgs_align_up((size_t)P * 4);
+    uint32_t* sorted = (uint32_t*)c;
+    // the array keeps the previous call's contents: the two counters start at zero, everything else is overwritten before use
+    FDGS_CUDA(cudaMemsetAsync(count, 0, (cells + 1) * 4, stream));
+    FDGS_CUDA(cudaMemsetAsync(cursor, 0, cells * 4, stream));
+    k_bbox_init<<<1, 32, 0, stream>>>(bb);
+    k_bbox<<<std::min((P + 255) / 256, 1184), 256, 0, stream>>>(P, points, bb);
+    k_knn_count<<<(P + 255) / 256, 256, 0, stream>>>(P, points, bb, n, count, cell_of);
+    k_scan_u32<<<1, 1024, 0, stream>>>((int)cells, count, start);
+    k_knn_scatter<<<(P + 255) / 256, 256, 0, stream>>>(P, cell_of, start, cursor, sorted);
+    k_knn_search<<<(P + 127) / 128, 128, 0, stream>>>(P, points, bb, n, start, sorted, mean_dist2);
+    FDGS_CUDA(cudaGetLastError());
     return FDGS_OK;
 }
 

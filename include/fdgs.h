@@ -34,7 +34,8 @@ enum {
     FDGS_E_BADARG = -1,    /* null/inconsistent arguments (reference: AT_ERROR, RAST/rasterize_points.cu:57-59) */
     FDGS_E_WORKSPACE = -2, /* a caller-owned workspace is smaller than fdgs_*_bytes() says */
     FDGS_E_UNSUPPORTED = -3,
-    FDGS_E_SMEM = -4       /* configuration does not fit the 227 KB shared-memory budget */
+    FDGS_E_SMEM = -4,      /* configuration does not fit the 227 KB shared-memory budget */
+    FDGS_E_TOO_LARGE = -5  /* problem size exceeds the fixed maximum of an allocation-free entry point (fdgs_*_static) */
 };
 
 /* ---- library info ------------------------------------------------------- */
@@ -398,6 +399,20 @@ int fdgs_densify_stats(int P, const int32_t* radii, const uint8_t* visible, cons
  * same, so the result is bit-identical).  ws: fdgs_knn_ws_bytes(P) bytes of device scratch.                               */
 size_t fdgs_knn_ws_bytes(int P);
 int fdgs_knn_mean_dist2(int P, const float* points /* [P,3] */, float* mean_dist2 /* [P] */, void* ws, size_t ws_bytes, void* stream);
+
+/* Allocation-free variant of fdgs_knn_mean_dist2.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  Same inputs, same output (bit-identical to fdgs_knn_mean_dist2), but the scratch is a file-scope
+ * `static __device__` array of the library instead of a caller workspace: the call performs no cudaMalloc / cudaFree and
+ * calls no allocating library routine.
+ *   - limit: P <= FDGS_KNN_STATIC_MAX_POINTS (= fdgs_knn_static_max_points()); a larger P returns FDGS_E_TOO_LARGE and
+ *     launches nothing.  The array is 3 689 728 bytes and is held by every GPU that loads the library until exit.
+ *   - the array is SHARED by all calls on a device and keeps the last call's contents (the call clears what must start at
+ *     zero): two calls that overlap on the GPU (different streams, or different host threads) RACE - serialise them.
+ *   - the device to use is the CURRENT device; `points` / `mean_dist2` are device pointers on it.                        */
+#define FDGS_KNN_STATIC_MAX_POINTS 262144
+int fdgs_knn_static_max_points(void);
+int fdgs_knn_mean_dist2_static(int P, const float* points /* [P,3] */, float* mean_dist2 /* [P] */, void* stream);
 
 /* Instant4D grid pruning (utils/grid_pruning.py:16-41 -> open3d PointCloud::VoxelDownSample): voxel index =
  * floor((p - (min_bound - voxel_size / 2)) / voxel_size) per axis, one output point per occupied voxel = the mean position
