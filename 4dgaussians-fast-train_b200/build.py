@@ -36,16 +36,24 @@ def build(force=False, verbose=True):
     objs = []
     procs = []
     os.makedirs(os.path.join(HERE, "build"), exist_ok=True)
+    hdrs = [os.path.join(CSRC, h) for h in HEADERS] + [os.path.abspath(__file__)]
+    stamp = os.path.join(HERE, "build", "flags.txt")          # objects are reused only under the same flags
+    same_flags = os.path.exists(stamp) and open(stamp).read() == " ".join(NVCC_FLAGS)
     for s in SOURCES:
         o = os.path.join(HERE, "build", s.replace(".cu", ".o"))
+        objs.append(o)
+        deps = [os.path.join(CSRC, s)] + [h for h in hdrs if os.path.exists(h)]
+        if not force and same_flags and os.path.exists(o) and not any(_newer(d, o) for d in deps):
+            continue
         cmd = [nvcc] + NVCC_FLAGS + ["-c", os.path.join(CSRC, s), "-o", o]
         if verbose:
             print(" ".join(cmd), flush=True)
         procs.append((subprocess.Popen(cmd), cmd))
-        objs.append(o)
     for p, cmd in procs:
         if p.wait() != 0:
             raise RuntimeError("nvcc failed: " + " ".join(cmd))
+    with open(stamp, "w") as f:
+        f.write(" ".join(NVCC_FLAGS))
     cmd = [nvcc, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", OUT] + objs + ["-lcudart"]
     if verbose:
         print(" ".join(cmd), flush=True)

@@ -12,6 +12,8 @@
 //   relu(h) hi/lo -> shared memory (K-major): the A operand of every head's first GEMM
 //   head j  z = relu(h) W1_j^T     D -> TMEM ACC ; relu(z) hi/lo -> TMEM (A operand of the output layer)
 //           o = relu(z) W2_j^T     N = 16 / 48 (out padded), D -> TMEM OUT ; the next head's z GEMM overlaps its epilogue
+//           heads with <= 4 outputs (pos, scales, rotations, opacity): o on the CUDA CORES inside the relu(z) pass
+//           (FDGS_FWD_OUT_CC, see below) - no hi/lo split, no TMEM stores, no N = 16 GEMM to wait for
 //   outputs are staged in shared memory and written (base + delta) with fully coalesced row-contiguous stores.
 // Training calls also keep feat, relu(h), relu(z_j) in a blocked layout for the backward kernels (deform_tc_bwd.cu).
 // Replaces scene/deformation.py:45-148 + scene/hexplane.py:73-183 (reference: ~200 ATen launches per view).
@@ -47,6 +49,10 @@ template <int WN> struct EpiCfg {
     static constexpr int NEW = 4 * NG;                                   // epilogue warps; warp NEW = producer, NEW + 1 = MMA issuer
     static constexpr int NTHREADS = NEPI + 64;
 };
+// Output layers with <= 4 columns on the CUDA cores (1) or as N = 16 tensor-core GEMMs like the 48-wide one (0, for A/B).
+#ifndef FDGS_FWD_OUT_CC
+#define FDGS_FWD_OUT_CC 1
+#endif
 constexpr int MAXCH = 96;          // chunks per tile: F/16 + heads * (Wn/16 + Wn/16)
 
 // Pre-formatted weights ("wprep" workspace): a chunk holds KCH=16 reduction columns of an [N rows][K] weight as a hi
@@ -58,6 +64,7 @@ struct TcPlan {
     int Wn, F, nheads;
     int heads[FDGS_NUM_HEADS];
     int nop[FDGS_NUM_HEADS];       // padded output width of plan slot j
+    int cc[FDGS_NUM_HEADS];        // plan slot j: output layer on the CUDA cores (its W2 is not formatted or streamed)
     int nchunks;
     int coff[MAXCH];               // float offset of chunk c inside wprep
     int cfl[MAXCH];                // floats of chunk c
@@ -65,6 +72,7 @@ struct TcPlan {
 };
 
 static inline int out_pad(int h) { return head_out(h) > 16 ? 48 : 16; }
+static inline int out_cc(int h) { return (FDGS_FWD_OUT_CC && head_out(h) <= 4) ? 1 : 0; }
 
 static inline TcPlan make_plan(const Layout& lo) {
     TcPlan p;
@@ -74,10 +82,11 @@ static inline TcPlan make_plan(const Layout& lo) {
     long long off1[FDGS_NUM_HEADS], off2[FDGS_NUM_HEADS];
     for (int j = 0; j < FDGS_NUM_HEADS; ++j) {
         p.nop[j] = j < p.nheads ? out_pad(p.heads[j]) : 16;
+        p.cc[j] = j < p.nheads ? out_cc(p.heads[j]) : 0;
         off1[j] = off2[j] = 0;
         if (j < p.nheads) {
             off1[j] = o; o += (long long)(lo.Wn / KCH) * 32 * lo.Wn;
-            off2[j] = o; o += (long long)(lo.Wn / KCH) * 32 * p.nop[j];
+            off2[j] = o; if (!p.cc[j]) o += (long long)(lo.Wn / KCH) * 32 * p.nop[j];
         }
     }
     p.floats = o;
@@ -87,7 +96,7 @@ static inline TcPlan make_plan(const Layout& lo) {
     if (p.nheads > 0) add(off1[0], lo.Wn / KCH, lo.Wn);
     for (int j = 0; j < p.nheads; ++j) {
         if (j + 1 < p.nheads) add(off1[j + 1], lo.Wn / KCH, lo.Wn);
-        add(off2[j], lo.Wn / KCH, p.nop[j]);
+        if (!p.cc[j]) add(off2[j], lo.Wn / KCH, p.nop[j]);
     }
     p.nchunks = c;
     return p;
@@ -123,6 +132,7 @@ struct TcNet {
     const float* b0;
     const float* b1[FDGS_NUM_HEADS];
     const float* b2[FDGS_NUM_HEADS];
+    const float* w2[FDGS_NUM_HEADS];     // raw [NO][Wn] output weights (CUDA-core output layers)
 };
 
 struct TcFwdIO {
@@ -192,6 +202,11 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
     float* B1s = sm + sp.off_b1;
     float* B2s = sm + sp.off_b2;
     float* OUTs = sm + sp.off_out;
+    // CUDA-core output layers (plan.cc): their W2 as [head][column][4] and the per-column-group partial sums, double
+    // buffered.  Both live in the staging buffer, which only a tensor-core output layer (the 48-wide head) fills with rows:
+    // W2s is therefore re-read at the start of every tile.
+    float* W2s = OUTs;                                        // [4][WN][4]
+    float* PARTs = OUTs + 4 * WN * 4;                         // [2][NG][128][4]
     float* ring = sm + sp.off_ring;
     uint64_t* bars = reinterpret_cast<uint64_t*>(sm + sp.off_bars);
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + B_COUNT + 2);
@@ -308,6 +323,7 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
                         gemm(tm + (((i + 1) & 1) ? TM_A1 : TM_A0), WN / KCH, WN, idesc, true, 0, 0);   // z_{i+1}: runs ahead
                         commit(B_ACCFULL + ((i + 1) & 1));
                     }
+                    if (plan.cc[i]) continue;                          // o_i is computed by the epilogue warps themselves
                     mbar_wait(&bars[B_RZFULL], ph_rz); ph_rz ^= 1;     // z_i drained, relu(z_i) hi/lo in TMEM
                     tc_fence_after();
                     gemm(tm + ((i & 1) ? TM_A1 : TM_A0), WN / KCH, plan.nop[i], make_idesc_tf32(128, plan.nop[i], 0, 0), false,
@@ -322,6 +338,8 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
         const uint32_t lane_base = tmem + ((uint32_t)((warp & 3) * 32) << 16);
         const int col0 = hf * NH;
         uint32_t ph_a0 = 0, ph_a1 = 0, ph_out = 0;
+        uint32_t plan_ccmask = 0;                                    // by head id
+        for (int j = 0; j < plan.nheads; ++j) if (plan.cc[j]) plan_ccmask |= 1u << plan.heads[j];
         const int C = lo.C;
         // sampler mapping: LP adjacent lanes share one point and take consecutive channel quads, so a warp-wide gather
         // touches 32/LP points x 64-byte taps instead of 32 unrelated lines (the L1 tag stage serves one line per cycle)
@@ -351,6 +369,14 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
         for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
             const int p0 = tile * TP;
             const size_t rowoff = (size_t)tile * TP * WN + (row >> 5) * 32 * WN + (row & 31) * 4;   // blocked save layout
+            // W2 of the CUDA-core output layers: 4 * WN * 4 floats = 4 per thread, loaded now and stored after the feat tile
+            float w2v[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const int e = tid + k * NEPI;
+                const int hh = e / (WN * 4), c = (e >> 2) % WN, o = e & 3;
+                w2v[k] = (((plan_ccmask >> hh) & 1) && o < head_out(hh)) ? __ldg(net.w2[hh] + o * WN + c) : 0.f;
+            }
             // ---- feat tile (hi / lo) from the values sampled ahead of time (see sample_pass) -------------------
             for (int pass = 0; pass < SPASS; ++pass) {
                 const int srow = pass * (NEW * PPW) + warp * PPW + sg;
@@ -369,6 +395,8 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
             }
             const int next_tile = tile + gridDim.x;
             int next_pass = 0;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) W2s[tid + k * NEPI] = w2v[k];
             fence_async_smem();
             epi_bar();
             if (tid == 0) mbar_arrive(&bars[B_FEATFULL]);
@@ -440,6 +468,69 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
 #define FDGS_RELU_UNROLL 1
 #endif
                 constexpr int RELU_UNROLL = FDGS_RELU_UNROLL;
+                if (plan.cc[i]) {
+                    // ---- <= 4 outputs: o = relu(z) W2^T on the CUDA cores, inside the pass that drains z ------------------
+                    // Each thread dots its NH columns of relu(z) with W2 (one broadcast LDS.128 per column) while it writes
+                    // the kept copy; the NG partial sums of a row meet in shared memory (fixed order: deterministic).
+                    float po[4] = {0.f, 0.f, 0.f, 0.f};
+                    const float* w2h = W2s + (h * WN + col0) * 4;
+#pragma unroll (RELU_UNROLL)
+                    for (int c0 = 0; c0 < NH; c0 += 16) {
+                        uint32_t v[16];
+                        tmem_ld16(acc + col0 + c0, v);
+                        tmem_wait_ld();
+                        uint32_t mbits = 0u;
+#pragma unroll
+                        for (int j = 0; j < 16; ++j) {
+                            const float z = fmaxf(__uint_as_float(v[j]) + B1s[h * WN + col0 + c0 + j], 0.f);
+                            const float4 w = *reinterpret_cast<const float4*>(w2h + (c0 + j) * 4);
+                            po[0] = fmaf(z, w.x, po[0]); po[1] = fmaf(z, w.y, po[1]);
+                            po[2] = fmaf(z, w.z, po[2]); po[3] = fmaf(z, w.w, po[3]);
+                            v[j] = __float_as_uint(z);
+                            mbits |= (z > 0.f ? 1u : 0u) << j;
+                        }
+                        if (c0 < 32) zm0 |= mbits << (c0 & 31); else zm1 |= mbits << (c0 & 31);
+                        if (rz) {
+#pragma unroll
+                            for (int j = 0; j < 16; j += 4)
+                                __stcs(reinterpret_cast<float4*>(rz + ((col0 + c0 + j) >> 2) * 128),
+                                       make_float4(__uint_as_float(v[j]), __uint_as_float(v[j + 1]), __uint_as_float(v[j + 2]), __uint_as_float(v[j + 3])));
+                        }
+                    }
+                    if (io.S_M) {
+                        uint32_t* mp = io.S_M + ((size_t)(1 + h) * io.Pp + (p0 + row)) * 4 + hf * (4 / NG);
+                        mp[0] = zm0;
+                        if (NH > 32) mp[1] = zm1;
+                    }
+                    const float* pb = PARTs + (i & 1) * (NG * 512);
+                    *reinterpret_cast<float4*>(PARTs + (i & 1) * (NG * 512) + (hf * 128 + row) * 4) = make_float4(po[0], po[1], po[2], po[3]);
+                    tc_fence_before();
+                    epi_bar();
+                    if (tid == 0 && i + 2 < plan.nheads) mbar_arrive(&bars[B_OUTFREE]);          // accumulator free for z_{i+2}
+                    PT(4)
+                    if (next_tile < ntiles && next_pass < SPASS) sample_pass(next_tile, next_pass++);
+                    PT(7)
+                    auto delta = [&](int idx) {
+                        const int r = idx / NO, n = idx - r * NO;
+                        float d = B2s[b2_row0(h) + n];
+#pragma unroll
+                        for (int g = 0; g < NG; ++g) d += pb[(g * 128 + r) * 4 + n];
+                        return d;
+                    };
+                    float* dst = outp + (size_t)p0 * NO;
+                    if (vec) {                                        // rows * NO <= 512 floats: one float4 per thread at most
+                        if (tid * 4 < total)
+                            reinterpret_cast<float4*>(dst)[tid] = make_float4(base[0].x + delta(tid * 4), base[0].y + delta(tid * 4 + 1),
+                                                                              base[0].z + delta(tid * 4 + 2), base[0].w + delta(tid * 4 + 3));
+                    } else if (h == 2 && lo.apply_rotation) {
+                        for (int idx = tid; idx < total; idx += NEPI) dst[idx] = delta(idx);
+                    } else {
+                        const float* src = inp + (size_t)p0 * NO;
+                        for (int idx = tid; idx < total; idx += NEPI) dst[idx] = src[idx] + delta(idx);
+                    }
+                    PT(6)
+                    continue;                                         // the partial sums are double buffered: no barrier here
+                }
 #pragma unroll (RELU_UNROLL)
                 for (int c0 = 0; c0 < NH; c0 += 16) {
                     uint32_t v[16], hi[16], lw[16];
@@ -587,6 +678,7 @@ int forward(const Layout& lo, const FdgsDeformForward* a, const float* packed, c
     for (int j = 0; j < plan.nheads; ++j) {
         const int h = plan.heads[j];
         pa.s[ns++] = PrepSec{a->net.head_w1[h], Wn, Wn, Wn, Wn, off}; off += (long long)(Wn / KCH) * 32 * Wn;
+        if (plan.cc[j]) continue;                            // read raw by the kernel (CUDA-core output layer)
         pa.s[ns++] = PrepSec{a->net.head_w2[h], Wn, plan.nop[j], head_out(h), Wn, off}; off += (long long)(Wn / KCH) * 32 * plan.nop[j];
     }
     pa.nsec = ns;
@@ -598,7 +690,7 @@ int forward(const Layout& lo, const FdgsDeformForward* a, const float* packed, c
 
     TcNet net;
     net.wprep = wprep; net.b0 = a->net.trunk_b[0];
-    for (int h = 0; h < FDGS_NUM_HEADS; ++h) { net.b1[h] = a->net.head_b1[h]; net.b2[h] = a->net.head_b2[h]; }
+    for (int h = 0; h < FDGS_NUM_HEADS; ++h) { net.b1[h] = a->net.head_b1[h]; net.b2[h] = a->net.head_b2[h]; net.w2[h] = a->net.head_w2[h]; }
     TcFwdIO io;
     io.P = a->P; io.sh_coeffs = a->sh_coeffs;
     io.xyz = a->xyz; io.scales = a->scales; io.rot = a->rotations; io.opacity = a->opacity; io.shs = a->shs;
