@@ -1,10 +1,11 @@
 // Tensor-core (tcgen05 + TMEM) implementation of the fused HexPlane sampler + deformation MLP for sm_100a.
 //
 // One persistent CTA per SM, 128 points per tile, warp-specialised:
-//   warps 0-7  sampler + epilogues (epilogues: thread = point row = TMEM lane, two column halves;
-//              sampler: LP adjacent lanes per point, see below)
-//   warp  8    producer: streams pre-formatted weight chunks global(L2) -> shared with 1-D bulk async copies
-//   warp  9    MMA issuer: one thread issues every tcgen05.mma and commits to mbarriers
+//   epilogue warps (8 or 16)  thread = point row = TMEM lane, 2 or 4 column groups
+//   sampler warps (8)         HexPlane gathers of tile t+1 WHILE the epilogue warps work through the heads of tile t
+//                             (LP adjacent lanes per point, see below); they write the feat tile once relu(h) is dead
+//   producer warp             streams pre-formatted weight chunks global(L2) -> shared with 1-D bulk async copies
+//   MMA warp                  one elected thread issues every tcgen05.mma and commits to mbarriers
 //
 // Every GEMM runs as 3xTF32 (hi*hi + lo*hi + hi*lo, FP32 accumulate in TMEM) so that results match the reference's
 // FP32 cuBLAS/ATen path to ~1e-6 (BASELINE north_star: images within 1e-5); precision==1 runs one pass.
@@ -24,7 +25,7 @@
 #ifdef FDGS_PHASE_TIMING
 #define PT_DECL long long pt_[8] = {0,0,0,0,0,0,0,0}; long long pt_t = clock64();
 #define PT(i) { const long long n_ = clock64(); pt_[i] += n_ - pt_t; pt_t = n_; }
-#define PT_PRINT if (blockIdx.x == 0 && tid == 0) printf("fwd phases (cycles, CTA0): sample %lld | wait_trunk %lld | trunk_epi %lld | wait_z %lld | relu_pass %lld | wait_out %lld | out_pass %lld | next_tile_sampling %lld\n", pt_[0], pt_[1], pt_[2], pt_[3], pt_[4], pt_[5], pt_[6], pt_[7]);
+#define PT_PRINT if (blockIdx.x == 0 && tid == 0) printf("fwd phases (cycles, epilogue thread 0 of CTA0): w2_load %lld | wait_trunk %lld | trunk_epi %lld | wait_z %lld | relu_pass %lld | wait_out %lld | out_pass %lld\n", pt_[0], pt_[1], pt_[2], pt_[3], pt_[4], pt_[5], pt_[6]);
 #else
 #define PT_DECL
 #define PT(i)
@@ -46,8 +47,10 @@ template <int WN> struct EpiCfg {
     static constexpr int NG = (FDGS_FWD_EPI16 && WN == 128) ? 4 : 2;   // column groups
     static constexpr int NH = WN / NG;                                   // accumulator columns per epilogue thread
     static constexpr int NEPI = 128 * NG;                                // epilogue threads
-    static constexpr int NEW = 4 * NG;                                   // epilogue warps; warp NEW = producer, NEW + 1 = MMA issuer
-    static constexpr int NTHREADS = NEPI + 64;
+    static constexpr int NEW = 4 * NG;                                   // epilogue warps
+    static constexpr int NSMP = 8;                                       // sampler warps: NEW .. NEW + NSMP - 1
+    static constexpr int WPROD = NEW + NSMP, WMMA = NEW + NSMP + 1;      // producer warp, MMA issuer warp
+    static constexpr int NTHREADS = NEPI + NSMP * 32 + 64;
 };
 // Output layers with <= 4 columns on the CUDA cores (1) or as N = 16 tensor-core GEMMs like the 48-wide one (0, for A/B).
 #ifndef FDGS_FWD_OUT_CC
@@ -181,7 +184,7 @@ template <int N> __device__ __forceinline__ void epi_bar_n() { asm volatile("bar
 // the other accumulator WHILE the epilogue warps turn z_i into relu(z_i) hi / lo.
 constexpr uint32_t TM_A0 = 0, TM_A1 = 128, TM_ZHI = 256, TM_ZLO = 384;
 constexpr int B_WFULL = 0, B_WEMPTY = 8, B_FEATFULL = 16, B_ACCFULL = 17 /* +1 */, B_HFULL = 19, B_RZFULL = 20, B_OUTFULL = 21,
-              B_OUTFREE = 22, B_COUNT = 23;
+              B_OUTFREE = 22, B_HSFREE = 23, B_TRUNKFULL = 24, B_COUNT = 25;
 
 __device__ __forceinline__ int b2_row0(int h) { return h == 0 ? 0 : h == 1 ? 3 : h == 2 ? 6 : h == 3 ? 10 : 11; }
 
@@ -213,6 +216,7 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int S = sp.slots;
     constexpr int NG = EpiCfg<WN>::NG, NH = EpiCfg<WN>::NH, NEPI = EpiCfg<WN>::NEPI, NEW = EpiCfg<WN>::NEW;
+    constexpr int NSMP = EpiCfg<WN>::NSMP, WPROD = EpiCfg<WN>::WPROD, WMMA = EpiCfg<WN>::WMMA;
     auto epi_bar = [] { epi_bar_n<EpiCfg<WN>::NEPI>(); };
     constexpr int SLOT = 32 * WN;              // floats per ring slot
     const int F = lo.F;
@@ -222,7 +226,7 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
         for (int i = 0; i < B_COUNT; ++i) mbar_init(&bars[i], 1);
         fence_mbar_init();
     }
-    if (warp == NEW + 1) tmem_alloc(tmem_slot, 512);
+    if (warp == WMMA) tmem_alloc(tmem_slot, 512);
     if (tid < NEPI) {
         for (int i = tid; i < WN; i += NEPI) B0s[i] = net.b0[i];
         for (int j = 0; j < plan.nheads; ++j) {
@@ -237,7 +241,7 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
     tc_fence_after();
     const uint32_t tmem = *tmem_slot;
 
-    if (warp == NEW) {
+    if (warp == WPROD) {
         // ===== producer: weight chunks, the same sequence for every tile ==================================
         if (lane == 0) {
             uint32_t g = 0;
@@ -251,7 +255,7 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
                 }
         }
         __syncwarp();
-    } else if (warp == NEW + 1) {
+    } else if (warp == WMMA) {
         // ===== MMA issuer: the whole warp runs the loop, one elected lane issues (see umma.cuh:elect_one) ============
         {
             const uint32_t tm = __shfl_sync(0xffffffffu, tmem, 0);
@@ -259,7 +263,7 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
             const uint32_t idesc = make_idesc_tf32(128, WN, 0, 0);
             const uint64_t f_hi0 = desc_kmajor(F_hi, 128, 0), f_lo0 = desc_kmajor(F_lo, 128, 0);   // feat and relu(h) alias
             const uint32_t ring_u = smem_addr(ring) >> 4;
-            uint32_t slot = 0, wph = 0, ph_feat = 0, ph_h = 0, ph_rz = 0;
+            uint32_t slot = 0, wph = 0, ph_feat = 0, ph_h = 0, ph_rz = 0, ph_free = 0;
             // D[acc] (+)= A . B^T over `nck` streamed chunks of an [N][K] weight; A: shared-memory tile (SS) or TMEM columns
             auto gemm = [&](uint32_t acc, int nck, int N, uint32_t id, bool ss, uint32_t ta_hi, uint32_t ta_lo) {
                 const uint64_t bd0 = make_sdesc(0u, (uint32_t)N * 16u, 128u);      // B descriptor without the start address
@@ -301,18 +305,24 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
                     if (++slot == (uint32_t)S) { slot = 0; wph ^= 1; }
                 }
             };
-            uint32_t ph_free = 0;
             auto commit = [&](int b) { if (leader) mma_commit(&bars[b]); __syncwarp(); };
+            // The trunk GEMM of tile t+1 can start while the epilogue warps still drain the LAST head of tile t (the sampler
+            // warps deliver the feat tile early): it goes to the accumulator that head does not use, once the head before
+            // it (the previous user of that accumulator) has been drained (B_OUTFREE, arrived by every head but the last).
+            const uint32_t trunk_acc = (plan.nheads & 1) ? TM_A1 : TM_A0;
             for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
                 mbar_wait(&bars[B_FEATFULL], ph_feat); ph_feat ^= 1;
+                if (tile != (int)blockIdx.x && plan.nheads >= 2) { mbar_wait(&bars[B_OUTFREE], ph_free); ph_free ^= 1; }
                 tc_fence_after();
-                gemm(tm + TM_A0, F / KCH, WN, idesc, true, 0, 0);                             // h = feat W0^T
-                commit(B_ACCFULL);
+                gemm(tm + trunk_acc, F / KCH, WN, idesc, true, 0, 0);                         // h = feat W0^T
+                commit(B_TRUNKFULL);        // a barrier of its own: this GEMM can complete before the epilogue warps have
+                                            // waited for the last z of the previous tile (a shared barrier would lap them)
                 mbar_wait(&bars[B_HFULL], ph_h); ph_h ^= 1;
                 tc_fence_after();
                 if (plan.nheads > 0) {
                     gemm(tm + TM_A0, WN / KCH, WN, idesc, true, 0, 0);                        // z_0 = relu(h) W1_0^T
                     commit(B_ACCFULL);
+                    if (plan.nheads == 1) commit(B_HSFREE);            // last reader of relu(h): the sampler warps may overwrite it
                 }
                 for (int i = 0; i < plan.nheads; ++i) {
                     if (i + 1 < plan.nheads) {
@@ -322,6 +332,7 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
                         }
                         gemm(tm + (((i + 1) & 1) ? TM_A1 : TM_A0), WN / KCH, WN, idesc, true, 0, 0);   // z_{i+1}: runs ahead
                         commit(B_ACCFULL + ((i + 1) & 1));
+                        if (i + 2 == plan.nheads) commit(B_HSFREE);
                     }
                     if (plan.cc[i]) continue;                          // o_i is computed by the epilogue warps themselves
                     mbar_wait(&bars[B_RZFULL], ph_rz); ph_rz ^= 1;     // z_i drained, relu(z_i) hi/lo in TMEM
@@ -332,54 +343,41 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
                 }
             }
         }
-    } else {
-        // ===== sampler + epilogues ===============================================================================
-        const int row = tid & 127, hf = tid >> 7;                    // epilogue mapping: TMEM lane = point row, column half
-        const uint32_t lane_base = tmem + ((uint32_t)((warp & 3) * 32) << 16);
-        const int col0 = hf * NH;
-        uint32_t ph_a0 = 0, ph_a1 = 0, ph_out = 0;
-        uint32_t plan_ccmask = 0;                                    // by head id
-        for (int j = 0; j < plan.nheads; ++j) if (plan.cc[j]) plan_ccmask |= 1u << plan.heads[j];
+    } else if (warp >= NEW) {
+        // ===== sampler warps =====================================================================================
+        // LP adjacent lanes share one point and take consecutive channel quads, so a warp-wide gather touches 32/LP points
+        // x 64-byte taps instead of 32 unrelated lines (the L1 tag stage serves one line per cycle).  The gathers of tile
+        // t+1 run while the epilogue warps and the tensor core work on tile t; the sampled values wait in nf[] until the
+        // last GEMM that reads relu(h) of tile t has completed (B_HSFREE: the feat tile aliases that buffer).
+        const int sw = warp - NEW, stid = tid - NEPI;
         const int C = lo.C;
-        // sampler mapping: LP adjacent lanes share one point and take consecutive channel quads, so a warp-wide gather
-        // touches 32/LP points x 64-byte taps instead of 32 unrelated lines (the L1 tag stage serves one line per cycle)
         const int items = F >> 2;
-        const int LP = (items & 7) == 0 ? 8 : 4, IPT = items / LP, PPW = 32 / LP, SPASS = TP / (NEW * PPW);
+        const int LP = (items & 7) == 0 ? 8 : 4, IPT = items / LP, PPW = 32 / LP, SPASS = TP / (NSMP * PPW);
         const int sg = lane / LP, sq = lane % LP;
-        PT_DECL
-        // HexPlane sampling of one quarter (8*PPW points) of tile t into registers/local memory.  The passes of tile t+1
-        // are issued inside tile t's head loop, where the epilogue warps would otherwise wait for the output-layer GEMM.
         float4 nf[8];                                                // SPASS * IPT <= 8 float4 per thread
-        auto sample_pass = [&](int t, int pass) {
-            const int srow = pass * (NEW * PPW) + warp * PPW + sg;
-            const int sp_ = t * TP + srow;
-            const bool sval = sp_ < io.P;
-            float q[4] = {0.f, 0.f, 0.f, 0.f};
-            if (sval) point_coords(lo, io.xyz, sp_, 0.f, q);
-            for (int it = 0; it < IPT; ++it) {
-                const int item = sq + it * LP;
-                const int l = (item * 4) / C, c0 = (item * 4) % C;
-                float prod[4] = {0.f, 0.f, 0.f, 0.f};
-                if (sval) sample_level<4>(lo, l, q, packed, trow, c0, prod);
-                nf[pass * IPT + it] = make_float4(prod[0], prod[1], prod[2], prod[3]);
-            }
-        };
-        if ((int)blockIdx.x < ntiles)
-            for (int pass = 0; pass < SPASS; ++pass) sample_pass(blockIdx.x, pass);
+        uint32_t ph_free = 0;
         for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-            const int p0 = tile * TP;
-            const size_t rowoff = (size_t)tile * TP * WN + (row >> 5) * 32 * WN + (row & 31) * 4;   // blocked save layout
-            // W2 of the CUDA-core output layers: 4 * WN * 4 floats = 4 per thread, loaded now and stored after the feat tile
-            float w2v[4];
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                const int e = tid + k * NEPI;
-                const int hh = e / (WN * 4), c = (e >> 2) % WN, o = e & 3;
-                w2v[k] = (((plan_ccmask >> hh) & 1) && o < head_out(hh)) ? __ldg(net.w2[hh] + o * WN + c) : 0.f;
-            }
-            // ---- feat tile (hi / lo) from the values sampled ahead of time (see sample_pass) -------------------
             for (int pass = 0; pass < SPASS; ++pass) {
-                const int srow = pass * (NEW * PPW) + warp * PPW + sg;
+                const int srow = pass * (NSMP * PPW) + sw * PPW + sg;
+                const int sp_ = tile * TP + srow;
+                const bool sval = sp_ < io.P;
+                float q[4] = {0.f, 0.f, 0.f, 0.f};
+                if (sval) point_coords(lo, io.xyz, sp_, 0.f, q);
+                for (int it = 0; it < IPT; ++it) {
+                    const int item = sq + it * LP;
+                    const int l = (item * 4) / C, c0 = (item * 4) % C;
+                    float prod[4] = {0.f, 0.f, 0.f, 0.f};
+                    if (sval) sample_level<4>(lo, l, q, packed, trow, c0, prod);
+                    nf[pass * IPT + it] = make_float4(prod[0], prod[1], prod[2], prod[3]);
+                }
+            }
+            if (tile != (int)blockIdx.x) {                           // relu(h) of the previous tile is dead
+                mbar_wait(&bars[B_HSFREE], ph_free); ph_free ^= 1;
+                tc_fence_after();
+            }
+            // ---- feat tile (hi / lo) -> shared memory (A operand of the trunk GEMM), kept copy ---------------------
+            for (int pass = 0; pass < SPASS; ++pass) {
+                const int srow = pass * (NSMP * PPW) + sw * PPW + sg;
                 for (int it = 0; it < IPT; ++it) {
                     const int item = sq + it * LP;
                     const float4 pr = nf[pass * IPT + it];
@@ -393,23 +391,39 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
                         __stcs(reinterpret_cast<float4*>(io.S_F + (size_t)tile * TP * F + (srow >> 5) * 32 * F + (item * 32 + (srow & 31)) * 4), pr);
                 }
             }
-            const int next_tile = tile + gridDim.x;
-            int next_pass = 0;
-#pragma unroll
-            for (int k = 0; k < 4; ++k) W2s[tid + k * NEPI] = w2v[k];
             fence_async_smem();
-            epi_bar();
-            if (tid == 0) mbar_arrive(&bars[B_FEATFULL]);
+            asm volatile("bar.sync 2, %0;" ::"n"(NSMP * 32) : "memory");
+            if (stid == 0) mbar_arrive(&bars[B_FEATFULL]);
+        }
+    } else {
+        // ===== epilogues ===========================================================================================
+        const int row = tid & 127, hf = tid >> 7;                    // epilogue mapping: TMEM lane = point row, column group
+        const uint32_t lane_base = tmem + ((uint32_t)((warp & 3) * 32) << 16);
+        const int col0 = hf * NH;
+        uint32_t ph_a0 = 0, ph_a1 = 0, ph_out = 0, ph_tr = 0;
+        uint32_t plan_ccmask = 0;                                    // by head id
+        for (int j = 0; j < plan.nheads; ++j) if (plan.cc[j]) plan_ccmask |= 1u << plan.heads[j];
+        PT_DECL
+        for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+            const int p0 = tile * TP;
+            const size_t rowoff = (size_t)tile * TP * WN + (row >> 5) * 32 * WN + (row & 31) * 4;   // blocked save layout
+            // W2 of the CUDA-core output layers: 4 * WN * 4 floats = 4 per thread (visible to the head loop through the
+            // barrier that ends the trunk epilogue)
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const int e = tid + k * NEPI;
+                const int hh = e / (WN * 4), c = (e >> 2) % WN, o = e & 3;
+                W2s[e] = (((plan_ccmask >> hh) & 1) && o < head_out(hh)) ? __ldg(net.w2[hh] + o * WN + c) : 0.f;
+            }
             PT(0)
-
             // ---- trunk epilogue: relu(h + b0) -> shared memory hi / lo (A operand of the heads), kept copy ----------
-            mbar_wait(&bars[B_ACCFULL], ph_a0); ph_a0 ^= 1;
+            mbar_wait(&bars[B_TRUNKFULL], ph_tr); ph_tr ^= 1;
             tc_fence_after();
             PT(1)
 #pragma unroll 1
             for (int c0 = 0; c0 < NH; c0 += 32) {
                 uint32_t v[32];
-                tmem_ld32(lane_base + TM_A0 + col0 + c0, v);
+                tmem_ld32(lane_base + ((plan.nheads & 1) ? TM_A1 : TM_A0) + col0 + c0, v);
                 tmem_wait_ld();
                 uint32_t m = 0;
 #pragma unroll
@@ -433,6 +447,7 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
             tc_fence_before();
             epi_bar();
             if (tid == 0) mbar_arrive(&bars[B_HFULL]);
+            if (tid == 0 && plan.nheads == 0) mbar_arrive(&bars[B_HSFREE]);      // otherwise: the MMA warp, after the last z GEMM
             PT(2)
 
             // ---- heads -----------------------------------------------------------------------------------------
@@ -440,22 +455,16 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
                 const int h = plan.heads[i];
                 const int NO = head_out(h);
                 const int OS = NO == 48 ? 52 : NO;                      // staging row stride
-                // base values (the head's input rows of this tile, contiguous) are fetched now: their DRAM latency hides
-                // behind the two GEMMs.  Thread t owns float4s t, t + 256, ... of the tile's rows * NO floats.
+                // base values (the head's input rows of this tile, contiguous): thread t owns float4s t, t + NEPI, ... of the
+                // tile's rows * NO floats; fetched ahead of the wait whose latency hides them
                 float* outp = h == 0 ? io.o_xyz : h == 1 ? io.o_scales : h == 2 ? io.o_rot : h == 3 ? io.o_opacity : io.o_shs;
                 const float* inp = h == 0 ? io.xyz : h == 1 ? io.scales : h == 2 ? io.rot : h == 3 ? io.opacity : io.shs;
                 const int rows = io.P - p0 < TP ? io.P - p0 : TP;
                 const int total = rows * NO;
                 const bool vec = (total & 3) == 0 && !(h == 2 && lo.apply_rotation) && !(h == 4 && io.sh_coeffs != 16);
-                float4 base[6];
-                if (vec) {
-                    const float4* src4 = reinterpret_cast<const float4*>(inp + (size_t)p0 * NO);
-#pragma unroll
-                    for (int k = 0; k < 6; ++k) {
-                        const int i4 = tid + k * NEPI;
-                        base[k] = (i4 * 4 < total) ? __ldcs(src4 + i4) : make_float4(0.f, 0.f, 0.f, 0.f);
-                    }
-                }
+                const float4* src4 = reinterpret_cast<const float4*>(inp + (size_t)p0 * NO);
+                float4 base0 = make_float4(0.f, 0.f, 0.f, 0.f);       // <= 4 outputs: rows * NO <= 512 floats, one float4 per thread
+                if (vec && plan.cc[i] && tid * 4 < total) base0 = __ldcs(src4 + tid);
                 // z = relu(acc + b1): kept copy, hi / lo -> TMEM (A operand of the output layer)
                 const uint32_t acc = lane_base + ((i & 1) ? TM_A1 : TM_A0);
                 if (i & 1) { mbar_wait(&bars[B_ACCFULL + 1], ph_a1); ph_a1 ^= 1; }
@@ -506,10 +515,8 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
                     *reinterpret_cast<float4*>(PARTs + (i & 1) * (NG * 512) + (hf * 128 + row) * 4) = make_float4(po[0], po[1], po[2], po[3]);
                     tc_fence_before();
                     epi_bar();
-                    if (tid == 0 && i + 2 < plan.nheads) mbar_arrive(&bars[B_OUTFREE]);          // accumulator free for z_{i+2}
+                    if (tid == 0 && i + 1 < plan.nheads) mbar_arrive(&bars[B_OUTFREE]);          // accumulator free for z_{i+2} / the next trunk
                     PT(4)
-                    if (next_tile < ntiles && next_pass < SPASS) sample_pass(next_tile, next_pass++);
-                    PT(7)
                     auto delta = [&](int idx) {
                         const int r = idx / NO, n = idx - r * NO;
                         float d = B2s[b2_row0(h) + n];
@@ -520,8 +527,8 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
                     float* dst = outp + (size_t)p0 * NO;
                     if (vec) {                                        // rows * NO <= 512 floats: one float4 per thread at most
                         if (tid * 4 < total)
-                            reinterpret_cast<float4*>(dst)[tid] = make_float4(base[0].x + delta(tid * 4), base[0].y + delta(tid * 4 + 1),
-                                                                              base[0].z + delta(tid * 4 + 2), base[0].w + delta(tid * 4 + 3));
+                            reinterpret_cast<float4*>(dst)[tid] = make_float4(base0.x + delta(tid * 4), base0.y + delta(tid * 4 + 1),
+                                                                              base0.z + delta(tid * 4 + 2), base0.w + delta(tid * 4 + 3));
                     } else if (h == 2 && lo.apply_rotation) {
                         for (int idx = tid; idx < total; idx += NEPI) dst[idx] = delta(idx);
                     } else {
@@ -566,8 +573,14 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
                 epi_bar();
                 if (tid == 0) mbar_arrive(&bars[B_RZFULL]);
                 PT(4)
-                if (next_tile < ntiles && next_pass < SPASS) sample_pass(next_tile, next_pass++);     // overlaps o_i GEMM
-                PT(7)
+                float4 base[6];                                       // fetched now: the latency hides behind the o_i GEMM
+                if (vec) {
+#pragma unroll
+                    for (int k = 0; k < 6; ++k) {
+                        const int i4 = tid + k * NEPI;
+                        base[k] = (i4 * 4 < total) ? __ldcs(src4 + i4) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    }
+                }
 
                 // o = relu(z) W2^T (+ b2): accumulator -> staging [row][NO] -> coalesced base + delta
                 mbar_wait(&bars[B_OUTFULL], ph_out); ph_out ^= 1;
@@ -602,7 +615,7 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
                 }
                 tc_fence_before();
                 epi_bar();
-                if (tid == 0 && i + 2 < plan.nheads) mbar_arrive(&bars[B_OUTFREE]);      // accumulator free for z_{i+2}
+                if (tid == 0 && i + 1 < plan.nheads) mbar_arrive(&bars[B_OUTFREE]);      // accumulator free for z_{i+2} / the next trunk
                 {
                     const bool nobase = (h == 2 && lo.apply_rotation);
                     float* dst = outp + (size_t)p0 * NO;
@@ -632,7 +645,6 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
                 epi_bar();                                            // staging buffer free for the next head
                 PT(6)
             }
-            while (next_tile < ntiles && next_pass < SPASS) sample_pass(next_tile, next_pass++);
         }
         PT_PRINT
     }
@@ -640,7 +652,7 @@ k_deform_fwd_tc(Layout lo, TcPlan plan, SmemPlan sp, TcNet net, TcFwdIO io, cons
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
-    if (warp == NEW + 1) tmem_free(tmem, 512);
+    if (warp == WMMA) tmem_free(tmem, 512);
 }
 
 static int sm_count() {          // of the CURRENT device (one process may drive several)
