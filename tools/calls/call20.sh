@@ -1,0 +1,11 @@
+#!/bin/bash
+mkdir -p gpurun_out
+timeout 150 python -m pytest tests/test_gpu_deform.py tests/test_gpu_e2e.py tests/test_gpu_glue.py -m gpu -x -q > gpurun_out/r02_gputest_20.log 2>&1
+rc=$?; echo "pytest rc=$rc" >> gpurun_out/r02_gputest_20.log
+tail -5 gpurun_out/r02_gputest_20.log
+if [ $rc -ne 0 ]; then exit 0; fi
+B="timeout 200 python bench.py --steps 8 --warmup 3 --no-cpu-baseline"
+$B > gpurun_out/r02_ab_wdirect.json 2> gpurun_out/r02_ab_wdirect.err; echo "bench rc=$?"
+FDGS_LIB=$PWD/tools/_bin/libfdgs_wring.so $B > gpurun_out/r02_ab_wring.json 2> gpurun_out/r02_ab_wring.err; echo "bench0 rc=$?"
+FDGS_DW1_GZ_REBUILD=1 $B > gpurun_out/r02_ab_wdirect_gz.json 2> gpurun_out/r02_ab_wdirect_gz.err; echo "bench gz rc=$?"
+FDGS_DW1_GZ_REBUILD=1 timeout 150 python -m pytest tests/test_gpu_deform.py -m gpu -x -q > gpurun_out/r02_gputest_20gz.log 2>&1; tail -2 gpurun_out/r02_gputest_20gz.log
