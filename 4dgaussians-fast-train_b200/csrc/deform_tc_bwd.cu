@@ -1064,15 +1064,21 @@ k_deform_bwd_weights(WArgs args)
         // every pass and stage, so its column sums (bias gradients) stay in registers.
         constexpr int NI = 1024 / (NSW * 32);                        // float4s of A per thread per stage
         const int gprB = nblkB * 8;                                 // float4 groups per staged B row (8, 16 or 32)
+        // Bank conflicts: a 128-bit shared-memory access is served one quarter-warp (8 lanes) at a time, so the 8 lanes of a
+        // quarter must touch 8 different 16-byte bank groups in BOTH layouts.  Raw stage [col/4][32 rows][4]: the group is
+        // row % 8.  Swizzled tile32: the group is ((col/8 % 4) ^ (row % 4)) * 2 + (col/4 % 2).  Lanes 0-3 of a quarter take
+        // rows r..r+3 of column group cg, lanes 4-7 rows r+4..r+7 of column group cg ^ 1 (the neighbouring quarter does
+        // the opposite): conflict-free on both sides (8 rows of one column group made every tile store 2-way conflicted,
+        // 65 M of the kernel's 96 M shared-memory wavefronts, ncu).
         const int sub = lane >> 3, row8 = lane & 7;
         const int u0 = warp * 4 + sub;                              // 0 .. 4*NSW-1
-        const int cgA = u0 & 31;
+        const int cgA = (u0 & 31) ^ (row8 >> 2);
         int cgB, rowA[NI], rowB[NI];
         bool actB[NI];
 #pragma unroll
         for (int i = 0; i < NI; ++i) rowA[i] = ((i * (4 * NSW) + u0) >> 5) * 8 + row8;
         if (J.blkB) {
-            cgB = u0 % gprB;
+            cgB = (u0 % gprB) ^ (row8 >> 2);
 #pragma unroll
             for (int i = 0; i < NI; ++i) {
                 const int u = i * (4 * NSW) + u0;
@@ -1135,7 +1141,8 @@ k_deform_bwd_weights(WArgs args)
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&bars[WB_REMPTY + rslot]);
             }
-            // rows of a column group are spread over the 8 lanes of a quarter-warp and over warps w, w + 8
+            // rows of a column group are spread over 4 adjacent lanes (lanes 0-3 / 4-7 of a quarter-warp hold different
+            // column groups, see above) and over warps w, w + 8
 #pragma unroll
             for (int c = 0; c < 4; ++c)
 #pragma unroll
@@ -1143,7 +1150,6 @@ k_deform_bwd_weights(WArgs args)
                     float v = acc[c][o];
                     v += __shfl_xor_sync(0xffffffffu, v, 1);
                     v += __shfl_xor_sync(0xffffffffu, v, 2);
-                    v += __shfl_xor_sync(0xffffffffu, v, 4);
                     acc[c][o] = v;
                 }
             if (wantB) {          // warp-uniform condition: every lane takes part in the full-mask shuffles
@@ -1152,11 +1158,10 @@ k_deform_bwd_weights(WArgs args)
                     float v = sb[o];
                     v += __shfl_xor_sync(0xffffffffu, v, 1);
                     v += __shfl_xor_sync(0xffffffffu, v, 2);
-                    v += __shfl_xor_sync(0xffffffffu, v, 4);
-                    if (cgA == 0 && row8 == 0 && o < J.nb) atomicAdd(&csumB[o], v);
+                    if (cgA == 0 && (row8 & 3) == 0 && o < J.nb) atomicAdd(&csumB[o], v);
                 }
             }
-            if (row8 == 0 && onA) {
+            if ((row8 & 3) == 0 && onA) {
 #pragma unroll
                 for (int c = 0; c < 4; ++c)
 #pragma unroll
