@@ -26,6 +26,12 @@ namespace fdgs_deform_tc_bwd {
 using namespace fdgs_deform;
 using namespace fdgs_umma;
 
+// Saved-activation mode: the g_relu_h += g_z W1 GEMM of a head starts on the first column chunk of g_z while the epilogue
+// warps still produce the second one, and the next head's g_z goes into a chunk as soon as the tensor core has read it
+// (1: default; 0: one head at a time - epilogue and tensor core alternate - for A/B).
+#ifndef FDGS_BWD_PIPE
+#define FDGS_BWD_PIPE 1
+#endif
 constexpr int KCH = 16;            // K columns per streamed weight chunk
 constexpr int NTHREADS = 320;      // 8 sampler/epilogue warps + producer + MMA
 constexpr int NEPI = 256;
@@ -35,6 +41,7 @@ struct Plan {
     int heads[FDGS_NUM_HEADS];     // active heads that received an upstream gradient
     int nchunks_main;              // chunks of 32*Wn floats per tile: W0, then per head W1_j, W2_j^T (K padded to 16), W1_j^T
     int k2chunks[FDGS_NUM_HEADS];  // W2_j^T chunks of plan slot j: 1 (out <= 4) or 3 (out = 48)
+    int cc[FDGS_NUM_HEADS];        // plan slot j (saved mode, out <= 4): g_relu_z = g_o W2 on the CUDA cores, chunk-pipelined (below)
     int seq_n;                     // main chunks streamed per tile, in MMA order (all of them, or - when the forward kept
     short seq[112];                // the activations - only the W2_j^T and W1_j^T chunks)
     int nchunks_gf;                // chunks of 32*F floats (W0^T)
@@ -58,6 +65,8 @@ static inline Plan make_plan(const Layout& lo, int P, const bool has_grad[FDGS_N
         p.k2chunks[j] = j < p.nheads ? (head_out(p.heads[j]) + KCH - 1) / KCH : 0;
         p.nchunks_main += p.k2chunks[j];
     }
+    for (int j = 0; j < FDGS_NUM_HEADS; ++j)
+        p.cc[j] = (FDGS_BWD_PIPE && saved && j < p.nheads && head_out(p.heads[j]) <= 4) ? 1 : 0;
     p.nchunks_gf = lo.Wn / KCH;
     p.wprep_floats = (long long)p.nchunks_main * 32 * lo.Wn + (long long)p.nchunks_gf * 32 * lo.F;
     {
@@ -65,8 +74,18 @@ static inline Plan make_plan(const Layout& lo, int P, const bool has_grad[FDGS_N
         for (int k = 0; k < lo.F / KCH; ++k, ++c) if (!saved) p.seq[n++] = (short)c;                 // W0
         for (int j = 0; j < p.nheads; ++j) {
             for (int k = 0; k < lo.Wn / KCH; ++k, ++c) if (!saved) p.seq[n++] = (short)c;            // W1_j
-            for (int k = 0; k < p.k2chunks[j]; ++k, ++c) p.seq[n++] = (short)c;                      // W2_j^T
-            for (int k = 0; k < lo.Wn / KCH; ++k, ++c) p.seq[n++] = (short)c;                        // W1_j^T
+            for (int k = 0; k < p.k2chunks[j]; ++k, ++c) if (!p.cc[j]) p.seq[n++] = (short)c;        // W2_j^T
+            if (saved && FDGS_BWD_PIPE) {
+                // W1_j^T in the order the pipelined g_relu_h GEMM consumes it: the epilogue threads deliver g_z in two
+                // column chunks per half (thread = row, column half hf), so K chunk 0 = first half of both halves
+                const int nk = lo.Wn / KCH, hk = nk / 2, qk = hk / 2 > 0 ? hk / 2 : 1;
+                for (int ch = 0; ch < 2; ++ch)
+                    for (int hf = 0; hf < 2; ++hf)
+                        for (int k = 0; k < qk && ch * qk + k < hk; ++k) p.seq[n++] = (short)(c + hf * hk + ch * qk + k);
+                c += nk;
+            } else {
+                for (int k = 0; k < lo.Wn / KCH; ++k, ++c) p.seq[n++] = (short)c;                    // W1_j^T
+            }
         }
         p.seq_n = n;
     }
@@ -149,7 +168,7 @@ static inline Smem make_smem(const Layout& lo, bool saved = false) {
     // kept the activations only the g_feat staging tile remains
     s.off_hs_hi = o; o += al(128 * (saved ? lo.F : Wn));
     s.off_hs_lo = o; o += saved ? 0 : al(128 * Wn);
-    s.off_w2 = o;                              // (the output layers run on the tensor cores: no W2 copy)
+    s.off_w2 = o; o += (saved && FDGS_BWD_PIPE) ? al(4 * Wn * 4) : 0;   // W2 of the <= 4-output heads as [head][column][4]
     s.off_b0 = o; o += al(Wn);
     s.off_b1 = o; o += al(FDGS_NUM_HEADS * Wn);
     s.off_red = o; o += al(2 * 128 * 3);
@@ -169,7 +188,7 @@ __device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, 256;" ::: 
 #ifdef FDGS_PHASE_TIMING
 #define PT_DECL long long pt_[12] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0}; long long pt_t = clock64();
 #define PT(i) { const long long n_ = clock64(); pt_[i] += n_ - pt_t; pt_t = n_; }
-#define PT_PRINT if (blockIdx.x == 0 && tid == 0) printf("bwd_data phases (cycles, CTA0): sample %lld | wait_trunk %lld | trunk_epi %lld | wait_z %lld | head_epi %lld | wait_grh %lld | gh_epi %lld | wait_gf %lld | samp_bwd %lld | tail %lld\n", pt_[0], pt_[1], pt_[2], pt_[3], pt_[4], pt_[5], pt_[6], pt_[7], pt_[8], pt_[9]);
+#define PT_PRINT if (blockIdx.x == 0 && tid == 0) printf("bwd_data phases (cycles, CTA0): sample / chunk0 %lld | wait_trunk / wait_free1 %lld | trunk_epi %lld | wait_z / wait_free0 %lld | head_epi / chunk1 %lld | wait_grh %lld | gh_epi %lld | wait_gf %lld | samp_bwd %lld | tail %lld\n", pt_[0], pt_[1], pt_[2], pt_[3], pt_[4], pt_[5], pt_[6], pt_[7], pt_[8], pt_[9]);
 #else
 #define PT_DECL
 #define PT(i)
@@ -179,7 +198,8 @@ __device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, 256;" ::: 
 // TMEM column map (512 columns): accumulator (trunk h, head z, g_feat), g_z / g_h hi, lo, g_relu_h accumulator
 constexpr uint32_t TM_ACC = 0, TM_GHI = 128, TM_GLO = 256, TM_GRH = 384;
 constexpr int B_WFULL = 0, B_WEMPTY = 8, B_FEATFULL = 16, B_ACCFULL = 17, B_HFULL = 18, B_GZFULL = 19, B_GRHFULL = 20,
-              B_GHFULL = 21, B_GFFULL = 22, B_GOFULL = 23, B_COUNT = 24;
+              B_GHFULL = 21, B_GFFULL = 22, B_GOFULL = 23, B_GZFULL1 = 24, B_FREE1 = 25, B_COUNT = 26;
+// saved mode with FDGS_BWD_PIPE: g_z column chunk c full = B_GZFULL / B_GZFULL1, chunk c read by the tensor core = B_GRHFULL / B_FREE1
 
 __device__ __forceinline__ int w2_row0(int h) { return h == 0 ? 0 : h == 1 ? 3 : h == 2 ? 6 : h == 3 ? 10 : 11; }
 
@@ -547,6 +567,7 @@ k_deform_bwd_data(Layout lo, Plan plan, Smem sp, Net net, IO io, const float* __
     float* B0s = sm + sp.off_b0;
     float* B1s = sm + sp.off_b1;
     float* red = sm + sp.off_red;
+    float* W2s = sm + sp.off_w2;               // saved mode: W2 of the <= 4-output heads, [head][column][4]
     float* ring = sm + sp.off_ring;
     uint64_t* bars = reinterpret_cast<uint64_t*>(sm + sp.off_bars);
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + B_COUNT + 2);
@@ -570,6 +591,8 @@ k_deform_bwd_data(Layout lo, Plan plan, Smem sp, Net net, IO io, const float* __
             const int h = plan.heads[j];
             const int NO = head_out(h);
             for (int i = tid; i < WN; i += NEPI) B1s[h * WN + i] = net.b1[h][i];
+            if (plan.cc[j])                                  // W2 [NO][WN] -> [column][4] (zero padded)
+                for (int e = tid; e < WN * 4; e += NEPI) W2s[h * WN * 4 + e] = (e & 3) < NO ? net.w2[h][(e & 3) * WN + (e >> 2)] : 0.f;
         }
     }
     tc_fence_before();
@@ -604,10 +627,11 @@ k_deform_bwd_data(Layout lo, Plan plan, Smem sp, Net net, IO io, const float* __
             const uint32_t idesc_gf = make_idesc_tf32(128, F, 0, 0);
             const uint64_t s_hi0 = desc_kmajor(HS_hi, 128, 0), s_lo0 = desc_kmajor(HS_lo, 128, 0);   // feat aliases relu(h)
             const uint32_t ring_u = smem_addr(ring) >> 4;
-            uint32_t slot = 0, wph = 0, ph_feat = 0, ph_h = 0, ph_gz = 0, ph_gh = 0, ph_go = 0;
+            uint32_t slot = 0, wph = 0, ph_feat = 0, ph_h = 0, ph_gz = 0, ph_gz1 = 0, ph_gh = 0, ph_go = 0;
             // D[acc] (+)= A . B^T over `nck` streamed chunks (two 8-wide k-steps each, `ksteps` of them real) of an [N][K]
             // weight.  A: the shared-memory tile (ss) or TMEM columns ta_hi / ta_lo.  fresh: the first MMA overwrites D.
-            auto gemm = [&](uint32_t acc, int nck, int N, uint32_t id, bool ss, uint32_t ta_hi, uint32_t ta_lo, int ksteps, bool fresh) {
+            auto gemm = [&](uint32_t acc, int nck, int N, uint32_t id, bool ss, uint32_t ta_hi, uint32_t ta_lo, int ksteps, bool fresh,
+                            int kbase = 0) {       // kbase: first k-step (A operand column / 8) the streamed chunks refer to
                 const uint64_t bd0 = make_sdesc(0u, (uint32_t)N * 16u, 128u);
                 const uint32_t bstep = (uint32_t)N * 2u;
 #pragma unroll 1
@@ -620,7 +644,7 @@ k_deform_bwd_data(Layout lo, Plan plan, Smem sp, Net net, IO io, const float* __
 #pragma unroll
                         for (int ks = 0; ks < 2; ++ks) {
                             if (c * 2 + ks < ksteps) {
-                                const uint32_t kk = (uint32_t)(c * 2 + ks);
+                                const uint32_t kk = (uint32_t)(kbase + c * 2 + ks);
                                 const int first = (fresh && c == 0 && ks == 0) ? 0 : 1;
                                 const uint64_t dbh = dbh0 + ks * bstep, dbl = dbl0 + ks * bstep;
                                 if (ss) {
@@ -659,11 +683,28 @@ k_deform_bwd_data(Layout lo, Plan plan, Smem sp, Net net, IO io, const float* __
                         commit(B_ACCFULL);
                     }
                     // g_relu_z: ACC = g_o . W2       (A = g_o from TMEM, B = W2^T chunks, K padded to 8 / 48)
-                    mbar_wait(&bars[B_GOFULL], ph_go); ph_go ^= 1;
-                    tc_fence_after();
-                    gemm(tm + TM_ACC, plan.k2chunks[i], WN, idesc, false, tm + TM_GHI, tm + TM_GLO,
-                         head_out(plan.heads[i]) > 8 ? 6 : 1, true);
-                    commit(B_ACCFULL);
+                    if (!plan.cc[i]) {
+                        mbar_wait(&bars[B_GOFULL], ph_go); ph_go ^= 1;
+                        tc_fence_after();
+                        gemm(tm + TM_ACC, plan.k2chunks[i], WN, idesc, false, tm + TM_GHI, tm + TM_GLO,
+                             head_out(plan.heads[i]) > 8 ? 6 : 1, true);
+                        commit(B_ACCFULL);
+                    }
+                    if constexpr (SAVED && FDGS_BWD_PIPE) {
+                        // g_relu_h += g_z . W1 in two K chunks (column chunk ch of both column halves), each released to the
+                        // epilogue warps for the next head's g_z as soon as it has been read
+                        constexpr int HK = WN / KCH / 2, QK = HK / 2;
+#pragma unroll
+                        for (int ch = 0; ch < 2; ++ch) {
+                            mbar_wait(&bars[ch ? B_GZFULL1 : B_GZFULL], ch ? ph_gz1 : ph_gz);
+                            if (ch) ph_gz1 ^= 1; else ph_gz ^= 1;
+                            tc_fence_after();
+                            gemm(tm + TM_GRH, QK, WN, idesc, false, tm + TM_GHI, tm + TM_GLO, 1 << 20, i == 0 && ch == 0, (ch * QK) * 2);
+                            gemm(tm + TM_GRH, QK, WN, idesc, false, tm + TM_GHI, tm + TM_GLO, 1 << 20, false, (HK + ch * QK) * 2);
+                            commit(ch ? B_FREE1 : B_GRHFULL);
+                        }
+                        continue;
+                    }
                     // g_relu_h += g_z . W1          (A from TMEM, B = W1^T chunks)
                     mbar_wait(&bars[B_GZFULL], ph_gz); ph_gz ^= 1;
                     tc_fence_after();
@@ -683,7 +724,7 @@ k_deform_bwd_data(Layout lo, Plan plan, Smem sp, Net net, IO io, const float* __
         const int row = tid & 127, hf = tid >> 7;
         const uint32_t lane_base = tmem + ((uint32_t)((warp & 3) * 32) << 16);
         const int col0 = hf * NH;
-        uint32_t ph_acc = 0, ph_grh = 0, ph_gf = 0;
+        uint32_t ph_acc = 0, ph_grh = 0, ph_gf = 0, ph_free1 = 0;
         const int C = lo.C, CH = C >> 1;
         // sampler mapping (see below): LP lanes per point, IPT channel quads per lane, PPW points per warp
         const int items = F >> 2;
@@ -805,6 +846,84 @@ k_deform_bwd_data(Layout lo, Plan plan, Smem sp, Net net, IO io, const float* __
                 const size_t rowoff = (size_t)tile * TP * WN + (row >> 5) * 32 * WN + (row & 31) * 4;
                 float* gz_row = io.S_GZ[i] + rowoff;
                 uint32_t zgate[NH / 32 + 1];
+                if constexpr (SAVED && FDGS_BWD_PIPE) {
+                    const uint32_t* mp = io.V_M + ((size_t)(1 + h) * io.Pp + p) * 4 + hf * 2;
+                    zgate[0] = __ldcs(mp);
+                    if (NH > 32) zgate[1] = __ldcs(mp + 1);
+                    if (plan.cc[i]) {
+                        // ---- <= 4 outputs: g_z = (g_o W2)[z > 0] on the CUDA cores, delivered in two column chunks ---------
+                        // Chunk ch is written as soon as the tensor core has read the previous head's chunk ch, and the
+                        // g_relu_h GEMM starts on it while the second chunk is still being produced: epilogue and tensor
+                        // core overlap instead of taking turns.
+                        float go4[4] = {0.f, 0.f, 0.f, 0.f};
+                        if (valid) {
+#pragma unroll
+                            for (int o = 0; o < 4; ++o) if (o < NO) go4[o] = gsrc[o];
+                        }
+                        constexpr int CW = NH / 2;
+                        const float* w2h = W2s + (h * WN + col0) * 4;
+#pragma unroll
+                        for (int ch = 0; ch < 2; ++ch) {
+                            if (ch) { PT(0) }                           // (phase timing: chunk 0 produced)
+                            if (i > 0) {                                // the previous head's chunk ch has been read
+                                if (ch) { mbar_wait(&bars[B_FREE1], ph_free1); ph_free1 ^= 1; }
+                                else { mbar_wait(&bars[B_GRHFULL], ph_grh); ph_grh ^= 1; }
+                                tc_fence_after();
+                            }
+                            if (ch == 0) { PT(3) } else { PT(1) }       // (waits for the tensor core: chunk 0 / chunk 1)
+#pragma unroll
+                            for (int c0 = ch * CW; c0 < (ch + 1) * CW; c0 += 16) {
+                                uint32_t hi[16], lw[16];
+                                float g[16];
+                                const uint32_t m = zgate[c0 / 32] >> (c0 & 31);
+#pragma unroll
+                                for (int j = 0; j < 16; ++j) {
+                                    const float4 w = *reinterpret_cast<const float4*>(w2h + (c0 + j) * 4);
+                                    float acc = go4[0] * w.x;
+                                    acc = fmaf(go4[1], w.y, acc); acc = fmaf(go4[2], w.z, acc); acc = fmaf(go4[3], w.w, acc);
+                                    g[j] = ((m >> j) & 1u) ? acc : 0.f;
+                                    float a, b;
+                                    split_tf32_rn(g[j], a, b);
+                                    hi[j] = __float_as_uint(a); lw[j] = __float_as_uint(b);
+                                }
+                                if (gz_row) {
+#pragma unroll
+                                    for (int j = 0; j < 16; j += 4)
+                                        __stcs(reinterpret_cast<float4*>(gz_row + ((col0 + c0 + j) >> 2) * 128), make_float4(g[j], g[j + 1], g[j + 2], g[j + 3]));
+                                }
+                                tmem_st16(lane_base + TM_GHI + col0 + c0, hi);
+                                tmem_st16(lane_base + TM_GLO + col0 + c0, lw);
+                            }
+                            tmem_wait_st();
+                            tc_fence_before();
+                            epi_bar();
+                            if (tid == 0) mbar_arrive(&bars[ch ? B_GZFULL1 : B_GZFULL]);
+                        }
+                        PT(4)
+                        continue;
+                    }
+                    // ---- 48 outputs: g_o W2 on the tensor core; needs the whole g_z buffer (g_o is staged in its head) --------
+                    float gox[24];
+                    go_load(gox, hf, NO, valid, gsrc);
+                    if (i > 0) {
+                        mbar_wait(&bars[B_GRHFULL], ph_grh); ph_grh ^= 1;
+                        mbar_wait(&bars[B_FREE1], ph_free1); ph_free1 ^= 1;
+                        tc_fence_after();
+                    }
+                    PT(3)
+                    go_store(lane_base, hf, NO, gox);
+                    tc_fence_before();
+                    epi_bar();
+                    if (tid == 0) mbar_arrive(&bars[B_GOFULL]);
+                    mbar_wait(&bars[B_ACCFULL], ph_acc); ph_acc ^= 1;  // accumulator = g_o . W2
+                    tc_fence_after();
+                    head_pass2<NH>(lane_base, col0, gz_row, zgate);
+                    tc_fence_before();
+                    epi_bar();
+                    if (tid == 0) { mbar_arrive(&bars[B_GZFULL]); mbar_arrive(&bars[B_GZFULL1]); }
+                    PT(4)
+                    continue;
+                }
                 float gox[24];
                 go_load(gox, hf, NO, valid, gsrc);
                 if constexpr (SAVED) {
@@ -838,6 +957,7 @@ k_deform_bwd_data(Layout lo, Plan plan, Smem sp, Net net, IO io, const float* __
 
             // ---- g_h = g_relu_h [h > 0] -> scratch, TMEM hi / lo -----------------------------------------------------
             mbar_wait(&bars[B_GRHFULL], ph_grh); ph_grh ^= 1;
+            if constexpr (SAVED && FDGS_BWD_PIPE) { mbar_wait(&bars[B_FREE1], ph_free1); ph_free1 ^= 1; }   // last head's second chunk
             tc_fence_after();
             PT(5)
 #pragma unroll
