@@ -376,9 +376,11 @@ __device__ __forceinline__ void gate_from_saved(const float* __restrict__ row, i
 
 // ---- pass 2: g_z = (g_o W2)[z > 0] (accumulator) -> scratch, hi/lo -> TMEM (A operand of g_relu_h += g_z W1) -----------
 template <int NH>
-__device__ __forceinline__ void head_pass2(uint32_t lane_base, int col0, float* __restrict__ gz_row, const uint32_t (&zgate)[NH / 32 + 1]) {
+__device__ __forceinline__ void head_pass2(uint32_t lane_base, int col0, float* __restrict__ gz_row, const uint32_t (&zgate)[NH / 32 + 1],
+                                           int cb = 0, int ce = NH) {          // columns [cb, ce) of this thread's NH
 #pragma unroll
     for (int c0 = 0; c0 < NH; c0 += 16) {
+        if (c0 < cb || c0 >= ce) continue;
         uint32_t v[16], hi[16], lw[16];
         tmem_ld16(lane_base + TM_ACC + col0 + c0, v);
         tmem_wait_ld();
@@ -917,10 +919,14 @@ k_deform_bwd_data(Layout lo, Plan plan, Smem sp, Net net, IO io, const float* __
                     if (tid == 0) mbar_arrive(&bars[B_GOFULL]);
                     mbar_wait(&bars[B_ACCFULL], ph_acc); ph_acc ^= 1;  // accumulator = g_o . W2
                     tc_fence_after();
-                    head_pass2<NH>(lane_base, col0, gz_row, zgate);
+                    head_pass2<NH>(lane_base, col0, gz_row, zgate, 0, NH / 2);          // chunk 0: the GEMM starts on it
                     tc_fence_before();
                     epi_bar();
-                    if (tid == 0) { mbar_arrive(&bars[B_GZFULL]); mbar_arrive(&bars[B_GZFULL1]); }
+                    if (tid == 0) mbar_arrive(&bars[B_GZFULL]);
+                    head_pass2<NH>(lane_base, col0, gz_row, zgate, NH / 2, NH);
+                    tc_fence_before();
+                    epi_bar();
+                    if (tid == 0) mbar_arrive(&bars[B_GZFULL1]);
                     PT(4)
                     continue;
                 }
