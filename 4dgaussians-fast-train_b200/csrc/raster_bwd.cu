@@ -672,15 +672,15 @@ k_preprocess_bwd(int P, int D, int M, const float* __restrict__ means3D, const i
     const long long base = (long long)blockIdx.x * blockDim.x * rowf;
     const long long avail = (long long)P * rowf - base;
     const int n = (int)(avail < (long long)blockDim.x * rowf ? avail : (long long)blockDim.x * rowf);
+    constexpr int RF = 48;                       // sh_staged implies M == 16: a compile-time row length keeps the index
+                                                 // arithmetic below free of integer divisions (8 per float4 before)
     if (sh_staged) {
         const float4* src = reinterpret_cast<const float4*>(shs + base);
         for (int i = threadIdx.x; i * 4 < n; i += blockDim.x) {
             const float4 v = src[i];
-            const int e = i * 4;
-            s_sh[(e / rowf) * (rowf + 1) + e % rowf] = v.x;
-            s_sh[((e + 1) / rowf) * (rowf + 1) + (e + 1) % rowf] = v.y;
-            s_sh[((e + 2) / rowf) * (rowf + 1) + (e + 2) % rowf] = v.z;
-            s_sh[((e + 3) / rowf) * (rowf + 1) + (e + 3) % rowf] = v.w;
+            const int r = i / (RF / 4), c = (i - r * (RF / 4)) * 4;      // a float4 never straddles two rows (RF % 4 == 0)
+            float* d = s_sh + r * (RF + 1) + c;
+            d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
         }
     }
     __syncthreads();
@@ -693,9 +693,9 @@ k_preprocess_bwd(int P, int D, int M, const float* __restrict__ means3D, const i
         __syncthreads();
         float4* dst = reinterpret_cast<float4*>(dL_dsh + base);
         for (int i = threadIdx.x; i * 4 < n; i += blockDim.x) {
-            const int e = i * 4;
-            dst[i] = make_float4(s_sh[(e / rowf) * (rowf + 1) + e % rowf], s_sh[((e + 1) / rowf) * (rowf + 1) + (e + 1) % rowf],
-                                 s_sh[((e + 2) / rowf) * (rowf + 1) + (e + 2) % rowf], s_sh[((e + 3) / rowf) * (rowf + 1) + (e + 3) % rowf]);
+            const int r = i / (RF / 4), c = (i - r * (RF / 4)) * 4;
+            const float* d = s_sh + r * (RF + 1) + c;
+            dst[i] = make_float4(d[0], d[1], d[2], d[3]);
         }
     }
 }

@@ -72,11 +72,10 @@ k_preprocess(int P, int D, int M,
         const float4* src = reinterpret_cast<const float4*>(shs + base);          // base is a multiple of 4 floats
         for (int i = threadIdx.x; i * 4 < n; i += blockDim.x) {
             const float4 v = src[i];                                              // n is a multiple of 4 (rowf = 48)
-            const int e = i * 4;
-            s_sh[(e / rowf) * (rowf + 1) + e % rowf] = v.x;
-            s_sh[((e + 1) / rowf) * (rowf + 1) + (e + 1) % rowf] = v.y;
-            s_sh[((e + 2) / rowf) * (rowf + 1) + (e + 2) % rowf] = v.z;
-            s_sh[((e + 3) / rowf) * (rowf + 1) + (e + 3) % rowf] = v.w;
+            constexpr int RF = 48;               // sh_staged implies M == 16: compile-time row length, no integer divisions
+            const int r = i / (RF / 4), c = (i - r * (RF / 4)) * 4;              // a float4 never straddles two rows
+            float* d = s_sh + r * (RF + 1) + c;
+            d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
         }
     }
     __syncthreads();
