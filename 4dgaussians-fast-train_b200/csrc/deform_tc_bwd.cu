@@ -1513,7 +1513,11 @@ int backward(const Layout& lo, const FdgsDeformBackward* a, const float* packed,
     // per-stage cost of a CUDA-core dW2 job relative to a tensor-core dW1 job (FDGS_DW2_COST overrides, for tuning)
     // measured (cycles per 32-point stage, FDGS_PHASE_TIMING): dW1 1718, dW2 on the CUDA cores 889 (HBM-bound: ~1000 when all four
     // such jobs stream at once), dW2 (shs) 1543, dW0 1455
-    const double cc_cost = getenv("FDGS_DW2_COST") ? atof(getenv("FDGS_DW2_COST")) : 0.65;
+    double cc_cost = getenv("FDGS_DW2_COST") ? atof(getenv("FDGS_DW2_COST")) : 0.65, shs_cost = 0.90, dw0_cost = 0.85;
+    if (const char* e = getenv("FDGS_W_COSTS")) {            // "cc,shs,dw0" relative to a dW1 job (tuning)
+        double a_ = 0, b_ = 0, c_ = 0;
+        if (sscanf(e, "%lf,%lf,%lf", &a_, &b_, &c_) == 3 && a_ > 0 && b_ > 0 && c_ > 0) { cc_cost = a_; shs_cost = b_; dw0_cost = c_; }
+    }
     for (int j = 0; j < plan.nheads; ++j) {
         const int h = plan.heads[j];
         const int NO = head_out(h);
@@ -1521,10 +1525,10 @@ int backward(const Layout& lo, const FdgsDeformBackward* a, const float* packed,
         cost[nj++] = 1.0;                                 // relative per-stage cost, measured (cycles/stage 1750 : 2050 : 1530)
         const int cc = (NO <= 4 && !getenv("FDGS_DW2_TENSOR")) ? 1 : 0;
         wa.j[nj] = WJob{io.S_RZ[j], Wn, Wn, (int)plan.Pp, gsrc[h], NO, NO, a->P, a->d_head_w2[h], Wn, 1, nullptr, a->d_head_b2[h], 1, 1, 0, cc};
-        cost[nj++] = cc ? cc_cost : 0.90;
+        cost[nj++] = cc ? cc_cost : shs_cost;
     }
     wa.j[nj] = WJob{io.S_GH, Wn, Wn, (int)plan.Pp, io.S_F, F, F, (int)plan.Pp, a->d_trunk_w[0], F, 0, a->d_trunk_b[0], nullptr, 1, 1, 1, 0};
-    cost[nj++] = 0.85;
+    cost[nj++] = dw0_cost;
     wa.njobs = nj; wa.rows = plan.Pp;
     // distribute the SMs over the jobs in proportion to the bytes they stream
     double tot = 0; for (int i = 0; i < nj; ++i) tot += cost[i];
