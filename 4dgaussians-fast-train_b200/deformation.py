@@ -281,6 +281,24 @@ class Deformation(nn.Module):
     def _trunk_linears(self):
         return [m for m in self.feature_out if isinstance(m, nn.Linear)]
 
+    def _flat(self):
+        """(planes[l][k], [(trunk w, b)], [(head w1, b1, w2, b2)]) - the Parameter objects the kernels read, looked up once:
+        the module structure is static, and walking ModuleList / Sequential / nn.Module.__getattr__ on every call was a
+        measurable part of the host time per view (hundreds of attribute look-ups).  Re-derived if a parameter object was
+        replaced (two identity checks)."""
+        c = self.__dict__.get("_flat_cache")
+        if c is not None and c[0][0][0] is self.grid.grids[0][0] and c[2][0][0] is getattr(self, HEADS[0])[1].weight:
+            return c
+        planes = [[p for p in pl] for pl in self.grid.grids]
+        trunk = [(lin.weight, lin.bias) for lin in self._trunk_linears()]
+        heads = []
+        for name in HEADS:
+            seq = getattr(self, name)
+            heads.append((seq[1].weight, seq[1].bias, seq[3].weight, seq[3].bias))
+        c = (planes, trunk, heads)
+        self.__dict__["_flat_cache"] = c
+        return c
+
     def _fill_net(self, net):
         """Fills an FdgsDeformNet with shapes and raw device pointers; returns tensors to keep alive."""
         keep = []
@@ -296,28 +314,27 @@ class Deformation(nn.Module):
                 net.res[l][i] = int(res[i])
         for i, v in enumerate(g.aabb_host()):
             net.aabb[i] = v
-        for l, planes in enumerate(g.grids):
+        planes_f, trunk_f, heads_f = self._flat()
+
+        def ptr(p):                      # a Parameter is normally contiguous: its own storage, nothing to keep alive
+            if p.is_contiguous():
+                return p.data_ptr()
+            t = p.detach().contiguous()
+            keep.append(t)
+            return t.data_ptr()
+
+        for l, planes in enumerate(planes_f):
             for k, p in enumerate(planes):
-                t = p.detach()
-                if not t.is_contiguous():
-                    t = t.contiguous()
-                keep.append(t)
-                net.planes[l][k] = t.data_ptr()
-        for d, lin in enumerate(self._trunk_linears()):
-            w, b = lin.weight.detach().contiguous(), lin.bias.detach().contiguous()
-            keep += [w, b]
-            net.trunk_w[d], net.trunk_b[d] = w.data_ptr(), b.data_ptr()
-        for h, name in enumerate(HEADS):
-            seq = getattr(self, name)
-            w1, b1 = seq[1].weight.detach().contiguous(), seq[1].bias.detach().contiguous()
-            w2, b2 = seq[3].weight.detach().contiguous(), seq[3].bias.detach().contiguous()
-            keep += [w1, b1, w2, b2]
-            net.head_w1[h], net.head_b1[h] = w1.data_ptr(), b1.data_ptr()
-            net.head_w2[h], net.head_b2[h] = w2.data_ptr(), b2.data_ptr()
+                net.planes[l][k] = ptr(p)
+        for d, (w, b) in enumerate(trunk_f):
+            net.trunk_w[d], net.trunk_b[d] = ptr(w), ptr(b)
+        for h, (w1, b1, w2, b2) in enumerate(heads_f):
+            net.head_w1[h], net.head_b1[h] = ptr(w1), ptr(b1)
+            net.head_w2[h], net.head_b2[h] = ptr(w2), ptr(b2)
         return keep
 
     def _plane_key(self):
-        return tuple((p.data_ptr(), p._version) for planes in self.grid.grids for p in planes)
+        return tuple((p.data_ptr(), p._version) for planes in self._flat()[0] for p in planes)
 
     def _packed_planes(self, lib, net):
         """Channel-last copy of the planes, rebuilt only when a plane parameter changed."""
@@ -360,13 +377,14 @@ class Deformation(nn.Module):
 
     def _param_list(self):
         """Parameters that receive gradients, in the order `_alloc_param_grads` returns them."""
-        ps = [p for planes in self.grid.grids for p in planes]
-        for lin in self._trunk_linears():
-            ps += [lin.weight, lin.bias]
-        for h, name in enumerate(HEADS):
-            if (self.head_mask >> h) & 1:
-                seq = getattr(self, name)
-                ps += [seq[1].weight, seq[1].bias, seq[3].weight, seq[3].bias]
+        planes_f, trunk_f, heads_f = self._flat()
+        ps = [p for planes in planes_f for p in planes]
+        for w, b in trunk_f:
+            ps += [w, b]
+        hm = self.head_mask
+        for h, hp in enumerate(heads_f):
+            if (hm >> h) & 1:
+                ps += list(hp)
         return ps
 
     def _alloc_param_grads(self, a, g):
@@ -385,16 +403,17 @@ class Deformation(nn.Module):
             grads.append(t)
             return t.data_ptr()
 
-        for l, planes in enumerate(self.grid.grids):
+        planes_f, trunk_f, heads_f = self._flat()
+        for l, planes in enumerate(planes_f):
             for k, p in enumerate(planes):
                 a.d_planes[l][k] = buf(p)
-        for d, lin in enumerate(self._trunk_linears()):
-            a.d_trunk_w[d], a.d_trunk_b[d] = buf(lin.weight), buf(lin.bias)
-        for h, name in enumerate(HEADS):
-            if (self.head_mask >> h) & 1:
-                seq = getattr(self, name)
-                a.d_head_w1[h], a.d_head_b1[h] = buf(seq[1].weight), buf(seq[1].bias)
-                a.d_head_w2[h], a.d_head_b2[h] = buf(seq[3].weight), buf(seq[3].bias)
+        for d, (w, b) in enumerate(trunk_f):
+            a.d_trunk_w[d], a.d_trunk_b[d] = buf(w), buf(b)
+        hm = self.head_mask
+        for h, (w1, b1, w2, b2) in enumerate(heads_f):
+            if (hm >> h) & 1:
+                a.d_head_w1[h], a.d_head_b1[h] = buf(w1), buf(b1)
+                a.d_head_w2[h], a.d_head_b2[h] = buf(w2), buf(b2)
         return grads
 
     # ---- reference API ------------------------------------------------------------------------
