@@ -22,7 +22,7 @@ class _FusedActivations(torch.autograd.Function):
         s, r, o = torch.empty_like(s_raw), torch.empty_like(r_raw), torch.empty_like(o_raw)
         a = L.FdgsActivateForward(P=s_raw.shape[0], scales_raw=L.ptr(s_raw), rotations_raw=L.ptr(r_raw), opacity_raw=L.ptr(o_raw),
                                   scales=L.ptr(s), rotations=L.ptr(r), opacity=L.ptr(o))
-        L.check(lib.fdgs_activate_forward(C.byref(a), C.c_void_p(torch.cuda.current_stream().cuda_stream)), "fdgs_activate_forward")
+        L.check(lib.fdgs_activate_forward(C.byref(a), L.stream_ptr()), "fdgs_activate_forward")
         ctx.save_for_backward(r_raw, s, r, o)
         for t, need in zip((s, r, o), ctx.needs_input_grad):
             if not need:
@@ -43,7 +43,7 @@ class _FusedActivations(torch.autograd.Function):
         a = L.FdgsActivateBackward(P=s.shape[0], rotations_raw=L.ptr(r_raw), scales=L.ptr(s), rotations=L.ptr(r), opacity=L.ptr(o),
                                    g_scales=L.ptr(g_s), g_rotations=L.ptr(g_r), g_opacity=L.ptr(g_o),
                                    d_scales_raw=L.ptr(d_s), d_rotations_raw=L.ptr(d_r), d_opacity_raw=L.ptr(d_o))
-        L.check(lib.fdgs_activate_backward(C.byref(a), C.c_void_p(torch.cuda.current_stream().cuda_stream)), "fdgs_activate_backward")
+        L.check(lib.fdgs_activate_backward(C.byref(a), L.stream_ptr()), "fdgs_activate_backward")
         return d_s, d_r, d_o
 
 

@@ -112,7 +112,7 @@ class _DeformFunction(torch.autograd.Function):
                 torch.empty((P, 4), **f) if (hm >> 2) & 1 else None,
                 torch.empty((P, 1), **f) if (hm >> 3) & 1 else None,
                 torch.empty((P, 16, 3), **f) if (hm >> 4) & 1 else None]
-        with torch.cuda.device(dev):
+        with L.on_device(dev):
             a = L.FdgsDeformForward()
             keep = net_mod._fill_net(a.net)
             a.P = P
@@ -137,7 +137,7 @@ class _DeformFunction(torch.autograd.Function):
                     saved = torch.empty((nsave,), dtype=torch.uint8, device=dev)
                     a.save_ws, a.save_bytes = saved.data_ptr(), saved.numel()
             a.debug = 0
-            L.check(lib.fdgs_deform_forward(C.byref(a), C.c_void_p(torch.cuda.current_stream().cuda_stream)),
+            L.check(lib.fdgs_deform_forward(C.byref(a), L.stream_ptr()),
                     "fdgs_deform_forward")
             net_mod._mark_packed_valid()
             del keep
@@ -184,7 +184,7 @@ class _DeformFunction(torch.autograd.Function):
         sink = getattr(mod, "identity_sink", None)
         if sink is not None and not mod.args.apply_rotation and ctx.sh_coeffs == 16:
             consumed = sink(g) or ()
-        with torch.cuda.device(dev):
+        with L.on_device(dev):
             a = L.FdgsDeformBackward()
             keep = mod._fill_net(a.net)
             a.P = P
@@ -205,7 +205,7 @@ class _DeformFunction(torch.autograd.Function):
             if ctx.saved_act is not None and scratch is not None:
                 a.saved_ws, a.saved_bytes = ctx.saved_act.data_ptr(), ctx.saved_act.numel()
             a.debug = 0
-            L.check(lib.fdgs_deform_backward(C.byref(a), C.c_void_p(torch.cuda.current_stream().cuda_stream)),
+            L.check(lib.fdgs_deform_backward(C.byref(a), L.stream_ptr()),
                     "fdgs_deform_backward")
             ctx.saved_act = None      # stream-ordered: the caching allocator may hand the block out again
             del keep
@@ -300,7 +300,25 @@ class Deformation(nn.Module):
         return c
 
     def _fill_net(self, net):
-        """Fills an FdgsDeformNet with shapes and raw device pointers; returns tensors to keep alive."""
+        """Fills an FdgsDeformNet with shapes and raw device pointers; returns tensors to keep alive.
+        The filled block is cached and copied (one memmove) while the parameters' storage, the aabb and the head flags are
+        unchanged: writing ~60 fields of nested ctypes arrays one by one took ~80 us per call, twice per view."""
+        planes_f, trunk_f, heads_f = self._flat()
+        flat = [p for pl in planes_f for p in pl] + [p for wb in trunk_f for p in wb] + [p for hp in heads_f for p in hp]
+        g = self.grid
+        aabb = g.aabb_host()
+        key = (tuple(p.data_ptr() for p in flat), tuple(aabb), self.head_mask, bool(self.args.apply_rotation), self.W, self.D)
+        cached = self.__dict__.get("_net_cache")
+        if cached is not None and cached[0] == key:
+            C.memmove(C.addressof(net), cached[1], C.sizeof(net))
+            return []
+        keep = self._fill_net_fields(net)
+        if not keep and all(p.is_contiguous() for p in flat):
+            # kept as bytes: a ctypes block with pointer fields would make the module un-picklable / un-deepcopy-able
+            self.__dict__["_net_cache"] = (key, C.string_at(C.addressof(net), C.sizeof(net)))
+        return keep
+
+    def _fill_net_fields(self, net):
         keep = []
         g = self.grid
         net.levels = len(g.grids)

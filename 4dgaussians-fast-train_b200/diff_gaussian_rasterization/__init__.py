@@ -132,7 +132,7 @@ def _f32(t, name, device):
 
 
 def _stream():
-    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    return L.stream_ptr()
 
 
 class _Workspaces:
@@ -153,7 +153,7 @@ def _forward_native(bg, means3D, colors_precomp, opacities, scales, rotations, s
     dev = means3D.device
     P = means3D.size(0)
     H, W = int(image_height), int(image_width)
-    with torch.cuda.device(dev):
+    with L.on_device(dev):
         color = torch.empty((3, H, W), dtype=torch.float32, device=dev)
         depth = torch.empty((1, H, W), dtype=torch.float32, device=dev)
         radii = torch.empty((P,), dtype=torch.int32, device=dev)
@@ -250,7 +250,7 @@ def count_pairs(render_fn, cam, pc, bg):
         _keep_last = False
         _last_ws = None
     counts = torch.zeros(2, dtype=torch.int64, device=img.device)
-    with torch.cuda.device(img.device):
+    with L.on_device(img.device):
         L.check(lib.fdgs_raster_count_pairs(img.data_ptr(), binb.data_ptr() if binb.numel() else None, int(R), W, H,
                                             counts.data_ptr(), _stream()), "fdgs_raster_count_pairs")
     c = counts.cpu().tolist()
@@ -286,7 +286,7 @@ def _backward_native(bg, means3D, radii, colors_precomp, scales, rotations, scal
     P = means3D.size(0)
     H, W = grad_out_color.size(1), grad_out_color.size(2)
     M = sh.size(1) if (sh is not None and sh.numel() != 0 and sh.dim() >= 2 and sh.size(0) != 0) else 0
-    with torch.cuda.device(dev):
+    with L.on_device(dev):
         f = dict(dtype=torch.float32, device=dev)
         dL_dmeans3D = torch.empty((P, 3), **f)
         dL_dmeans2D = torch.empty((P, 3), **f)
@@ -329,7 +329,7 @@ def _mark_visible(positions, viewmatrix, projmatrix):
     P = positions.size(0)
     present = torch.zeros((P,), dtype=torch.bool, device=positions.device)
     if P != 0:
-        with torch.cuda.device(positions.device):
+        with L.on_device(positions.device):
             pos = _f32(positions, "positions", positions.device)
             vm = _f32(viewmatrix, "viewmatrix", positions.device)
             pm = _f32(projmatrix, "projmatrix", positions.device)

@@ -30,9 +30,9 @@ def distCUDA2(points):
     if P == 0:
         return out
     ws = torch.empty((lib.fdgs_knn_ws_bytes(P),), dtype=torch.uint8, device=pts.device)
-    with torch.cuda.device(pts.device):
+    with L.on_device(pts.device):
         L.check(lib.fdgs_knn_mean_dist2(P, pts.data_ptr(), out.data_ptr(), ws.data_ptr(), ws.numel(),
-                                        C.c_void_p(torch.cuda.current_stream().cuda_stream)), "fdgs_knn_mean_dist2")
+                                        L.stream_ptr()), "fdgs_knn_mean_dist2")
     return out
 
 
@@ -50,10 +50,10 @@ def voxel_downsample(points, colors, voxel_size):
     n_out = torch.zeros((1,), dtype=torch.int32, device=dev)
     if P:
         ws = torch.empty((lib.fdgs_voxel_downsample_ws_bytes(P),), dtype=torch.uint8, device=dev)
-        with torch.cuda.device(dev):
+        with L.on_device(dev):
             L.check(lib.fdgs_voxel_downsample(P, pts.data_ptr(), L.ptr(cols), float(voxel_size), out_p.data_ptr(), L.ptr(out_c), P,
                                               n_out.data_ptr(), ws.data_ptr(), ws.numel(),
-                                              C.c_void_p(torch.cuda.current_stream().cuda_stream)), "fdgs_voxel_downsample")
+                                              L.stream_ptr()), "fdgs_voxel_downsample")
     V = int(n_out.item())
     out_p = out_p[:V]
     order = torch.arange(V, device=dev)

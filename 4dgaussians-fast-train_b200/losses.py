@@ -17,7 +17,7 @@ class _L1Loss(torch.autograd.Function):
         a_c, b_c = a.contiguous(), b.contiguous()
         loss = torch.zeros((), dtype=torch.float32, device=a.device)
         L.check(lib.fdgs_l1_loss_forward(L.ptr(a_c), L.ptr(b_c), a_c.numel(), float(scale), loss.data_ptr(),
-                                         C.c_void_p(torch.cuda.current_stream().cuda_stream)), "fdgs_l1_loss_forward")
+                                         L.stream_ptr()), "fdgs_l1_loss_forward")
         ctx.save_for_backward(a_c, b_c)
         ctx.scale = float(scale)
         return loss
@@ -29,7 +29,7 @@ class _L1Loss(torch.autograd.Function):
         g = g.contiguous().to(torch.float32)
         d_a = torch.empty_like(a_c)
         L.check(lib.fdgs_l1_loss_backward(L.ptr(a_c), L.ptr(b_c), a_c.numel(), ctx.scale, g.data_ptr(), d_a.data_ptr(),
-                                          C.c_void_p(torch.cuda.current_stream().cuda_stream)), "fdgs_l1_loss_backward")
+                                          L.stream_ptr()), "fdgs_l1_loss_backward")
         d_b = -d_a if ctx.needs_input_grad[1] else None
         return d_a, d_b, None
 

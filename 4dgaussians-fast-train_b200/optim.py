@@ -71,8 +71,8 @@ class FusedAdam(torch.optim.Optimizer):
                 t.exp_avg, t.exp_avg_sq = st["exp_avg"].data_ptr(), st["exp_avg_sq"].data_ptr()
                 t.n, t.lr, t.step = p.numel(), lr, int(st["step"])
             a = L.FdgsAdamStep(ntensors=len(items), zero_grad=int(bool(zero_grad)), beta1=b1, beta2=b2, eps=eps, t=arr)
-            with torch.cuda.device(dev):
-                L.check(lib.fdgs_adam_step(C.byref(a), C.c_void_p(torch.cuda.current_stream().cuda_stream)), "fdgs_adam_step")
+            with L.on_device(dev):
+                L.check(lib.fdgs_adam_step(C.byref(a), L.stream_ptr()), "fdgs_adam_step")
         return loss
 
 
@@ -98,7 +98,7 @@ def add_densification_stats(radii, viewspace_grad, max_radii2D=None, xyz_gradien
     vis = None
     if visibility is not None:
         vis = visibility.contiguous().view(torch.uint8) if visibility.dtype == torch.bool else visibility.to(torch.uint8).contiguous()
-    with torch.cuda.device(radii.device):
+    with L.on_device(radii.device):
         L.check(lib.fdgs_densify_stats(int(P), radii.data_ptr(), L.ptr(vis), L.ptr(vg), L.ptr(max_radii2D),
                                        L.ptr(xyz_gradient_accum), L.ptr(denom),
-                                       C.c_void_p(torch.cuda.current_stream().cuda_stream)), "fdgs_densify_stats")
+                                       L.stream_ptr()), "fdgs_densify_stats")

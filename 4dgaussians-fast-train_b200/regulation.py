@@ -70,8 +70,8 @@ def _launch(grids, weights, grad_ptrs, loss, grad_scale=None):
     a.grad_scale = grad_scale.data_ptr() if grad_scale is not None else None
     a.loss = loss.data_ptr() if loss is not None else None
     dev = grids[0][0].device
-    with torch.cuda.device(dev):
-        L.check(lib.fdgs_plane_regulation(C.byref(a), C.c_void_p(torch.cuda.current_stream().cuda_stream)),
+    with L.on_device(dev):
+        L.check(lib.fdgs_plane_regulation(C.byref(a), L.stream_ptr()),
                 "fdgs_plane_regulation")
     del keep
 
@@ -126,10 +126,10 @@ class _PlaneSmoothness(torch.autograd.Function):
         B, Cc, H, W = tc.shape
         loss = torch.zeros((), dtype=torch.float32, device=t.device)
         grad = torch.zeros_like(tc) if ctx.needs_input_grad[0] else None
-        with torch.cuda.device(t.device):
+        with L.on_device(t.device):
             L.check(lib.fdgs_plane_smoothness(tc.data_ptr(), grad.data_ptr() if grad is not None else None, int(B * Cc), int(H),
                                               int(W), 1.0, None, loss.data_ptr(),
-                                              C.c_void_p(torch.cuda.current_stream().cuda_stream)), "fdgs_plane_smoothness")
+                                              L.stream_ptr()), "fdgs_plane_smoothness")
         ctx.grad = grad
         return loss
 

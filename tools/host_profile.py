@@ -31,7 +31,12 @@ for rep in range(3):
     print(f"views {a.views}: host queued everything after {1e3 * (t1 - t0):.2f} ms; GPU span {e0.elapsed_time(e1):.2f} ms; wall to idle {1e3 * (t2 - t0):.2f} ms")
 pr = cProfile.Profile()
 torch.cuda.synchronize()
-pr.enable(); step(); pr.disable()
-torch.cuda.synchronize()
-s = io.StringIO(); pstats.Stats(pr, stream=s).sort_stats("cumulative").print_stats(45); print(s.getvalue()[:9000])
-s = io.StringIO(); pstats.Stats(pr, stream=s).sort_stats("tottime").print_stats(25); print(s.getvalue()[:6000])
+N = 100                                  # pstats prints milliseconds: profile N iterations so that per-call costs show
+pr.enable()
+for _ in range(N):
+    step()
+    torch.cuda.synchronize()             # (outside the per-function times that matter: it is its own entry)
+pr.disable()
+print(f"cProfile over {N} iterations of {a.views} view(s): divide the times by {N}")
+s = io.StringIO(); pstats.Stats(pr, stream=s).sort_stats("cumulative").print_stats(50); print(s.getvalue()[:11000])
+s = io.StringIO(); pstats.Stats(pr, stream=s).sort_stats("tottime").print_stats(40); print(s.getvalue()[:9000])
