@@ -32,6 +32,7 @@ using namespace fdgs_umma;
 #ifndef FDGS_BWD_PIPE
 #define FDGS_BWD_PIPE 1
 #endif
+constexpr int WACC_CTAS = 192;     // weight kernel: CTAs that can have a private accumulation buffer (>= SMs of the device)
 constexpr int KCH = 16;            // K columns per streamed weight chunk
 constexpr int NTHREADS = 320;      // 8 sampler/epilogue warps + producer + MMA
 constexpr int NEPI = 256;
@@ -48,7 +49,7 @@ struct Plan {
     long long wprep_floats;
     // scratch (floats), Pp = ntiles * 128 rows each
     long long Pp;
-    long long off_wprep, off_F, off_H, off_GH, off_GF, off_RZ[FDGS_NUM_HEADS], off_GZ[FDGS_NUM_HEADS], total_floats;
+    long long off_wprep, off_F, off_H, off_GH, off_GF, off_RZ[FDGS_NUM_HEADS], off_GZ[FDGS_NUM_HEADS], off_wacc, total_floats;
 };
 
 static inline bool tc_supported(const Layout& lo) {
@@ -102,6 +103,7 @@ static inline Plan make_plan(const Layout& lo, int P, const bool has_grad[FDGS_N
         p.off_RZ[j] = o; if (j < p.nheads) o += al(p.Pp * lo.Wn);
         p.off_GZ[j] = o; if (j < p.nheads) o += al(p.Pp * lo.Wn);
     }
+    p.off_wacc = o; o += (long long)WACC_CTAS * 128 * 128;      // per-CTA FP32 sums of the weight kernel (WArgs::priv)
     p.total_floats = o;
     return p;
 }
@@ -1062,14 +1064,21 @@ struct WJob {
                                              // MMA padded to N = 16 (the job then costs about a third of a tensor-core one)
 };
 constexpr int MAXJOBS = 2 * FDGS_NUM_HEADS + 1;
-struct WArgs { WJob j[MAXJOBS]; int njobs; long long rows; };   // rows = Pp (multiple of 128)
+struct WArgs {
+    WJob j[MAXJOBS]; int njobs; long long rows;    // rows = Pp (multiple of 128)
+    // Block-wise accumulation of the tensor-core jobs: the TMEM accumulator adds with truncation, so a CTA that sums its
+    // whole slice (586 stages = 18.7 k points at 300 k Gaussians) in it drifts (1.2e-4 of the reference on dW0, measured);
+    // every `flush` stages the accumulator is drained into a per-CTA FP32 buffer `priv` ([CTA][n][m], plain read-add-write:
+    // only this CTA touches it) and the next block starts fresh in the other of two TMEM accumulators.  0: one block.
+    int flush; float* priv;
+};
 
 constexpr int WK = 32;             // points per stage
 constexpr int TSTAGES = 2;         // formatted (hi/lo tile32) operand stages feeding the tensor core
 constexpr int RSTAGES = 3;         // raw FP32 stages filled by bulk async copies
 constexpr int NSW = 16;            // staging / epilogue warps
 constexpr int W_THREADS = (NSW + 2) * 32;   // + MMA warp + bulk-copy producer warp
-constexpr int WB_TFULL = 0, WB_TEMPTY = 2, WB_RFULL = 4, WB_REMPTY = 7, WB_DONE = 10, WB_COUNT = 11;
+constexpr int WB_TFULL = 0, WB_TEMPTY = 2, WB_RFULL = 4, WB_REMPTY = 7, WB_DONE = 10 /* +1: one per TMEM accumulator */, WB_COUNT = 12;
 
 __device__ __forceinline__ float4 load4(const float* __restrict__ base, int ld, long long r, int c, int ncols, long long nrows) {
     float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -1081,6 +1090,48 @@ __device__ __forceinline__ float4 load4(const float* __restrict__ base, int ld, 
     if (c + 2 < ncols) v.z = p[2];
     if (c + 3 < ncols) v.w = p[3];
     return v;
+}
+
+// Drains one accumulation block of a tensor-core job (WArgs::flush): TMEM accumulator -> per-CTA FP32 sums (block 0 stores,
+// the middle blocks add, the last block adds and sends the sum to the caller's gradient with one reduction per element).
+// Every thread meets the same (m, n) elements in every drain, so the per-CTA buffer needs no synchronisation.
+// NOT inlined on purpose: inlined into k_deform_bwd_weights its registers and spills changed the allocation of the stage loop,
+// which is sensitive to it (535 -> 600-690 us per view with identical loop source, measured).
+#ifndef FDGS_W_DRAIN
+#define FDGS_W_DRAIN 1      // 0: inline, 16-column groups; 1: inline, 8-column groups; 2: the function below; 3: as 1, loop not unrolled
+#endif
+struct WDrain { uint32_t lane_base; int m, ma, nb, nb0, nb1, transposed, ldc; float* C; float* priv; bool first, last; };
+__device__ __noinline__ void w_drain(uint64_t* done_bar, uint32_t parity, WDrain d)
+{
+    mbar_wait(done_bar, parity);
+    tc_fence_after();
+    // 16-column TMEM loads (two per drain at N = 128): a tcgen05.ld issued while the tensor core works on the other
+    // accumulator waits for the MMAs in flight
+    for (int c0 = d.nb0; c0 < d.nb1; c0 += 16) {                    // warp-uniform bounds; columns beyond N16 are never used
+        // the running sums first, all 16 loads in flight together (read one by one between the stores below they serialise on
+        // the L2 round trip: 23 k cycles per drain, measured)
+        float pv[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+            const int n = c0 + j;
+            pv[j] = (!d.first && d.m < d.ma && n < d.nb1 && n < d.nb) ? __ldcg(d.priv + n * 128 + d.m) : 0.f;
+        }
+        uint32_t v[16];
+        tmem_ld16(d.lane_base + c0, v);
+        tmem_wait_ld();
+        if (d.m < d.ma) {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+                const int n = c0 + j;
+                if (n < d.nb1 && n < d.nb) {
+                    const float x = __uint_as_float(v[j]) + pv[j];
+                    if (d.last) atomicAdd(d.transposed ? &d.C[(size_t)n * d.ldc + d.m] : &d.C[(size_t)d.m * d.ldc + n], x);
+                    else __stcg(d.priv + n * 128 + d.m, x);          // [n][m]: a warp's lanes are consecutive m
+                }
+            }
+        }
+    }
+    tc_fence_before();                                              // the loads are complete before this warp's next TFULL arrive
 }
 
 // Pipeline per CTA:  producer warp: cp.async.bulk of the stage's 32 rows of A (and B) -> raw ring (mbarrier tx bytes)
@@ -1127,7 +1178,7 @@ k_deform_bwd_weights(WArgs args)
     }
     if (tid < 128) { csumA[tid] = 0.f; csumB[tid] = 0.f; }
     for (int e = tid; e < 128 * 4; e += W_THREADS) cc_acc[e] = 0.f;
-    if (warp == NSW) tmem_alloc(&tmem_slot, 128);
+    if (warp == NSW) tmem_alloc(&tmem_slot, 256);       // two accumulators of up to 128 columns (see WArgs::flush)
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -1164,6 +1215,8 @@ k_deform_bwd_weights(WArgs args)
         if (lane == 0 && !J.cuda_core) {
             const uint32_t idesc = make_idesc_tf32(128, N16, 1, 1);
             uint32_t g = 0;
+            const uint32_t FL = args.flush > 0 ? (uint32_t)args.flush : 0xffffffffu;   // stages per accumulation block
+            uint32_t blk = 0, gi = 0;
             for (long long s = s_begin; s < s_end; ++s, ++g) {
                 const uint32_t slot = g % TSTAGES;
                 mbar_wait(&bars[WB_TFULL + slot], (g / TSTAGES) & 1);
@@ -1172,16 +1225,21 @@ k_deform_bwd_weights(WArgs args)
                 const float* Al = Ah + 4096;
                 const float* Bh = Al + 4096;
                 const float* Bl = Bh + nblkB * 1024;
+                const uint32_t tacc = tmem + (blk & 1u) * 128u;     // block b accumulates in accumulator b & 1 (drained by the
+                                                                    // staging warps when they have staged block b + 1)
 #pragma unroll
                 for (int p = 0; p < WK; p += 8) {
-                    const int acc = (g == 0 && p == 0) ? 0 : 1;
-                    mma_tf32_ss(tmem, desc_mn32(Al, WK, p, 0), desc_mn32(Bh, WK, p, 0), idesc, acc);
-                    mma_tf32_ss(tmem, desc_mn32(Ah, WK, p, 0), desc_mn32(Bl, WK, p, 0), idesc, 1);
-                    mma_tf32_ss(tmem, desc_mn32(Ah, WK, p, 0), desc_mn32(Bh, WK, p, 0), idesc, 1);
+                    const int acc = (gi == 0 && p == 0) ? 0 : 1;
+                    mma_tf32_ss(tacc, desc_mn32(Al, WK, p, 0), desc_mn32(Bh, WK, p, 0), idesc, acc);
+                    mma_tf32_ss(tacc, desc_mn32(Ah, WK, p, 0), desc_mn32(Bl, WK, p, 0), idesc, 1);
+                    mma_tf32_ss(tacc, desc_mn32(Ah, WK, p, 0), desc_mn32(Bh, WK, p, 0), idesc, 1);
                 }
                 mma_commit(&bars[WB_TEMPTY + slot]);
+                // block complete: one barrier per accumulator (a single barrier could be lapped - block b + 1 may complete
+                // before the staging warps look at block b - and the wait would then never return)
+                if (gi == FL - 1 || s == s_end - 1) mma_commit(&bars[WB_DONE + (blk & 1u)]);
+                if (++gi == FL) { gi = 0; ++blk; }
             }
-            mma_commit(&bars[WB_DONE]);
         }
         __syncwarp();
     } else {
@@ -1303,7 +1361,72 @@ k_deform_bwd_weights(WArgs args)
                 if (wantB && tid < J.nb) atomicAdd(&J.biasB[tid], csumB[tid]);
             }
         } else {
-        for (long long s = s_begin; s < s_end; ++s, ++g) {
+        // ---- block-wise accumulation (WArgs::flush): drain a completed block's TMEM accumulator -------------------------------
+        const unsigned long long FLs = args.flush > 0 ? (unsigned long long)args.flush : 0xffffffffull;
+        const long long len = s_end - s_begin;
+        const uint32_t nblk = len > 0 ? (uint32_t)(((unsigned long long)len + FLs - 1) / FLs) : 0u;
+        uint32_t next_drain = 0;
+        float* priv = args.priv ? args.priv + (size_t)blockIdx.x * (128 * 128) : nullptr;
+        // Every thread meets the same (m, n) elements in every drain, so the per-CTA buffer needs no synchronisation: block 0
+        // stores, the middle blocks add, the last block adds and sends the sum to the caller's gradient with one reduction.
+        auto drain = [&](uint32_t b) {
+            constexpr int NGc = NSW / 4;                             // warps per TMEM lane quarter: split the columns
+            const int per = ((N16 + NGc - 1) / NGc + 7) & ~7;
+            const int nb0 = (warp >> 2) * per, nb1 = nb0 + per < N16 ? nb0 + per : N16;
+#if FDGS_W_DRAIN == 2
+            WDrain d;
+            d.lane_base = tmem + (b & 1u) * 128u + ((uint32_t)((warp & 3) * 32) << 16);
+            d.m = (warp & 3) * 32 + lane; d.ma = J.ma; d.nb = J.nb; d.nb0 = nb0; d.nb1 = nb1;
+            d.transposed = J.transposed; d.ldc = J.ldc; d.C = J.C; d.priv = priv;
+            d.first = b == 0; d.last = b + 1 == nblk;
+            w_drain(&bars[WB_DONE + (b & 1u)], (b >> 1) & 1u, d);    // the (b / 2)-th completion of accumulator b & 1
+#else
+            mbar_wait(&bars[WB_DONE + (b & 1u)], (b >> 1) & 1u);     // the (b / 2)-th completion of accumulator b & 1
+            tc_fence_after();
+            const bool first = b == 0, last = b + 1 == nblk;
+            const int m = (warp & 3) * 32 + lane;
+            const uint32_t lane_base = tmem + (b & 1u) * 128u + ((uint32_t)((warp & 3) * 32) << 16);
+            constexpr int GW = (FDGS_W_DRAIN == 0) ? 16 : 8;         // columns per TMEM load
+#if FDGS_W_DRAIN == 3
+#pragma unroll 1
+#endif
+            for (int c0 = nb0; c0 < nb1; c0 += GW) {                // warp-uniform bounds; columns beyond N16 are never used
+                // the running sums first, all GW loads in flight together (read one by one between the stores below they
+                // serialise on the L2 round trip - the compiler cannot move a load above a store to the same array: 23 k
+                // cycles per drain, measured)
+                float pv[GW];
+#pragma unroll
+                for (int j = 0; j < GW; ++j) {
+                    const int n = c0 + j;
+                    pv[j] = (!first && m < J.ma && n < nb1 && n < J.nb) ? __ldcg(priv + n * 128 + m) : 0.f;
+                }
+                uint32_t v[GW];
+                if (GW == 16) tmem_ld16(lane_base + c0, reinterpret_cast<uint32_t(&)[16]>(v[0]));
+                else tmem_ld8(lane_base + c0, reinterpret_cast<uint32_t(&)[8]>(v[0]));
+                tmem_wait_ld();
+                if (m < J.ma) {
+#pragma unroll
+                    for (int j = 0; j < GW; ++j) {
+                        const int n = c0 + j;
+                        if (n < nb1 && n < J.nb) {
+                            const float x = __uint_as_float(v[j]) + pv[j];
+                            if (last) atomicAdd(J.transposed ? &J.C[(size_t)n * J.ldc + m] : &J.C[(size_t)m * J.ldc + n], x);
+                            else __stcg(priv + n * 128 + m, x);      // [n][m]: a warp's lanes are consecutive m
+                        }
+                    }
+                }
+            }
+            tc_fence_before();                                      // the loads are complete before this warp's next TFULL arrive
+#endif
+        };
+        // Outer loop over accumulation blocks, so that the drain code stays out of the stage loop (inlined there it cost the
+        // loop 24 % - 1390 -> 1717 cycles per stage).  Block b - 2 is drained before block b is staged: the tensor core
+        // finished it long ago (no wait), and its accumulator is not written again before the first stage of block b, whose
+        // tiles this warp has not delivered yet.
+        for (long long blk_s = s_begin; blk_s < s_end; blk_s += (long long)FLs) {
+        const long long blk_e = blk_s + (long long)FLs < s_end ? blk_s + (long long)FLs : s_end;
+        if (blk_s > s_begin + (long long)FLs) drain(next_drain++);
+        for (long long s = blk_s; s < blk_e; ++s, ++g) {
             const uint32_t rslot = g % RSTAGES, tslot = g % TSTAGES;
             const float* rawA = raw0 + (size_t)rslot * raw_floats;
             const float* rawB = rawA + rawA_f;
@@ -1360,6 +1483,7 @@ k_deform_bwd_weights(WArgs args)
             __syncwarp();
             if (lane == 0) mbar_arrive(&bars[WB_TFULL + tslot]);
         }
+        }   // accumulation blocks
         // ---- bias gradients ------------------------------------------------------------------------------------
         if (wantA && onA) {
 #pragma unroll
@@ -1374,34 +1498,14 @@ k_deform_bwd_weights(WArgs args)
             if (wantA && tid < J.ma) atomicAdd(&J.biasA[tid], csumA[tid]);
             if (wantB && tid < J.nb) atomicAdd(&J.biasB[tid], csumB[tid]);
         }
-        // ---- accumulator -> global (+=) ----------------------------------------------------------------------------
-        mbar_wait(&bars[WB_DONE], 0);
-        tc_fence_after();
-        if (s_end > s_begin) {
-            const int m = (warp & 3) * 32 + lane;
-            const uint32_t lane_base = tmem + ((uint32_t)((warp & 3) * 32) << 16);
-            constexpr int NG = NSW / 4;                              // warps per TMEM lane quarter: split the columns
-            const int per = ((N16 + NG - 1) / NG + 7) & ~7;
-            const int nb0 = (warp >> 2) * per, nb1 = nb0 + per < N16 ? nb0 + per : N16;
-            for (int c0 = nb0; c0 < nb1; c0 += 8) {
-                uint32_t v[8];
-                tmem_ld8(lane_base + c0, v);
-                tmem_wait_ld();
-                if (m < J.ma) {
-#pragma unroll
-                    for (int j = 0; j < 8; ++j) {
-                        const int n = c0 + j;
-                        if (n < J.nb) atomicAdd(J.transposed ? &J.C[(size_t)n * J.ldc + m] : &J.C[(size_t)m * J.ldc + n], __uint_as_float(v[j]));
-                    }
-                }
-            }
-        }
+        // ---- remaining accumulator blocks -> per-CTA sums -> global (+=) -------------------------------------------------
+        while (next_drain < nblk) drain(next_drain++);
         }   // tensor-core path
     }
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
-    if (warp == NSW) tmem_free(tmem, 128);
+    if (warp == NSW) tmem_free(tmem, 256);
 #ifdef FDGS_PHASE_TIMING
     if (tid == 0) printf("bwd_weights cta %d job %d slice %d/%d stages %lld cycles %lld\n", (int)blockIdx.x, jb, slice, J.slices, s_end - s_begin, clock64() - t_start_);
 #endif
@@ -1541,6 +1645,10 @@ int backward(const Layout& lo, const FdgsDeformBackward* a, const float* packed,
         wa.j[i].slices = s; used += s;
     }
     for (int i = 0; used < sm_count() && i < nj; i += 2) if (wa.j[i].slices < nst) { wa.j[i].slices++; used++; }
+    // accumulation block of the tensor-core jobs (stages of 32 points); FDGS_W_FLUSH=0: one block per CTA (round-1 behaviour)
+    wa.flush = getenv("FDGS_W_FLUSH") ? atoi(getenv("FDGS_W_FLUSH")) : 32;
+    wa.priv = S + plan.off_wacc;
+    if (used > WACC_CTAS || (wa.flush > 0 && wa.flush < 8)) wa.flush = 0;
     const int nblk_max = (Wn + 31) / 32;
     const size_t wsm = ((size_t)TSTAGES * (2 * 4096 + 2 * nblk_max * 1024) + (size_t)RSTAGES * (64 * Wn)) * 4 + 1024;
     FDGS_CUDA(cudaFuncSetAttribute(k_deform_bwd_weights, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wsm));
